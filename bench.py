@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""Benchmark of the basketball step path (BASELINE.json metric: env steps/sec = worlds x steps / s).
+
+    python bench.py --gpus N --steps K --warmup W            # B200 engine (this repo)
+    python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle restatement of the
+                                                             # reference's CPU path on all host threads
+                                                             # (the Madrona CPU executor itself cannot be
+                                                             # built here: its submodule is absent)
+
+A "step" is one Manager::step() over one batch of synthetic random actions for
+this rank's worlds.  Workload at N GPUs: 8192 worlds per GPU (BASELINE.json configs[1]; 8 GPUs x 8192
+= configs[2]'s 65 536 worlds), sharded by world with no collective in the step => weak scaling.
+
+Prints ONE JSON line on rank 0.  Timing: CUDA events on the launching stream, max over ranks; L2 is
+flushed (256 MiB memset) before every timed step and the flush is outside the per-step events.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "env_steps_per_sec"
+UNIT = "world-steps/s"
+WORLDS_PER_GPU = 8192
+BYTES_PER_WORLD_STEP = 1872  # 56 in + 348 state read + 348 state write + 1120 outputs
+SEED = 1234
+LARGE_WORLDS = 1 << 20       # HBM-bound regime (working set 1.9 GB >> 126 MB L2)
+
+
+def measured_peak_gbs():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """Samples SM clock + throttle reasons through NVML while timed regions run."""
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._active = threading.Event()
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+        except Exception as e:  # NVML missing: report that instead of inventing numbers
+            self._nv = None
+            self.error = repr(e)
+
+    def _run(self):
+        nv = self._nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+            nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake",
+        }
+        while not self._stop.is_set():
+            if self._active.is_set():
+                try:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+                    for bit, name in names.items():
+                        if mask & bit:
+                            self.reasons.add(name)
+                except Exception:
+                    pass
+            time.sleep(0.002)
+
+    def __enter__(self):
+        self._active.set()
+        return self
+
+    def __exit__(self, *a):
+        self._active.clear()
+
+    def report(self):
+        self._stop.set()
+        if self._nv is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "error": getattr(self, "error", "nvml unavailable")}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def time_cpu_arm(worlds: int, steps: int, warmup: int, threads: int):
+    """Times the oracle (CPU restatement of the reference's step) on `threads` host threads."""
+    import oracle
+
+    orc = oracle.Oracle(worlds, start_x=31.515 / 2.0, start_y=16.764 / 2.0)
+    orc.run_synthetic(SEED, 0, warmup, 0, threads)
+    t0 = time.perf_counter()
+    orc.run_synthetic(SEED, warmup, steps, 0, threads)
+    dt = time.perf_counter() - t0
+    return worlds * steps / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    worlds = WORLDS_PER_GPU * args.gpus
+    # each "step" is one pass over the whole batch; bound the run to a few minutes
+    steps, warmup = args.steps, args.warmup
+    value, dt = time_cpu_arm(worlds, steps, warmup, threads)
+    sample = f"{worlds} worlds x {steps} steps (after {warmup} warm-up), synthetic random actions"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": dt / steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{WORLDS_PER_GPU} worlds per GPU x {args.gpus} = {worlds} worlds, random actions seed {SEED}, "
+                               "CPU restatement of the reference step (Madrona CPU executor unavailable on this box)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def run_engine(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from madrona_basketball_b200.shard import ShardedSimulator, env_rank
+
+    rank, local_rank, world_size = env_rank()
+    if world_size > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    n_gpus = max(world_size, 1)
+    if args.gpus != n_gpus and rank == 0:
+        print(f"[bench] --gpus {args.gpus} but WORLD_SIZE={world_size}; using {n_gpus}", file=sys.stderr)
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+
+    K, Wm = args.steps, args.warmup
+    total_worlds = args.worlds_per_gpu * n_gpus
+    shard = ShardedSimulator(total_worlds, rank=rank, world_size=n_gpus, gpu_id=local_rank)
+    sim, n = shard.sim, shard.num_worlds
+    sampler = ClockSampler(local_rank)
+
+    # inputs resident in HBM before the timed region: one action batch per step
+    actions = torch.empty((K + Wm, n, 2, 6), dtype=torch.int32, device=dev)
+    for s in range(K + Wm):
+        shard.fill_actions(SEED, s, out=actions[s])
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------------------------------------------------------- value: device-resident, per-step events
+    for s in range(Wm):
+        sim.step_with_actions(actions[s])
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    stops = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
+    launches0 = sim.launch_count()
+    barrier()
+    with sampler:
+        wall0 = time.perf_counter()
+        for s in range(K):
+            flush.zero_()                      # L2 flush, outside the events
+            starts[s].record()
+            sim.step_with_actions(actions[Wm + s])
+            stops[s].record()
+        barrier()
+        wall = time.perf_counter() - wall0
+    gpu_launches = sim.launch_count() - launches0
+    step_ms = [a.elapsed_time(b) for a, b in zip(starts, stops)]
+    dev_ms = float(sum(step_ms))
+    t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    max_ms = float(t.item())
+    value = total_worlds * K / (max_ms * 1e-3)
+
+    # ---------------------------------------------------------------- L2-warm, graph-launched (informational)
+    g = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream(dev)
+    with torch.cuda.stream(side):
+        for s in range(3):
+            sim.step_with_actions(actions[s])
+    torch.cuda.synchronize()
+    with torch.cuda.graph(g, stream=side):
+        for s in range(K):
+            sim.step_with_actions(actions[Wm + s])
+    g.replay()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with sampler:
+        e0.record()
+        g.replay()
+        e1.record()
+        barrier()
+    warm_ms = e0.elapsed_time(e1)
+    t = torch.tensor([warm_ms], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    warm_value = total_worlds * K / (float(t.item()) * 1e-3)
+
+    # ---------------------------------------------------------------- e2e: host buffers through the C ABI
+    h_act = torch.empty((n, 2, 6), dtype=torch.int32).pin_memory()
+    h_rew = torch.empty((n, 2), dtype=torch.float32).pin_memory()
+    h_done = torch.empty((n, 2), dtype=torch.float32).pin_memory()
+    h_actions_all = actions[Wm:Wm + min(K, 64)].cpu()  # host-side source batches (cycled)
+    np_act, np_rew, np_done = h_act.numpy(), h_rew.numpy(), h_done.numpy()
+    for s in range(Wm):
+        sim.step_host(np_act, np_rew, np_done)
+    barrier()
+    with sampler:
+        t0 = time.perf_counter()
+        for s in range(K):
+            h_act.copy_(h_actions_all[s % h_actions_all.shape[0]])   # this step's inputs, in pinned host memory
+            sim.step_host(np_act, np_rew, np_done)                    # H2D + step + D2H, synchronous
+        barrier()
+        e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = total_worlds * K / float(t.item())
+    h2d, d2h = n * 48, n * 16
+
+    # ---------------------------------------------------------------- roofline
+    peak, peak_src = measured_peak_gbs()
+    avg_kernel_s = (dev_ms / K) * 1e-3
+    achieved = n * BYTES_PER_WORLD_STEP / avg_kernel_s / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "bb_step_kernel", "worlds_per_launch": n,
+                "algorithmic_bytes_per_launch": n * BYTES_PER_WORLD_STEP, "peak_source": peak_src,
+                "note": "8192 worlds (15 MB) is latency/launch-bound by construction; see roofline_hbm_bound"}
+
+    roofline_large = None
+    cpu_baseline = None
+    if rank == 0 and n_gpus == 1:
+        # HBM-bound regime: 2^20 worlds on one GPU, same kernel
+        del sim, shard
+        big = ShardedSimulator(LARGE_WORLDS, rank=0, world_size=1, gpu_id=local_rank)
+        bsim = big.sim
+        bact = torch.empty((4, LARGE_WORLDS, 2, 6), dtype=torch.int32, device=dev)
+        for s in range(4):
+            big.fill_actions(SEED, s, out=bact[s])
+        for s in range(3):
+            bsim.step_with_actions(bact[s % 4])
+        reps = 20
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+        torch.cuda.synchronize()
+        with sampler:
+            for s in range(reps):
+                ev[s][0].record()
+                bsim.step_with_actions(bact[s % 4])
+                ev[s][1].record()
+            torch.cuda.synchronize()
+        ms = sorted(a.elapsed_time(b) for a, b in ev)
+        avg = sum(ms) / len(ms) * 1e-3
+        ach = LARGE_WORLDS * BYTES_PER_WORLD_STEP / avg / 1e9
+        roofline_large = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                          "traffic": None, "worlds_per_launch": LARGE_WORLDS, "ms_per_launch": avg * 1e3,
+                          "world_steps_per_s": LARGE_WORLDS / avg,
+                          "note": "working set 1.9 GB > L2, so no flush needed; same kernel as the bench workload"}
+        del bsim, big, bact
+        threads = os.cpu_count() or 1
+        cpu_steps = args.cpu_steps
+        cv, cdt = time_cpu_arm(args.worlds_per_gpu, cpu_steps, 5, threads)
+        cpu_baseline = {"value": cv, "unit": UNIT, "cores": threads, "kind": "port",
+                        "sample": f"{args.worlds_per_gpu} worlds x {cpu_steps} steps, {cdt:.1f} s of CPU work; oracle/ restatement "
+                                  "(the reference's Madrona CPU executor cannot be built: submodule absent)"}
+
+    clocks = sampler.report()
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": K, "warmup": Wm,
+            "ms_per_step": max_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.worlds_per_gpu} worlds per GPU x {n_gpus} GPU = {total_worlds} worlds, 2 agents + ball per world, "
+                                   f"random actions for both agents (Threefry, seed {SEED}), sim seed 0",
+                       "l2": "flushed before every timed step (256 MiB memset outside the per-step CUDA events)",
+                       "parallelism": f"world-sharded x{n_gpus}, no collective in the step"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "what": "bb_step_host: pinned-host actions H2D, step, reward+done D2H, synchronous per step"},
+            "gpu_launches": int(gpu_launches),
+            "clocks": clocks,
+            "roofline": roofline,
+            "roofline_hbm_bound": roofline_large,
+            "cpu_baseline": cpu_baseline,
+            "l2_warm_graph": {"value": warm_value, "unit": UNIT,
+                              "what": "same K steps replayed as one CUDA graph, no L2 flush (informational)"},
+            "wall_s_timed_region": wall,
+        }
+        print(json.dumps(line))
+    if world_size > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
+    ap.add_argument("--worlds-per-gpu", type=int, default=WORLDS_PER_GPU)
+    ap.add_argument("--cpu-steps", type=int, default=1000)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_engine(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,777 @@
+/*
+ * bb_engine.cu — kernels + C ABI (include/bb_engine.h) of the B200 step engine.
+ *
+ * Replaces Manager / Impl / MWCudaExecutor of the reference
+ * (/root/reference/src/mgr.cpp) for the step path: one fused kernel per
+ * Manager::step() instead of Madrona's 19 ParallelForNodes + 3 sorts
+ * (game.cpp:1467-1523, sim.cpp:100-136).
+ *
+ * Data layout: one device column per component, in exactly the AoS-per-component
+ * layout the reference exports (mgr.cpp:317-445), so exported pointers ARE the
+ * simulation state (zero-copy torch views, writable from Python like the
+ * reference's).  World slots are fixed (world w owns rows w*k..w*k+k-1), which is
+ * why the reference's GPU-only sort-by-world pass has no equivalent here.
+ *
+ * Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false (bit-exact
+ * float parity with the CPU oracle needs unfused multiply-add).
+ */
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "../../include/bb_engine.h"
+#include "bb_world.cuh"
+
+namespace bb {
+
+/* ------------------------------ columns ----------------------------------- */
+struct Columns {
+    int32_t *reset;        /* [N,2]     */
+    float *gameState;      /* [N,14] (int fields stored as bit patterns) */
+    int32_t *action;       /* [N,2,6]   */
+    int32_t *actionMask;   /* [N,2,4]   */
+    float *agentPos;       /* [N,2,3]   */
+    float *obs;            /* [N,2,128] */
+    float *reward;         /* [N,2]     */
+    float *done;           /* [N,2]     */
+    int32_t *agentEntity;  /* [N,2,2]  {gen,id} */
+    int32_t *possession;   /* [N,2,3]   */
+    float *orientation;    /* [N,2,4]   */
+    int32_t *team;         /* [N,2,5]   */
+    float *stats;          /* [N,2,2]   */
+    float *ballPos;        /* [N,3]     */
+    int32_t *ballPhysics;  /* [N,7]     */
+    int32_t *ballEntity;   /* [N,2]     */
+    int32_t *grabbed;      /* [N,2]     */
+    float *ballVel;        /* [N,3]     */
+    float *hoopPos;        /* [N,2,3]   */
+    float *agentVel;       /* [N,2,3]   */
+    int32_t *inbounding;   /* [N,2,2]   */
+    float *cooldown;       /* [N,2]     */
+    float *attributes;     /* [N,2,9]   */
+    uint32_t *curStep;     /* [N,2]     */
+    int32_t *worldClock;   /* [N]       */
+    uint32_t *rngCount;    /* [N]       */
+};
+
+/* bytes per world of each column, in canonical (checksum) order */
+static const int kColBytes[26] = {8, 56, 48, 32, 24, 1024, 8, 8, 16, 24, 32, 40, 16, 12, 28, 8, 8, 12, 24,
+                                  24, 16, 8, 72, 8, 4, 4};
+
+struct StepParams {
+    Columns col;
+    SimConst sc;
+    const int32_t *actionSrc; /* optional external Action source, [N,2,6] */
+    int64_t numWorlds;
+};
+
+/* ------------------------------ obs image --------------------------------- *
+ * Observation rows (game.cpp:1256-1460, layout SURVEY App. A) are 55 % of the
+ * step's bytes.  The owning thread writes the ~100 distinct values of its world
+ * once into a shared-memory "image" (feature k at word p(k) of a 109-word,
+ * odd-stride row: conflict-free for thread-per-world writes); then the warp
+ * emits both agents' 512-byte rows for its 32 worlds with 16-byte coalesced
+ * stores, lane L owning columns 4L..4L+3.  p(k) puts k, k+4, k+8.. in
+ * consecutive words so those gathers are conflict-free too.  Agent 1's row is a
+ * block permutation of agent 0's (self <-> opponent blocks, scores and hoops
+ * swapped), so one image serves both rows. */
+constexpr int kFeat = 108;        /* feature slots: 0..103 row-0 image, 104..106 row-1 vec_to, 107 zero */
+constexpr int kFeatStride = 109;  /* odd */
+constexpr int kZeroFeat = 107;
+
+BBD int feat_pos(int k) { return (k & 3) * 27 + (k >> 2); }
+
+/* obs column -> feature, row of agent 0 */
+BBD int row0_src(int cidx) { return (cidx >= 103 || (cidx >= 26 && cidx <= 29)) ? kZeroFeat : cidx; }
+/* obs column -> feature, row of agent 1 */
+BBD int row1_src(int cidx)
+{
+    if (cidx >= 103) return kZeroFeat;
+    if (cidx == 5) return 6;
+    if (cidx == 6) return 5;
+    if (cidx >= 17 && cidx <= 19) return cidx + 3;
+    if (cidx >= 20 && cidx <= 22) return cidx - 3;
+    if (cidx >= 23 && cidx <= 25) return cidx + 38;
+    if (cidx >= 26 && cidx <= 29) return kZeroFeat;
+    if (cidx >= 30 && cidx <= 60) return cidx + 38;
+    if (cidx >= 61 && cidx <= 63) return cidx - 38;
+    if (cidx >= 64 && cidx <= 66) return cidx + 40;
+    if (cidx == 67) return 67;
+    if (cidx >= 68 && cidx <= 98) return cidx - 38;
+    return cidx;
+}
+
+struct AgentFeat {
+    Vec3 ov, vn, hoopDir, ballDir;
+    float speed, vdot, accel, hoopDist, ballDist;
+};
+
+/* per-agent part of game.cpp:1290-1322 (self block) == 1384-1421 (opponent block) */
+BBD AgentFeat agent_features(const AgentS &A, Vec3 ownAttackHoop, Vec3 ballPos)
+{
+    AgentFeat f;
+    f.ov = rotate_vec(A.q, v3(0.f, 1.f, 0.f));
+    bool moving = len2(A.vel) > 1e-6f;
+    f.vn = moving ? normalize(A.vel) : v3(0.f, 0.f, 0.f);
+    f.speed = len(A.vel);
+    f.vdot = moving ? dot(f.vn, f.ov) : 0.f;
+    f.accel = (f.vdot <= 0.8f) ? 0.1f : 1.f;
+    Vec3 dh = ownAttackHoop - A.pos;
+    f.hoopDist = len(dh);
+    f.hoopDir = (f.hoopDist > 1e-6f) ? normalize(dh) : v3(0.f, 0.f, 0.f);
+    Vec3 db = ballPos - A.pos;
+    f.ballDist = len(db);
+    f.ballDir = (f.ballDist > 1e-6f) ? normalize(db) : v3(0.f, 0.f, 0.f);
+    return f;
+}
+
+BBD void put(float *img, int k, float v) { img[feat_pos(k)] = v; }
+BBD void put3(float *img, int k, Vec3 v) { put(img, k, v.x); put(img, k + 1, v.y); put(img, k + 2, v.z); }
+
+BBD void put_agent_block(float *img, int base, const AgentS &A, const AgentFeat &f)
+{
+    /* offsets inside the 38-float block; [3..6] differ between self and opponent and are written by the caller */
+    put3(img, base + 0, A.pos);
+    put(img, base + 7, A.q.w); put(img, base + 8, A.q.x); put(img, base + 9, A.q.y); put(img, base + 10, A.q.z);
+    put3(img, base + 11, f.ov);
+    put3(img, base + 14, f.vn);
+    put(img, base + 17, f.speed);
+    put(img, base + 18, f.vdot);
+    put(img, base + 19, f.accel);
+    put3(img, base + 20, f.hoopDir);
+    put(img, base + 23, f.hoopDist);
+    put3(img, base + 24, f.ballDir);
+    put(img, base + 27, f.ballDist);
+    put(img, base + 28, (float)A.imInb);
+    put(img, base + 29, A.cooldown);
+    put(img, base + 30, A.maxSpeed);
+    put(img, base + 31, A.quickness);
+    put(img, base + 32, A.shooting);
+    put(img, base + 33, A.ftPct);
+    put(img, base + 34, A.reaction);
+    put(img, base + 35, A.curShot);
+    put(img, base + 36, (float)A.pointsWorth);
+    put(img, base + 37, (float)A.hasBall);
+}
+
+/* System 18 (fillObservationsSystem, game.cpp:1175-1461) for both agents -> image */
+BBD void write_obs_image(float *img, const World &W, const SimConst &c)
+{
+    const GameS &g = W.g;
+    const BallS &B = W.b;
+    put(img, 0, g.gameClock); put(img, 1, g.shotClock); put(img, 2, g.period);
+    put(img, 3, (float)g.inbInProgress); put(img, 4, g.inboundClock);
+    put(img, 5, g.team0Score); put(img, 6, g.team1Score);
+    put3(img, 7, B.pos); put3(img, 10, B.vel);
+    put(img, 13, (float)B.isGrabbed); put(img, 14, (float)B.inFlight);
+    put(img, 15, (float)B.spv); put(img, 16, (float)B.ltTeam);
+    put3(img, 17, hoop_pos(c, 1)); /* agent 0 attacks hoop 1 */
+    put3(img, 20, hoop_pos(c, 0));
+    AgentFeat f0 = agent_features(W.a[0], hoop_pos(c, 1), B.pos);
+    AgentFeat f1 = agent_features(W.a[1], hoop_pos(c, 0), B.pos);
+    put_agent_block(img, 23, W.a[0], f0);
+    put_agent_block(img, 61, W.a[1], f1);
+    /* vec_to_agent / distance (game.cpp:1334,1381-1383) seen from agent 0 and from agent 1 */
+    Vec3 v01 = W.a[1].pos - W.a[0].pos;
+    Vec3 v10 = W.a[0].pos - W.a[1].pos;
+    float l2 = len2(v01);
+    float dist = bb_sqrtf(l2);
+    Vec3 n01 = v3(0.f, 0.f, 0.f), n10 = v3(0.f, 0.f, 0.f);
+    if (l2 > 1e-6f) { float inv = bb_divf(1.f, dist); n01 = v01 * inv; n10 = v10 * inv; }
+    put3(img, 64, n01); put(img, 67, dist);
+    put3(img, 104, n10);
+    /* one-hots (game.cpp:1441-1452) */
+    int32_t inbounder = -1;
+    if ((float)W.a[0].imInb > 0.5f) inbounder = agent_id(W, 0);
+    if ((float)W.a[1].imInb > 0.5f) inbounder = agent_id(W, 1);
+    put(img, 99, (agent_id(W, 0) == B.holder) ? 1.f : 0.f);
+    put(img, 100, (agent_id(W, 1) == B.holder) ? 1.f : 0.f);
+    put(img, 101, (agent_id(W, 0) == inbounder) ? 1.f : 0.f);
+    put(img, 102, (agent_id(W, 1) == inbounder) ? 1.f : 0.f);
+    put(img, kZeroFeat, 0.f);
+}
+
+/* ------------------------------ load / store ------------------------------ */
+BBD void load_world(World &W, const StepParams &p, int64_t w)
+{
+    const Columns &C = p.col;
+    W.idBase = (int32_t)(w * 5);
+    {
+        const int4 *ap = reinterpret_cast<const int4 *>((p.actionSrc ? p.actionSrc : C.action) + w * 12);
+        int4 a0 = ap[0], a1 = ap[1], a2 = ap[2];
+        W.a[0].move = a0.x; W.a[0].moveAngle = a0.y; W.a[0].rotate = a0.z; W.a[0].grab = a0.w;
+        W.a[0].pass = a1.x; W.a[0].shoot = a1.y;
+        W.a[1].move = a1.z; W.a[1].moveAngle = a1.w; W.a[1].rotate = a2.x; W.a[1].grab = a2.y;
+        W.a[1].pass = a2.z; W.a[1].shoot = a2.w;
+    }
+    {
+        int2 r = *reinterpret_cast<const int2 *>(C.reset + w * 2);
+        W.a[0].reset = r.x; W.a[1].reset = r.y;
+    }
+    {
+        const float2 *pp = reinterpret_cast<const float2 *>(C.agentPos + w * 6);
+        float2 p0 = pp[0], p1 = pp[1], p2 = pp[2];
+        W.a[0].pos = v3(p0.x, p0.y, p1.x); W.a[1].pos = v3(p1.y, p2.x, p2.y);
+        const float2 *vp = reinterpret_cast<const float2 *>(C.agentVel + w * 6);
+        float2 v0 = vp[0], v1 = vp[1], v2 = vp[2];
+        W.a[0].vel = v3(v0.x, v0.y, v1.x); W.a[1].vel = v3(v1.y, v2.x, v2.y);
+    }
+    {
+        const float4 *qp = reinterpret_cast<const float4 *>(C.orientation + w * 8);
+        float4 q0 = qp[0], q1 = qp[1];
+        W.a[0].q.w = q0.x; W.a[0].q.x = q0.y; W.a[0].q.y = q0.z; W.a[0].q.z = q0.w;
+        W.a[1].q.w = q1.x; W.a[1].q.x = q1.y; W.a[1].q.y = q1.z; W.a[1].q.z = q1.w;
+    }
+    {
+        const int2 *ip = reinterpret_cast<const int2 *>(C.possession + w * 6);
+        int2 i0 = ip[0], i1 = ip[1], i2 = ip[2];
+        W.a[0].hasBall = i0.x; W.a[0].ballId = i0.y; W.a[0].pointsWorth = i1.x;
+        W.a[1].hasBall = i1.y; W.a[1].ballId = i2.x; W.a[1].pointsWorth = i2.y;
+        int4 ib = *reinterpret_cast<const int4 *>(C.inbounding + w * 4);
+        W.a[0].imInb = ib.x; W.a[0].allowedToMove = ib.y; W.a[1].imInb = ib.z; W.a[1].allowedToMove = ib.w;
+        float2 cd = *reinterpret_cast<const float2 *>(C.cooldown + w * 2);
+        W.a[0].cooldown = cd.x; W.a[1].cooldown = cd.y;
+        float4 st = *reinterpret_cast<const float4 *>(C.stats + w * 4);
+        W.a[0].points = st.x; W.a[0].fouls = st.y; W.a[1].points = st.z; W.a[1].fouls = st.w;
+        uint2 cs = *reinterpret_cast<const uint2 *>(C.curStep + w * 2);
+        W.a[0].curStep = cs.x; W.a[1].curStep = cs.y;
+    }
+    {
+        const float2 *tp = reinterpret_cast<const float2 *>(C.attributes + w * 18);
+        float2 t[9];
+#pragma unroll
+        for (int k = 0; k < 9; k++) t[k] = tp[k];
+        AgentS &A0 = W.a[0], &A1 = W.a[1];
+        A0.maxSpeed = t[0].x; A0.quickness = t[0].y; A0.shooting = t[1].x; A0.ftPct = t[1].y; A0.reaction = t[2].x;
+        A0.target = v3(t[2].y, t[3].x, t[3].y); A0.curShot = t[4].x;
+        A1.maxSpeed = t[4].y; A1.quickness = t[5].x; A1.shooting = t[5].y; A1.ftPct = t[6].x; A1.reaction = t[6].y;
+        A1.target = v3(t[7].x, t[7].y, t[8].x); A1.curShot = t[8].y;
+    }
+    {
+        const float *bp = C.ballPos + w * 3;
+        W.b.pos = v3(bp[0], bp[1], bp[2]);
+        const float *bv = C.ballVel + w * 3;
+        W.b.vel = v3(bv[0], bv[1], bv[2]);
+        const int32_t *ph = C.ballPhysics + w * 7;
+        W.b.inFlight = ph[0]; W.b.ltAgent = ph[1]; W.b.ltTeam = ph[2]; W.b.sbAgent = ph[3];
+        W.b.sbTeam = ph[4]; W.b.spv = ph[5]; W.b.goingIn = ph[6];
+        int2 gr = *reinterpret_cast<const int2 *>(C.grabbed + w * 2);
+        W.b.isGrabbed = gr.x; W.b.holder = gr.y;
+    }
+    {
+        const float2 *gp = reinterpret_cast<const float2 *>(C.gameState + w * 14);
+        float2 g0 = gp[0], g1 = gp[1], g2 = gp[2], g3 = gp[3], g4 = gp[4], g5 = gp[5], g6 = gp[6];
+        GameS &g = W.g;
+        g.inbInProgress = __float_as_int(g0.x); g.liveBall = __float_as_int(g0.y);
+        g.period = g1.x; g.teamInPoss = g1.y;
+        g.team0Hoop = __float_as_int(g2.x); g.team0Score = g2.y;
+        g.team1Hoop = __float_as_int(g3.x); g.team1Score = g3.y;
+        g.gameClock = g4.x; g.shotClock = g4.y;
+        g.scoredBaskets = g5.x; g.oobCount = g5.y;
+        g.inboundClock = g6.x; g.isOneOnOne = __float_as_int(g6.y);
+    }
+    W.resetNow = C.worldClock[w];
+    W.rng = C.rngCount[w];
+    /* mask / reward / done are fully rewritten by tick and actionMask */
+}
+
+BBD void store_world(const World &W, const StepParams &p, int64_t w, bool storeAll)
+{
+    const Columns &C = p.col;
+    {
+        int4 *ap = reinterpret_cast<int4 *>(C.action + w * 12);
+        ap[0] = make_int4(W.a[0].move, W.a[0].moveAngle, W.a[0].rotate, W.a[0].grab);
+        ap[1] = make_int4(W.a[0].pass, W.a[0].shoot, W.a[1].move, W.a[1].moveAngle);
+        ap[2] = make_int4(W.a[1].rotate, W.a[1].grab, W.a[1].pass, W.a[1].shoot);
+        int4 *mp = reinterpret_cast<int4 *>(C.actionMask + w * 8);
+        mp[0] = make_int4(W.a[0].canMove, W.a[0].canGrab, W.a[0].canPass, W.a[0].canShoot);
+        mp[1] = make_int4(W.a[1].canMove, W.a[1].canGrab, W.a[1].canPass, W.a[1].canShoot);
+    }
+    if (W.didReset || storeAll) { /* resetWorld clears Reset (gen.cpp:273) and rewrites Team (gen.cpp:283) */
+        *reinterpret_cast<int2 *>(C.reset + w * 2) = make_int2(W.a[0].reset, W.a[1].reset);
+        int32_t *tp = C.team + w * 10;
+        const bool gen = storeAll; /* generateWorld colours: constants.hpp:18-19; resetWorld: gen.cpp:258 */
+        tp[0] = 0; tp[1] = __float_as_int(0.f); tp[2] = __float_as_int(100.f); tp[3] = __float_as_int(255.f); tp[4] = hoop_id(W, 0);
+        tp[5] = 1; tp[6] = __float_as_int(gen ? 128.f : 255.f); tp[7] = __float_as_int(0.f);
+        tp[8] = __float_as_int(gen ? 128.f : 100.f); tp[9] = hoop_id(W, 1);
+    }
+    {
+        float2 *pp = reinterpret_cast<float2 *>(C.agentPos + w * 6);
+        pp[0] = make_float2(W.a[0].pos.x, W.a[0].pos.y);
+        pp[1] = make_float2(W.a[0].pos.z, W.a[1].pos.x);
+        pp[2] = make_float2(W.a[1].pos.y, W.a[1].pos.z);
+        float2 *vp = reinterpret_cast<float2 *>(C.agentVel + w * 6);
+        vp[0] = make_float2(W.a[0].vel.x, W.a[0].vel.y);
+        vp[1] = make_float2(W.a[0].vel.z, W.a[1].vel.x);
+        vp[2] = make_float2(W.a[1].vel.y, W.a[1].vel.z);
+        float4 *qp = reinterpret_cast<float4 *>(C.orientation + w * 8);
+        qp[0] = make_float4(W.a[0].q.w, W.a[0].q.x, W.a[0].q.y, W.a[0].q.z);
+        qp[1] = make_float4(W.a[1].q.w, W.a[1].q.x, W.a[1].q.y, W.a[1].q.z);
+    }
+    {
+        int2 *ip = reinterpret_cast<int2 *>(C.possession + w * 6);
+        ip[0] = make_int2(W.a[0].hasBall, W.a[0].ballId);
+        ip[1] = make_int2(W.a[0].pointsWorth, W.a[1].hasBall);
+        ip[2] = make_int2(W.a[1].ballId, W.a[1].pointsWorth);
+        *reinterpret_cast<int4 *>(C.inbounding + w * 4) = make_int4(W.a[0].imInb, W.a[0].allowedToMove, W.a[1].imInb, W.a[1].allowedToMove);
+        *reinterpret_cast<float2 *>(C.cooldown + w * 2) = make_float2(W.a[0].cooldown, W.a[1].cooldown);
+        *reinterpret_cast<float4 *>(C.stats + w * 4) = make_float4(W.a[0].points, W.a[0].fouls, W.a[1].points, W.a[1].fouls);
+        *reinterpret_cast<uint2 *>(C.curStep + w * 2) = make_uint2(W.a[0].curStep, W.a[1].curStep);
+        *reinterpret_cast<float2 *>(C.reward + w * 2) = make_float2(W.a[0].reward, W.a[1].reward);
+        *reinterpret_cast<float2 *>(C.done + w * 2) = make_float2(W.a[0].done, W.a[1].done);
+    }
+    {
+        float2 *tp = reinterpret_cast<float2 *>(C.attributes + w * 18);
+        const AgentS &A0 = W.a[0], &A1 = W.a[1];
+        tp[0] = make_float2(A0.maxSpeed, A0.quickness); tp[1] = make_float2(A0.shooting, A0.ftPct);
+        tp[2] = make_float2(A0.reaction, A0.target.x); tp[3] = make_float2(A0.target.y, A0.target.z);
+        tp[4] = make_float2(A0.curShot, A1.maxSpeed); tp[5] = make_float2(A1.quickness, A1.shooting);
+        tp[6] = make_float2(A1.ftPct, A1.reaction); tp[7] = make_float2(A1.target.x, A1.target.y);
+        tp[8] = make_float2(A1.target.z, A1.curShot);
+    }
+    {
+        float *bp = C.ballPos + w * 3;
+        bp[0] = W.b.pos.x; bp[1] = W.b.pos.y; bp[2] = W.b.pos.z;
+        float *bv = C.ballVel + w * 3;
+        bv[0] = W.b.vel.x; bv[1] = W.b.vel.y; bv[2] = W.b.vel.z;
+        int32_t *ph = C.ballPhysics + w * 7;
+        ph[0] = W.b.inFlight; ph[1] = W.b.ltAgent; ph[2] = W.b.ltTeam; ph[3] = W.b.sbAgent;
+        ph[4] = W.b.sbTeam; ph[5] = W.b.spv; ph[6] = W.b.goingIn;
+        *reinterpret_cast<int2 *>(C.grabbed + w * 2) = make_int2(W.b.isGrabbed, W.b.holder);
+    }
+    {
+        float2 *gp = reinterpret_cast<float2 *>(C.gameState + w * 14);
+        const GameS &g = W.g;
+        gp[0] = make_float2(__int_as_float(g.inbInProgress), __int_as_float(g.liveBall));
+        gp[1] = make_float2(g.period, g.teamInPoss);
+        gp[2] = make_float2(__int_as_float(g.team0Hoop), g.team0Score);
+        gp[3] = make_float2(__int_as_float(g.team1Hoop), g.team1Score);
+        gp[4] = make_float2(g.gameClock, g.shotClock);
+        gp[5] = make_float2(g.scoredBaskets, g.oobCount);
+        gp[6] = make_float2(g.inboundClock, __int_as_float(g.isOneOnOne));
+    }
+    C.worldClock[w] = W.resetNow;
+    C.rngCount[w] = W.rng;
+}
+
+/* ------------------------------ kernels ----------------------------------- */
+constexpr int kThreads = 128;
+constexpr int kWarpsPerBlock = kThreads / 32;
+constexpr int kSmemBytes = kWarpsPerBlock * 32 * kFeatStride * 4;
+
+/* Coalesced emission of both observation rows of the warp's worlds from the image. */
+BBD void emit_obs_rows(const float *warpImg, float *obs, int64_t warpWorld0, int nValid, int lane)
+{
+    int off[2][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        off[0][i] = feat_pos(row0_src(lane * 4 + i));
+        off[1][i] = feat_pos(row1_src(lane * 4 + i));
+    }
+    float4 *dst = reinterpret_cast<float4 *>(obs + warpWorld0 * 256) + lane;
+#pragma unroll 4
+    for (int j = 0; j < nValid; j++) {
+        const float *img = warpImg + j * kFeatStride;
+        float4 r0 = make_float4(img[off[0][0]], img[off[0][1]], img[off[0][2]], img[off[0][3]]);
+        float4 r1 = make_float4(img[off[1][0]], img[off[1][1]], img[off[1][2]], img[off[1][3]]);
+        dst[j * 64] = r0;
+        dst[j * 64 + 32] = r1;
+    }
+}
+
+template <bool kTagMask>
+__global__ void __launch_bounds__(kThreads) bb_step_kernel(const __grid_constant__ StepParams p)
+{
+    extern __shared__ float smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float *warpImg = smem + warp * 32 * kFeatStride;
+    const int64_t w = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    const int64_t warpWorld0 = w - lane;
+    if (w < p.numWorlds) {
+        World W;
+        load_world(W, p, w);
+        step_world_logic<kTagMask>(W, p.sc);                 /* systems 1-17 */
+        write_obs_image(warpImg + lane * kFeatStride, W, p.sc); /* system 18 */
+#pragma unroll
+        for (int i = 0; i < 2; i++) sys_reward(W, i);        /* system 19 */
+        store_world(W, p, w, false);
+    }
+    __syncwarp();
+    int64_t remain = p.numWorlds - warpWorld0;
+    int nValid = remain >= 32 ? 32 : (remain > 0 ? (int)remain : 0);
+    emit_obs_rows(warpImg, p.col.obs, warpWorld0, nValid, lane);
+}
+
+/* Sim::Sim -> generateWorld (sim.cpp:86-96) for every world + the constant columns. */
+__global__ void __launch_bounds__(kThreads) bb_init_kernel(const __grid_constant__ StepParams p)
+{
+    const int64_t w = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    if (w >= p.numWorlds) return;
+    const Columns &C = p.col;
+    World W;
+    W.idBase = (int32_t)(w * 5);
+    W.rng = 0;
+    W.didReset = false;
+    generate_world(W, p.sc);
+    store_world(W, p, w, true);
+    /* entity columns {gen = 0, id} and hoops */
+    C.agentEntity[w * 4 + 0] = 0; C.agentEntity[w * 4 + 1] = agent_id(W, 0);
+    C.agentEntity[w * 4 + 2] = 0; C.agentEntity[w * 4 + 3] = agent_id(W, 1);
+    C.ballEntity[w * 2 + 0] = 0;  C.ballEntity[w * 2 + 1] = ball_id(W);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        Vec3 hp = hoop_pos(p.sc, h);
+        C.hoopPos[w * 6 + h * 3 + 0] = hp.x; C.hoopPos[w * 6 + h * 3 + 1] = hp.y; C.hoopPos[w * 6 + h * 3 + 2] = hp.z;
+    }
+}
+
+/* SURVEY 8(d) synthetic action stream; ranges scripts/env.py:96-102 */
+__global__ void bb_fill_actions_kernel(int32_t *actions, int64_t numWorlds, uint32_t seed, uint32_t step, int64_t worldOffset)
+{
+    int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; /* (world, agent) */
+    if (idx >= numWorlds * 2) return;
+    uint32_t world = (uint32_t)(idx / 2 + worldOffset), agent = (uint32_t)(idx & 1);
+    uint32_t a, b;
+    threefry2x32(seed, agent, world, step, a, b);
+    int2 *dst = reinterpret_cast<int2 *>(actions + idx * 6);
+    dst[0] = make_int2((int32_t)(a & 1u), (int32_t)((a >> 1) & 7u));
+    dst[1] = make_int2((int32_t)((a >> 8) % 3u), (int32_t)(b & 1u));
+    dst[2] = make_int2((int32_t)((b >> 1) & 1u), (int32_t)((b >> 2) & 1u));
+}
+
+struct ChecksumParams {
+    const uint32_t *col[26];
+    int words[26];
+};
+
+__global__ void bb_checksum_kernel(const __grid_constant__ ChecksumParams cp, int64_t numWorlds, uint64_t *out)
+{
+    int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= numWorlds) return;
+    uint64_t h = 0xcbf29ce484222325ull;
+    for (int c = 0; c < 26; c++) {
+        const uint32_t *ptr = cp.col[c] + w * cp.words[c];
+        for (int i = 0; i < cp.words[c]; i++) h = (h ^ ptr[i]) * 0x100000001b3ull;
+    }
+    out[w] = h;
+}
+
+} // namespace bb
+
+/* ================================ host side ================================ */
+
+static thread_local std::string g_last_error;
+
+static void set_error(const std::string &msg) { g_last_error = msg; }
+
+#define BB_CUDA_OK(expr)                                                                           \
+    do {                                                                                           \
+        cudaError_t err__ = (expr);                                                                \
+        if (err__ != cudaSuccess) {                                                                \
+            set_error(std::string(#expr) + ": " + cudaGetErrorString(err__));                      \
+            return -1;                                                                             \
+        }                                                                                          \
+    } while (0)
+
+struct bb_engine {
+    bb_config cfg;
+    int64_t N;        /* worlds */
+    int64_t Npad;     /* allocation, multiple of 32 worlds */
+    void *slab;       /* one allocation for every column */
+    size_t slabBytes;
+    void *colPtr[26];
+    bb::StepParams params;
+    cudaStream_t hostStream; /* bb_step_host / setters */
+    int64_t launches;
+};
+
+namespace {
+
+/* Host-side evaluation of the finite-domain trig of SURVEY App. E with the same
+ * spec the device uses (include/bb_math.h is bit-identical on both sides). */
+bb::Quat host_angle_axis_z(float angle)
+{
+    float c = bb_cosf(angle / 2.f), s = bb_sinf(angle / 2.f);
+    bb::Quat q;
+    q.w = c; q.x = 0.f * s; q.y = 0.f * s; q.z = 1.f * s;
+    return q;
+}
+
+void fill_sim_const(bb::SimConst &sc, const bb_config &cfg)
+{
+    /* bindings.cpp:28-51 */
+    const int32_t cells_per_meter = 1;
+    sc.startX = cfg.start_x;
+    sc.startY = cfg.start_y;
+    sc.width = (float)cfg.discrete_x / (float)cells_per_meter;
+    sc.height = (float)cfg.discrete_y / (float)cells_per_meter;
+    /* gen.cpp:96-141 */
+    volatile float court_start_x = (sc.width - bb::kCourtLen) / 2.0f;
+    volatile float hx0 = court_start_x + bb::kHoopFromBaseline;
+    volatile float t = court_start_x + bb::kCourtLen;
+    volatile float hx1 = t - bb::kHoopFromBaseline;
+    sc.hoopX[0] = hx0;
+    sc.hoopX[1] = hx1;
+    sc.hoopY = sc.height / 2.0f;
+    volatile float deg = bb::kPi / 180.f;
+    sc.turnPos = host_angle_axis_z(deg * 6);
+    sc.turnNeg = host_angle_axis_z(deg * -6);
+    sc.spawnQ[0] = host_angle_axis_z(-bb::kPi / 2.0f);
+    sc.spawnQ[1] = host_angle_axis_z(bb::kPi / 2.0f);
+    sc.piZ = host_angle_axis_z(bb::kPi);
+    for (int k = 0; k < 8; k++) {
+        volatile float ang = (float)k * bb::kAngleBetweenDirs;
+        sc.moveSin[k] = bb_sinf(ang);
+        sc.moveCos[k] = bb_cosf(ang);
+    }
+    volatile float two = 1.f * 1.f + 1.f * 1.f;
+    sc.invSqrt2 = 1.f / __builtin_sqrtf(two);
+    sc.flags = cfg.flags;
+}
+
+/* host Threefry for the world key (mgr.cpp:155 initKey, sim.cpp:89 split_i(key,0,0)) */
+void host_threefry(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t out[2])
+{
+    static const int R[8] = {13, 15, 26, 6, 17, 29, 16, 24};
+    uint32_t ks[3] = {k0, k1, 0x1BD11BDAu ^ k0 ^ k1};
+    uint32_t x0 = c0 + ks[0], x1 = c1 + ks[1];
+    for (int r = 0; r < 20; r++) {
+        x0 += x1;
+        x1 = (x1 << R[r & 7]) | (x1 >> (32 - R[r & 7]));
+        x1 ^= x0;
+        if ((r & 3) == 3) {
+            int s = r / 4 + 1;
+            x0 += ks[s % 3];
+            x1 += ks[(s + 1) % 3] + (uint32_t)s;
+        }
+    }
+    out[0] = x0;
+    out[1] = x1;
+}
+
+int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream)
+{
+    bb::StepParams p = e->params;
+    p.actionSrc = actions_dev;
+    const int blocks = (int)((e->N + bb::kThreads - 1) / bb::kThreads);
+    if (e->cfg.flags & BB_FLAG_TAG_MASK)
+        bb::bb_step_kernel<true><<<blocks, bb::kThreads, bb::kSmemBytes, stream>>>(p);
+    else
+        bb::bb_step_kernel<false><<<blocks, bb::kThreads, bb::kSmemBytes, stream>>>(p);
+    e->launches++;
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *bb_last_error(void) { return g_last_error.c_str(); }
+
+bb_engine *bb_create(const bb_config *cfg)
+{
+    g_last_error.clear();
+    if (!cfg || cfg->num_worlds <= 0) { set_error("bb_create: num_worlds must be positive"); return nullptr; }
+    int ndev = 0;
+    cudaError_t err = cudaGetDeviceCount(&ndev);
+    if (err != cudaSuccess || ndev == 0) {
+        set_error(std::string("bb_create: no CUDA device (") + cudaGetErrorString(err) +
+                  "); this engine has no CPU path");
+        return nullptr;
+    }
+    int dev = cfg->gpu_id < 0 ? 0 : cfg->gpu_id;
+    if (dev >= ndev) { set_error("bb_create: gpu_id out of range"); return nullptr; }
+    if (cudaSetDevice(dev) != cudaSuccess) { set_error("bb_create: cudaSetDevice failed"); return nullptr; }
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, dev);
+    if (prop.major != 10) {
+        set_error("bb_create: device is sm_" + std::to_string(prop.major * 10 + prop.minor) +
+                  "; libbball.so is built for sm_100a only");
+        return nullptr;
+    }
+
+    bb_engine *e = new bb_engine();
+    e->cfg = *cfg;
+    e->cfg.gpu_id = dev;
+    e->N = cfg->num_worlds;
+    e->Npad = (e->N + 31) / 32 * 32;
+    e->launches = 0;
+
+    /* one slab, every column 256-byte aligned */
+    size_t offs[26], total = 0;
+    for (int c = 0; c < 26; c++) {
+        offs[c] = total;
+        size_t bytes = (size_t)bb::kColBytes[c] * (size_t)e->Npad;
+        total += (bytes + 255) / 256 * 256;
+    }
+    e->slabBytes = total;
+    if (cudaMalloc(&e->slab, total) != cudaSuccess) {
+        set_error("bb_create: cudaMalloc of " + std::to_string(total) + " bytes failed");
+        delete e;
+        return nullptr;
+    }
+    cudaMemset(e->slab, 0, total);
+    for (int c = 0; c < 26; c++) e->colPtr[c] = (char *)e->slab + offs[c];
+
+    bb::Columns &C = e->params.col;
+    C.reset = (int32_t *)e->colPtr[0];        C.gameState = (float *)e->colPtr[1];
+    C.action = (int32_t *)e->colPtr[2];       C.actionMask = (int32_t *)e->colPtr[3];
+    C.agentPos = (float *)e->colPtr[4];       C.obs = (float *)e->colPtr[5];
+    C.reward = (float *)e->colPtr[6];         C.done = (float *)e->colPtr[7];
+    C.agentEntity = (int32_t *)e->colPtr[8];  C.possession = (int32_t *)e->colPtr[9];
+    C.orientation = (float *)e->colPtr[10];   C.team = (int32_t *)e->colPtr[11];
+    C.stats = (float *)e->colPtr[12];         C.ballPos = (float *)e->colPtr[13];
+    C.ballPhysics = (int32_t *)e->colPtr[14]; C.ballEntity = (int32_t *)e->colPtr[15];
+    C.grabbed = (int32_t *)e->colPtr[16];     C.ballVel = (float *)e->colPtr[17];
+    C.hoopPos = (float *)e->colPtr[18];       C.agentVel = (float *)e->colPtr[19];
+    C.inbounding = (int32_t *)e->colPtr[20];  C.cooldown = (float *)e->colPtr[21];
+    C.attributes = (float *)e->colPtr[22];    C.curStep = (uint32_t *)e->colPtr[23];
+    C.worldClock = (int32_t *)e->colPtr[24];  C.rngCount = (uint32_t *)e->colPtr[25];
+
+    fill_sim_const(e->params.sc, e->cfg);
+    uint32_t key[2];
+    host_threefry(cfg->rand_seed, 0u, 0u, 0u, key);
+    e->params.sc.key0 = key[0];
+    e->params.sc.key1 = key[1];
+    e->params.actionSrc = nullptr;
+    e->params.numWorlds = e->N;
+
+    cudaFuncSetAttribute(bb::bb_step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::kSmemBytes);
+    cudaFuncSetAttribute(bb::bb_step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::kSmemBytes);
+    if (cudaStreamCreateWithFlags(&e->hostStream, cudaStreamNonBlocking) != cudaSuccess) {
+        set_error("bb_create: cudaStreamCreate failed");
+        cudaFree(e->slab);
+        delete e;
+        return nullptr;
+    }
+
+    const int blocks = (int)((e->N + bb::kThreads - 1) / bb::kThreads);
+    bb::bb_init_kernel<<<blocks, bb::kThreads>>>(e->params);
+    e->launches++;
+    err = cudaDeviceSynchronize();
+    if (err != cudaSuccess) {
+        set_error(std::string("bb_create: init kernel failed: ") + cudaGetErrorString(err));
+        cudaStreamDestroy(e->hostStream);
+        cudaFree(e->slab);
+        delete e;
+        return nullptr;
+    }
+    return e;
+}
+
+void bb_destroy(bb_engine *e)
+{
+    if (!e) return;
+    cudaSetDevice(e->cfg.gpu_id);
+    cudaDeviceSynchronize();
+    cudaStreamDestroy(e->hostStream);
+    cudaFree(e->slab);
+    delete e;
+}
+
+int bb_step(bb_engine *e, void *cuda_stream) { return launch_step(e, nullptr, (cudaStream_t)cuda_stream); }
+
+int bb_step_with_actions(bb_engine *e, const int32_t *actions_dev, void *cuda_stream)
+{
+    return launch_step(e, actions_dev, (cudaStream_t)cuda_stream);
+}
+
+int bb_step_host(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host, float *obs_host)
+{
+    cudaStream_t s = e->hostStream;
+    const bb::Columns &C = e->params.col;
+    if (actions_host)
+        BB_CUDA_OK(cudaMemcpyAsync(C.action, actions_host, (size_t)e->N * 48, cudaMemcpyHostToDevice, s));
+    if (launch_step(e, nullptr, s) != 0) return -1;
+    if (reward_host) BB_CUDA_OK(cudaMemcpyAsync(reward_host, C.reward, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
+    if (done_host) BB_CUDA_OK(cudaMemcpyAsync(done_host, C.done, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
+    if (obs_host) BB_CUDA_OK(cudaMemcpyAsync(obs_host, C.obs, (size_t)e->N * 1024, cudaMemcpyDeviceToHost, s));
+    BB_CUDA_OK(cudaStreamSynchronize(s));
+    return 0;
+}
+
+int bb_export(bb_engine *e, int slot, void **dev_ptr, int *dtype, int64_t dims[4], int *ndim, int *device)
+{
+    struct Desc { int slot, col, dtype, ndim; int64_t d1, d2; };
+    static const Desc table[] = {
+        {BB_SLOT_RESET, 0, BB_DTYPE_I32, 3, 2, 1},           {BB_SLOT_GAME_STATE, 1, BB_DTYPE_F32, 2, 14, 0},
+        {BB_SLOT_ACTION, 2, BB_DTYPE_I32, 3, 2, 6},          {BB_SLOT_ACTION_MASK, 3, BB_DTYPE_I32, 3, 2, 4},
+        {BB_SLOT_AGENT_POS, 4, BB_DTYPE_F32, 3, 2, 3},       {BB_SLOT_OBSERVATIONS, 5, BB_DTYPE_F32, 3, 2, 128},
+        {BB_SLOT_REWARD, 6, BB_DTYPE_F32, 2, 2, 0},          {BB_SLOT_DONE, 7, BB_DTYPE_F32, 2, 2, 0},
+        {BB_SLOT_AGENT_ENTITY_ID, 8, BB_DTYPE_I32, 2, 2, 0}, {BB_SLOT_AGENT_POSSESSION, 9, BB_DTYPE_I32, 3, 2, 3},
+        {BB_SLOT_ORIENTATION, 10, BB_DTYPE_F32, 3, 2, 4},    {BB_SLOT_TEAM_DATA, 11, BB_DTYPE_I32, 3, 2, 5},
+        {BB_SLOT_AGENT_STATS, 12, BB_DTYPE_I32, 3, 2, 2},    {BB_SLOT_BASKETBALL_POS, 13, BB_DTYPE_F32, 3, 1, 3},
+        {BB_SLOT_BALL_PHYSICS, 14, BB_DTYPE_I32, 3, 1, 7},   {BB_SLOT_BALL_ENTITY_ID, 15, BB_DTYPE_I32, 2, 1, 0},
+        {BB_SLOT_BALL_GRABBED, 16, BB_DTYPE_I32, 3, 1, 2},   {BB_SLOT_BALL_VELOCITY, 17, BB_DTYPE_F32, 3, 1, 3},
+        {BB_SLOT_HOOP_POS, 18, BB_DTYPE_F32, 3, 2, 3},
+        {BB_SLOT_AGENT_VELOCITY, 19, BB_DTYPE_F32, 3, 2, 3}, {BB_SLOT_INBOUNDING, 20, BB_DTYPE_I32, 3, 2, 2},
+        {BB_SLOT_GRAB_COOLDOWN, 21, BB_DTYPE_F32, 2, 2, 0},  {BB_SLOT_ATTRIBUTES, 22, BB_DTYPE_F32, 3, 2, 9},
+        {BB_SLOT_CUR_STEP, 23, BB_DTYPE_I32, 2, 2, 0},       {BB_SLOT_WORLD_CLOCK, 24, BB_DTYPE_I32, 1, 0, 0},
+        {BB_SLOT_RNG_COUNT, 25, BB_DTYPE_I32, 1, 0, 0},
+    };
+    for (const Desc &d : table) {
+        if (d.slot != slot) continue;
+        *dev_ptr = e->colPtr[d.col];
+        *dtype = d.dtype;
+        *ndim = d.ndim;
+        dims[0] = e->N; dims[1] = d.d1; dims[2] = d.d2; dims[3] = 0;
+        *device = e->cfg.gpu_id;
+        return 0;
+    }
+    set_error("bb_export: unknown slot " + std::to_string(slot));
+    return -1;
+}
+
+int bb_set_action(bb_engine *e, int32_t world_idx, int32_t agent_idx, int32_t move_speed, int32_t move_angle,
+                  int32_t rotate, int32_t grab, int32_t pass, int32_t shoot)
+{
+    if (world_idx >= 0 && world_idx < (int32_t)e->N && agent_idx >= 0 && agent_idx < 2) {
+        int32_t host[6] = {move_speed, move_angle, rotate, grab, pass, shoot};
+        int32_t *dst = e->params.col.action + ((int64_t)world_idx * 2 + agent_idx) * 6;
+        BB_CUDA_OK(cudaMemcpy(dst, host, sizeof host, cudaMemcpyHostToDevice));
+    } else {
+        /* mgr.cpp:288-292 */
+        printf("ERROR: Invalid indices! world=%d (max=%d), agent=%d (max=%d)\n", world_idx, (int32_t)e->N - 1, agent_idx, 1);
+    }
+    return 0;
+}
+
+int bb_trigger_reset(bb_engine *e, int32_t world_idx)
+{
+    if (world_idx >= 0 && world_idx < (int32_t)e->N) {
+        int32_t host[2] = {1, 1};
+        BB_CUDA_OK(cudaMemcpy(e->params.col.reset + (int64_t)world_idx * 2, host, sizeof host, cudaMemcpyHostToDevice));
+    }
+    return 0;
+}
+
+int bb_fill_actions(bb_engine *e, int32_t *actions_dev, uint32_t seed, int64_t step, int64_t world_offset, void *cuda_stream)
+{
+    int32_t *dst = actions_dev ? actions_dev : e->params.col.action;
+    const int64_t n = e->N * 2;
+    bb::bb_fill_actions_kernel<<<(int)((n + 255) / 256), 256, 0, (cudaStream_t)cuda_stream>>>(dst, e->N, seed, (uint32_t)step, world_offset);
+    e->launches++;
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int bb_checksum(bb_engine *e, uint64_t *out_dev, void *cuda_stream)
+{
+    bb::ChecksumParams cp;
+    for (int c = 0; c < 26; c++) {
+        cp.col[c] = (const uint32_t *)e->colPtr[c];
+        cp.words[c] = bb::kColBytes[c] / 4;
+    }
+    bb::bb_checksum_kernel<<<(int)((e->N + 127) / 128), 128, 0, (cudaStream_t)cuda_stream>>>(cp, e->N, out_dev);
+    e->launches++;
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int64_t bb_launch_count(const bb_engine *e) { return e->launches; }
+int64_t bb_num_worlds(const bb_engine *e) { return e->N; }
+
+} // extern "C"
