@@ -22,7 +22,7 @@
 #include <string>
 
 #include "../../include/bb_engine.h"
-#include "bb_world.cuh"
+#include "bb_pair.cuh"
 
 namespace bb {
 
@@ -69,17 +69,17 @@ struct StepParams {
 
 /* ------------------------------ obs image --------------------------------- *
  * Observation rows (game.cpp:1256-1460, layout SURVEY App. A) are 55 % of the
- * step's bytes.  The owning thread writes the ~100 distinct values of its world
- * once into a shared-memory "image" (feature k at word p(k) of a 109-word,
- * odd-stride row: conflict-free for thread-per-world writes); then the warp
- * emits both agents' 512-byte rows for its 32 worlds with 16-byte coalesced
- * stores, lane L owning columns 4L..4L+3.  p(k) puts k, k+4, k+8.. in
- * consecutive words so those gathers are conflict-free too.  Agent 1's row is a
- * block permutation of agent 0's (self <-> opponent blocks, scores and hoops
- * swapped), so one image serves both rows. */
+ * step's bytes.  The lane pair of a world writes the ~100 distinct values of that
+ * world once into a shared-memory "image" (feature k at word p(k) of a 109-word,
+ * odd-stride row); then the warp emits both agents' 512-byte rows for its 16
+ * worlds with 16-byte coalesced stores, lane L owning columns 4L..4L+3.  p(k)
+ * puts k, k+4, k+8.. in consecutive words so those gathers are conflict-free.
+ * Agent 1's row is a block permutation of agent 0's (self <-> opponent blocks,
+ * scores and hoops swapped), so one image serves both rows. */
 constexpr int kFeat = 108;        /* feature slots: 0..103 row-0 image, 104..106 row-1 vec_to, 107 zero */
 constexpr int kFeatStride = 109;  /* odd */
 constexpr int kZeroFeat = 107;
+constexpr int kWorldsPerWarp = 16;
 
 BBD int feat_pos(int k) { return (k & 3) * 27 + (k >> 2); }
 
@@ -103,167 +103,142 @@ BBD int row1_src(int cidx)
     return cidx;
 }
 
-struct AgentFeat {
-    Vec3 ov, vn, hoopDir, ballDir;
-    float speed, vdot, accel, hoopDist, ballDist;
-};
-
-/* per-agent part of game.cpp:1290-1322 (self block) == 1384-1421 (opponent block) */
-BBD AgentFeat agent_features(const AgentS &A, Vec3 ownAttackHoop, Vec3 ballPos)
-{
-    AgentFeat f;
-    f.ov = rotate_vec(A.q, v3(0.f, 1.f, 0.f));
-    bool moving = len2(A.vel) > 1e-6f;
-    f.vn = moving ? normalize(A.vel) : v3(0.f, 0.f, 0.f);
-    f.speed = len(A.vel);
-    f.vdot = moving ? dot(f.vn, f.ov) : 0.f;
-    f.accel = (f.vdot <= 0.8f) ? 0.1f : 1.f;
-    Vec3 dh = ownAttackHoop - A.pos;
-    f.hoopDist = len(dh);
-    f.hoopDir = (f.hoopDist > 1e-6f) ? normalize(dh) : v3(0.f, 0.f, 0.f);
-    Vec3 db = ballPos - A.pos;
-    f.ballDist = len(db);
-    f.ballDir = (f.ballDist > 1e-6f) ? normalize(db) : v3(0.f, 0.f, 0.f);
-    return f;
-}
-
 BBD void put(float *img, int k, float v) { img[feat_pos(k)] = v; }
 BBD void put3(float *img, int k, Vec3 v) { put(img, k, v.x); put(img, k + 1, v.y); put(img, k + 2, v.z); }
 
-BBD void put_agent_block(float *img, int base, const AgentS &A, const AgentFeat &f)
+/* System 18 (fillObservationsSystem, game.cpp:1175-1461): each lane writes its own
+ * agent's 38-float block (self block of its row == opponent block of the partner's
+ * row, game.cpp:1290-1322 / 1380-1421); lane 0 adds the game / ball / hoop header,
+ * lane 1 the agent-to-agent vectors and the one-hots. */
+BBD void write_obs_image(float *img, const Lane &L, Vec3 opos, int32_t oInb, const SimConst &c)
 {
-    /* offsets inside the 38-float block; [3..6] differ between self and opponent and are written by the caller */
-    put3(img, base + 0, A.pos);
-    put(img, base + 7, A.q.w); put(img, base + 8, A.q.x); put(img, base + 9, A.q.y); put(img, base + 10, A.q.z);
-    put3(img, base + 11, f.ov);
-    put3(img, base + 14, f.vn);
-    put(img, base + 17, f.speed);
-    put(img, base + 18, f.vdot);
-    put(img, base + 19, f.accel);
-    put3(img, base + 20, f.hoopDir);
-    put(img, base + 23, f.hoopDist);
-    put3(img, base + 24, f.ballDir);
-    put(img, base + 27, f.ballDist);
-    put(img, base + 28, (float)A.imInb);
-    put(img, base + 29, A.cooldown);
-    put(img, base + 30, A.maxSpeed);
-    put(img, base + 31, A.quickness);
-    put(img, base + 32, A.shooting);
-    put(img, base + 33, A.ftPct);
-    put(img, base + 34, A.reaction);
-    put(img, base + 35, A.curShot);
-    put(img, base + 36, (float)A.pointsWorth);
-    put(img, base + 37, (float)A.hasBall);
-}
-
-/* System 18 (fillObservationsSystem, game.cpp:1175-1461) for both agents -> image */
-BBD void write_obs_image(float *img, const World &W, const SimConst &c)
-{
-    const GameS &g = W.g;
-    const BallS &B = W.b;
-    put(img, 0, g.gameClock); put(img, 1, g.shotClock); put(img, 2, g.period);
-    put(img, 3, (float)g.inbInProgress); put(img, 4, g.inboundClock);
-    put(img, 5, g.team0Score); put(img, 6, g.team1Score);
-    put3(img, 7, B.pos); put3(img, 10, B.vel);
-    put(img, 13, (float)B.isGrabbed); put(img, 14, (float)B.inFlight);
-    put(img, 15, (float)B.spv); put(img, 16, (float)B.ltTeam);
-    put3(img, 17, hoop_pos(c, 1)); /* agent 0 attacks hoop 1 */
-    put3(img, 20, hoop_pos(c, 0));
-    AgentFeat f0 = agent_features(W.a[0], hoop_pos(c, 1), B.pos);
-    AgentFeat f1 = agent_features(W.a[1], hoop_pos(c, 0), B.pos);
-    put_agent_block(img, 23, W.a[0], f0);
-    put_agent_block(img, 61, W.a[1], f1);
-    /* vec_to_agent / distance (game.cpp:1334,1381-1383) seen from agent 0 and from agent 1 */
-    Vec3 v01 = W.a[1].pos - W.a[0].pos;
-    Vec3 v10 = W.a[0].pos - W.a[1].pos;
-    float l2 = len2(v01);
-    float dist = bb_sqrtf(l2);
-    Vec3 n01 = v3(0.f, 0.f, 0.f), n10 = v3(0.f, 0.f, 0.f);
-    if (l2 > 1e-6f) { float inv = bb_divf(1.f, dist); n01 = v01 * inv; n10 = v10 * inv; }
-    put3(img, 64, n01); put(img, 67, dist);
-    put3(img, 104, n10);
-    /* one-hots (game.cpp:1441-1452) */
-    int32_t inbounder = -1;
-    if ((float)W.a[0].imInb > 0.5f) inbounder = agent_id(W, 0);
-    if ((float)W.a[1].imInb > 0.5f) inbounder = agent_id(W, 1);
-    put(img, 99, (agent_id(W, 0) == B.holder) ? 1.f : 0.f);
-    put(img, 100, (agent_id(W, 1) == B.holder) ? 1.f : 0.f);
-    put(img, 101, (agent_id(W, 0) == inbounder) ? 1.f : 0.f);
-    put(img, 102, (agent_id(W, 1) == inbounder) ? 1.f : 0.f);
-    put(img, kZeroFeat, 0.f);
+    const AgentS &A = L.A;
+    const BallS &B = L.B;
+    const int base = L.me ? 61 : 23;
+    {
+        Vec3 ov = rotate_vec(A.q, v3(0.f, 1.f, 0.f));
+        bool moving = len2(A.vel) > 1e-6f;
+        Vec3 vn = moving ? normalize(A.vel) : v3(0.f, 0.f, 0.f);
+        float vdot = moving ? dot(vn, ov) : 0.f;
+        Vec3 dh = v3(L.me ? c.hoopX[0] : c.hoopX[1], c.hoopY, 0.f) - A.pos; /* the hoop this agent attacks */
+        float hoopDist = len(dh);
+        Vec3 hoopDir = (hoopDist > 1e-6f) ? normalize(dh) : v3(0.f, 0.f, 0.f);
+        Vec3 db = B.pos - A.pos;
+        float ballDist = len(db);
+        Vec3 ballDir = (ballDist > 1e-6f) ? normalize(db) : v3(0.f, 0.f, 0.f);
+        /* offsets inside the block; [3..6] differ between self and opponent view (written below) */
+        put3(img, base + 0, A.pos);
+        put(img, base + 7, A.q.w); put(img, base + 8, A.q.x); put(img, base + 9, A.q.y); put(img, base + 10, A.q.z);
+        put3(img, base + 11, ov);
+        put3(img, base + 14, vn);
+        put(img, base + 17, len(A.vel));
+        put(img, base + 18, vdot);
+        put(img, base + 19, (vdot <= 0.8f) ? 0.1f : 1.f);
+        put3(img, base + 20, hoopDir);
+        put(img, base + 23, hoopDist);
+        put3(img, base + 24, ballDir);
+        put(img, base + 27, ballDist);
+        put(img, base + 28, (float)A.imInb);
+        put(img, base + 29, A.cooldown);
+        put(img, base + 30, A.maxSpeed);
+        put(img, base + 31, A.quickness);
+        put(img, base + 32, A.shooting);
+        put(img, base + 33, A.ftPct);
+        put(img, base + 34, A.reaction);
+        put(img, base + 35, A.curShot);
+        put(img, base + 36, (float)A.pointsWorth);
+        put(img, base + 37, (float)A.hasBall);
+    }
+    if (L.me == 0) {
+        const GameS &g = L.G;
+        put(img, 0, g.gameClock); put(img, 1, g.shotClock); put(img, 2, g.period);
+        put(img, 3, (float)g.inbInProgress); put(img, 4, g.inboundClock);
+        put(img, 5, g.team0Score); put(img, 6, g.team1Score);
+        put3(img, 7, B.pos); put3(img, 10, B.vel);
+        put(img, 13, (float)B.isGrabbed); put(img, 14, (float)B.inFlight);
+        put(img, 15, (float)B.spv); put(img, 16, (float)B.ltTeam);
+        put3(img, 17, hoop_pos(c, 1)); /* agent 0 attacks hoop 1 */
+        put3(img, 20, hoop_pos(c, 0));
+    } else {
+        /* vec_to_agent / distance (game.cpp:1334,1381-1383) seen from agent 0 and from agent 1 */
+        Vec3 v01 = A.pos - opos;
+        Vec3 v10 = opos - A.pos;
+        float l2 = len2(v01);
+        float dist = bb_sqrtf(l2);
+        Vec3 n01 = v3(0.f, 0.f, 0.f), n10 = v3(0.f, 0.f, 0.f);
+        if (l2 > 1e-6f) { float inv = bb_divf(1.f, dist); n01 = v01 * inv; n10 = v10 * inv; }
+        put3(img, 64, n01); put(img, 67, dist);
+        put3(img, 104, n10);
+        /* one-hots (game.cpp:1441-1452): ball holder; inbounder = last agent with imInbounding */
+        const int32_t id0 = L.idBase + 3, id1 = L.idBase + 4;
+        int32_t inbounder = -1;
+        if ((float)oInb > 0.5f) inbounder = id0;
+        if ((float)A.imInb > 0.5f) inbounder = id1;
+        put(img, 99, (id0 == B.holder) ? 1.f : 0.f);
+        put(img, 100, (id1 == B.holder) ? 1.f : 0.f);
+        put(img, 101, (id0 == inbounder) ? 1.f : 0.f);
+        put(img, 102, (id1 == inbounder) ? 1.f : 0.f);
+        put(img, kZeroFeat, 0.f);
+    }
 }
 
 /* ------------------------------ load / store ------------------------------ */
-BBD void load_world(World &W, const StepParams &p, int64_t w)
+
+/* Lane (w, me): its agent's rows + the world's ball / GameState / clock / RNG rows
+ * (the pair reads the same world addresses: one broadcast transaction). */
+BBD void load_lane(Lane &L, const StepParams &p, int64_t w, int me)
 {
     const Columns &C = p.col;
-    W.idBase = (int32_t)(w * 5);
+    const int64_t r = w * 2 + me; /* agent row */
+    AgentS &A = L.A;
+    L.idBase = (int32_t)(w * 5);
+    L.me = me;
+    L.didReset = false;
     {
-        const int4 *ap = reinterpret_cast<const int4 *>((p.actionSrc ? p.actionSrc : C.action) + w * 12);
-        int4 a0 = ap[0], a1 = ap[1], a2 = ap[2];
-        W.a[0].move = a0.x; W.a[0].moveAngle = a0.y; W.a[0].rotate = a0.z; W.a[0].grab = a0.w;
-        W.a[0].pass = a1.x; W.a[0].shoot = a1.y;
-        W.a[1].move = a1.z; W.a[1].moveAngle = a1.w; W.a[1].rotate = a2.x; W.a[1].grab = a2.y;
-        W.a[1].pass = a2.z; W.a[1].shoot = a2.w;
+        const int2 *ap = reinterpret_cast<const int2 *>((p.actionSrc ? p.actionSrc : C.action) + r * 6);
+        int2 a0 = ap[0], a1 = ap[1], a2 = ap[2];
+        A.move = a0.x; A.moveAngle = a0.y; A.rotate = a1.x; A.grab = a1.y; A.pass = a2.x; A.shoot = a2.y;
+    }
+    A.reset = C.reset[r];
+    {
+        const float *pp = C.agentPos + r * 3;
+        A.pos = v3(pp[0], pp[1], pp[2]);
+        const float *vp = C.agentVel + r * 3;
+        A.vel = v3(vp[0], vp[1], vp[2]);
+        float4 q = *reinterpret_cast<const float4 *>(C.orientation + r * 4);
+        A.q.w = q.x; A.q.x = q.y; A.q.y = q.z; A.q.z = q.w;
     }
     {
-        int2 r = *reinterpret_cast<const int2 *>(C.reset + w * 2);
-        W.a[0].reset = r.x; W.a[1].reset = r.y;
+        const int32_t *ip = C.possession + r * 3;
+        A.hasBall = ip[0]; A.ballId = ip[1]; A.pointsWorth = ip[2];
+        int2 ib = *reinterpret_cast<const int2 *>(C.inbounding + r * 2);
+        A.imInb = ib.x; A.allowedToMove = ib.y;
+        A.cooldown = C.cooldown[r];
+        float2 st = *reinterpret_cast<const float2 *>(C.stats + r * 2);
+        A.points = st.x; A.fouls = st.y;
+        A.curStep = C.curStep[r];
     }
     {
-        const float2 *pp = reinterpret_cast<const float2 *>(C.agentPos + w * 6);
-        float2 p0 = pp[0], p1 = pp[1], p2 = pp[2];
-        W.a[0].pos = v3(p0.x, p0.y, p1.x); W.a[1].pos = v3(p1.y, p2.x, p2.y);
-        const float2 *vp = reinterpret_cast<const float2 *>(C.agentVel + w * 6);
-        float2 v0 = vp[0], v1 = vp[1], v2 = vp[2];
-        W.a[0].vel = v3(v0.x, v0.y, v1.x); W.a[1].vel = v3(v1.y, v2.x, v2.y);
+        const float *tp = C.attributes + r * 9;
+        A.maxSpeed = tp[0]; A.quickness = tp[1]; A.shooting = tp[2]; A.ftPct = tp[3]; A.reaction = tp[4];
+        A.target = v3(tp[5], tp[6], tp[7]); A.curShot = tp[8];
     }
     {
-        const float4 *qp = reinterpret_cast<const float4 *>(C.orientation + w * 8);
-        float4 q0 = qp[0], q1 = qp[1];
-        W.a[0].q.w = q0.x; W.a[0].q.x = q0.y; W.a[0].q.y = q0.z; W.a[0].q.z = q0.w;
-        W.a[1].q.w = q1.x; W.a[1].q.x = q1.y; W.a[1].q.y = q1.z; W.a[1].q.z = q1.w;
-    }
-    {
-        const int2 *ip = reinterpret_cast<const int2 *>(C.possession + w * 6);
-        int2 i0 = ip[0], i1 = ip[1], i2 = ip[2];
-        W.a[0].hasBall = i0.x; W.a[0].ballId = i0.y; W.a[0].pointsWorth = i1.x;
-        W.a[1].hasBall = i1.y; W.a[1].ballId = i2.x; W.a[1].pointsWorth = i2.y;
-        int4 ib = *reinterpret_cast<const int4 *>(C.inbounding + w * 4);
-        W.a[0].imInb = ib.x; W.a[0].allowedToMove = ib.y; W.a[1].imInb = ib.z; W.a[1].allowedToMove = ib.w;
-        float2 cd = *reinterpret_cast<const float2 *>(C.cooldown + w * 2);
-        W.a[0].cooldown = cd.x; W.a[1].cooldown = cd.y;
-        float4 st = *reinterpret_cast<const float4 *>(C.stats + w * 4);
-        W.a[0].points = st.x; W.a[0].fouls = st.y; W.a[1].points = st.z; W.a[1].fouls = st.w;
-        uint2 cs = *reinterpret_cast<const uint2 *>(C.curStep + w * 2);
-        W.a[0].curStep = cs.x; W.a[1].curStep = cs.y;
-    }
-    {
-        const float2 *tp = reinterpret_cast<const float2 *>(C.attributes + w * 18);
-        float2 t[9];
-#pragma unroll
-        for (int k = 0; k < 9; k++) t[k] = tp[k];
-        AgentS &A0 = W.a[0], &A1 = W.a[1];
-        A0.maxSpeed = t[0].x; A0.quickness = t[0].y; A0.shooting = t[1].x; A0.ftPct = t[1].y; A0.reaction = t[2].x;
-        A0.target = v3(t[2].y, t[3].x, t[3].y); A0.curShot = t[4].x;
-        A1.maxSpeed = t[4].y; A1.quickness = t[5].x; A1.shooting = t[5].y; A1.ftPct = t[6].x; A1.reaction = t[6].y;
-        A1.target = v3(t[7].x, t[7].y, t[8].x); A1.curShot = t[8].y;
-    }
-    {
+        BallS &B = L.B;
         const float *bp = C.ballPos + w * 3;
-        W.b.pos = v3(bp[0], bp[1], bp[2]);
+        B.pos = v3(bp[0], bp[1], bp[2]);
         const float *bv = C.ballVel + w * 3;
-        W.b.vel = v3(bv[0], bv[1], bv[2]);
+        B.vel = v3(bv[0], bv[1], bv[2]);
         const int32_t *ph = C.ballPhysics + w * 7;
-        W.b.inFlight = ph[0]; W.b.ltAgent = ph[1]; W.b.ltTeam = ph[2]; W.b.sbAgent = ph[3];
-        W.b.sbTeam = ph[4]; W.b.spv = ph[5]; W.b.goingIn = ph[6];
+        B.inFlight = ph[0]; B.ltAgent = ph[1]; B.ltTeam = ph[2]; B.sbAgent = ph[3];
+        B.sbTeam = ph[4]; B.spv = ph[5]; B.goingIn = ph[6];
         int2 gr = *reinterpret_cast<const int2 *>(C.grabbed + w * 2);
-        W.b.isGrabbed = gr.x; W.b.holder = gr.y;
+        B.isGrabbed = gr.x; B.holder = gr.y;
     }
     {
         const float2 *gp = reinterpret_cast<const float2 *>(C.gameState + w * 14);
         float2 g0 = gp[0], g1 = gp[1], g2 = gp[2], g3 = gp[3], g4 = gp[4], g5 = gp[5], g6 = gp[6];
-        GameS &g = W.g;
+        GameS &g = L.G;
         g.inbInProgress = __float_as_int(g0.x); g.liveBall = __float_as_int(g0.y);
         g.period = g1.x; g.teamInPoss = g1.y;
         g.team0Hoop = __float_as_int(g2.x); g.team0Score = g2.y;
@@ -272,78 +247,64 @@ BBD void load_world(World &W, const StepParams &p, int64_t w)
         g.scoredBaskets = g5.x; g.oobCount = g5.y;
         g.inboundClock = g6.x; g.isOneOnOne = __float_as_int(g6.y);
     }
-    W.resetNow = C.worldClock[w];
-    W.rng = C.rngCount[w];
+    L.resetNow = C.worldClock[w];
+    L.rng = C.rngCount[w];
     /* mask / reward / done are fully rewritten by tick and actionMask */
 }
 
-BBD void store_world(const World &W, const StepParams &p, int64_t w, bool storeAll)
+BBD void store_lane(const Lane &L, const StepParams &p, int64_t w)
 {
     const Columns &C = p.col;
+    const int me = L.me;
+    const int64_t r = w * 2 + me;
+    const AgentS &A = L.A;
     {
-        int4 *ap = reinterpret_cast<int4 *>(C.action + w * 12);
-        ap[0] = make_int4(W.a[0].move, W.a[0].moveAngle, W.a[0].rotate, W.a[0].grab);
-        ap[1] = make_int4(W.a[0].pass, W.a[0].shoot, W.a[1].move, W.a[1].moveAngle);
-        ap[2] = make_int4(W.a[1].rotate, W.a[1].grab, W.a[1].pass, W.a[1].shoot);
-        int4 *mp = reinterpret_cast<int4 *>(C.actionMask + w * 8);
-        mp[0] = make_int4(W.a[0].canMove, W.a[0].canGrab, W.a[0].canPass, W.a[0].canShoot);
-        mp[1] = make_int4(W.a[1].canMove, W.a[1].canGrab, W.a[1].canPass, W.a[1].canShoot);
+        int2 *ap = reinterpret_cast<int2 *>(C.action + r * 6);
+        ap[0] = make_int2(A.move, A.moveAngle); ap[1] = make_int2(A.rotate, A.grab); ap[2] = make_int2(A.pass, A.shoot);
+        *reinterpret_cast<int4 *>(C.actionMask + r * 4) = make_int4(A.canMove, A.canGrab, A.canPass, A.canShoot);
     }
-    if (W.didReset || storeAll) { /* resetWorld clears Reset (gen.cpp:273) and rewrites Team (gen.cpp:283) */
-        *reinterpret_cast<int2 *>(C.reset + w * 2) = make_int2(W.a[0].reset, W.a[1].reset);
-        int32_t *tp = C.team + w * 10;
-        const bool gen = storeAll; /* generateWorld colours: constants.hpp:18-19; resetWorld: gen.cpp:258 */
-        tp[0] = 0; tp[1] = __float_as_int(0.f); tp[2] = __float_as_int(100.f); tp[3] = __float_as_int(255.f); tp[4] = hoop_id(W, 0);
-        tp[5] = 1; tp[6] = __float_as_int(gen ? 128.f : 255.f); tp[7] = __float_as_int(0.f);
-        tp[8] = __float_as_int(gen ? 128.f : 100.f); tp[9] = hoop_id(W, 1);
+    if (L.didReset) { /* resetWorld clears Reset (gen.cpp:273) and rewrites Team (gen.cpp:258,283) */
+        C.reset[r] = A.reset;
+        int32_t *tp = C.team + r * 5;
+        tp[0] = me;
+        tp[1] = __float_as_int(me ? 255.f : 0.f); tp[2] = __float_as_int(me ? 0.f : 100.f); tp[3] = __float_as_int(me ? 100.f : 255.f);
+        tp[4] = L.idBase + me;
     }
     {
-        float2 *pp = reinterpret_cast<float2 *>(C.agentPos + w * 6);
-        pp[0] = make_float2(W.a[0].pos.x, W.a[0].pos.y);
-        pp[1] = make_float2(W.a[0].pos.z, W.a[1].pos.x);
-        pp[2] = make_float2(W.a[1].pos.y, W.a[1].pos.z);
-        float2 *vp = reinterpret_cast<float2 *>(C.agentVel + w * 6);
-        vp[0] = make_float2(W.a[0].vel.x, W.a[0].vel.y);
-        vp[1] = make_float2(W.a[0].vel.z, W.a[1].vel.x);
-        vp[2] = make_float2(W.a[1].vel.y, W.a[1].vel.z);
-        float4 *qp = reinterpret_cast<float4 *>(C.orientation + w * 8);
-        qp[0] = make_float4(W.a[0].q.w, W.a[0].q.x, W.a[0].q.y, W.a[0].q.z);
-        qp[1] = make_float4(W.a[1].q.w, W.a[1].q.x, W.a[1].q.y, W.a[1].q.z);
+        float *pp = C.agentPos + r * 3;
+        pp[0] = A.pos.x; pp[1] = A.pos.y; pp[2] = A.pos.z;
+        float *vp = C.agentVel + r * 3;
+        vp[0] = A.vel.x; vp[1] = A.vel.y; vp[2] = A.vel.z;
+        *reinterpret_cast<float4 *>(C.orientation + r * 4) = make_float4(A.q.w, A.q.x, A.q.y, A.q.z);
     }
     {
-        int2 *ip = reinterpret_cast<int2 *>(C.possession + w * 6);
-        ip[0] = make_int2(W.a[0].hasBall, W.a[0].ballId);
-        ip[1] = make_int2(W.a[0].pointsWorth, W.a[1].hasBall);
-        ip[2] = make_int2(W.a[1].ballId, W.a[1].pointsWorth);
-        *reinterpret_cast<int4 *>(C.inbounding + w * 4) = make_int4(W.a[0].imInb, W.a[0].allowedToMove, W.a[1].imInb, W.a[1].allowedToMove);
-        *reinterpret_cast<float2 *>(C.cooldown + w * 2) = make_float2(W.a[0].cooldown, W.a[1].cooldown);
-        *reinterpret_cast<float4 *>(C.stats + w * 4) = make_float4(W.a[0].points, W.a[0].fouls, W.a[1].points, W.a[1].fouls);
-        *reinterpret_cast<uint2 *>(C.curStep + w * 2) = make_uint2(W.a[0].curStep, W.a[1].curStep);
-        *reinterpret_cast<float2 *>(C.reward + w * 2) = make_float2(W.a[0].reward, W.a[1].reward);
-        *reinterpret_cast<float2 *>(C.done + w * 2) = make_float2(W.a[0].done, W.a[1].done);
+        int32_t *ip = C.possession + r * 3;
+        ip[0] = A.hasBall; ip[1] = A.ballId; ip[2] = A.pointsWorth;
+        *reinterpret_cast<int2 *>(C.inbounding + r * 2) = make_int2(A.imInb, A.allowedToMove);
+        C.cooldown[r] = A.cooldown;
+        *reinterpret_cast<float2 *>(C.stats + r * 2) = make_float2(A.points, A.fouls);
+        C.curStep[r] = A.curStep;
+        C.reward[r] = A.reward;
+        C.done[r] = A.done;
     }
     {
-        float2 *tp = reinterpret_cast<float2 *>(C.attributes + w * 18);
-        const AgentS &A0 = W.a[0], &A1 = W.a[1];
-        tp[0] = make_float2(A0.maxSpeed, A0.quickness); tp[1] = make_float2(A0.shooting, A0.ftPct);
-        tp[2] = make_float2(A0.reaction, A0.target.x); tp[3] = make_float2(A0.target.y, A0.target.z);
-        tp[4] = make_float2(A0.curShot, A1.maxSpeed); tp[5] = make_float2(A1.quickness, A1.shooting);
-        tp[6] = make_float2(A1.ftPct, A1.reaction); tp[7] = make_float2(A1.target.x, A1.target.y);
-        tp[8] = make_float2(A1.target.z, A1.curShot);
+        float *tp = C.attributes + r * 9;
+        tp[0] = A.maxSpeed; tp[1] = A.quickness; tp[2] = A.shooting; tp[3] = A.ftPct; tp[4] = A.reaction;
+        tp[5] = A.target.x; tp[6] = A.target.y; tp[7] = A.target.z; tp[8] = A.curShot;
     }
-    {
+    if (me == 0) { /* replicated world state: lane 0 writes the ball, lane 1 the singletons */
+        const BallS &B = L.B;
         float *bp = C.ballPos + w * 3;
-        bp[0] = W.b.pos.x; bp[1] = W.b.pos.y; bp[2] = W.b.pos.z;
+        bp[0] = B.pos.x; bp[1] = B.pos.y; bp[2] = B.pos.z;
         float *bv = C.ballVel + w * 3;
-        bv[0] = W.b.vel.x; bv[1] = W.b.vel.y; bv[2] = W.b.vel.z;
+        bv[0] = B.vel.x; bv[1] = B.vel.y; bv[2] = B.vel.z;
         int32_t *ph = C.ballPhysics + w * 7;
-        ph[0] = W.b.inFlight; ph[1] = W.b.ltAgent; ph[2] = W.b.ltTeam; ph[3] = W.b.sbAgent;
-        ph[4] = W.b.sbTeam; ph[5] = W.b.spv; ph[6] = W.b.goingIn;
-        *reinterpret_cast<int2 *>(C.grabbed + w * 2) = make_int2(W.b.isGrabbed, W.b.holder);
-    }
-    {
+        ph[0] = B.inFlight; ph[1] = B.ltAgent; ph[2] = B.ltTeam; ph[3] = B.sbAgent;
+        ph[4] = B.sbTeam; ph[5] = B.spv; ph[6] = B.goingIn;
+        *reinterpret_cast<int2 *>(C.grabbed + w * 2) = make_int2(B.isGrabbed, B.holder);
+    } else {
         float2 *gp = reinterpret_cast<float2 *>(C.gameState + w * 14);
-        const GameS &g = W.g;
+        const GameS &g = L.G;
         gp[0] = make_float2(__int_as_float(g.inbInProgress), __int_as_float(g.liveBall));
         gp[1] = make_float2(g.period, g.teamInPoss);
         gp[2] = make_float2(__int_as_float(g.team0Hoop), g.team0Score);
@@ -351,15 +312,35 @@ BBD void store_world(const World &W, const StepParams &p, int64_t w, bool storeA
         gp[4] = make_float2(g.gameClock, g.shotClock);
         gp[5] = make_float2(g.scoredBaskets, g.oobCount);
         gp[6] = make_float2(g.inboundClock, __int_as_float(g.isOneOnOne));
+        C.worldClock[w] = L.resetNow;
+        C.rngCount[w] = L.rng;
     }
-    C.worldClock[w] = W.resetNow;
-    C.rngCount[w] = W.rng;
+}
+
+/* thread-per-world store of a freshly generated world (init kernel only) */
+BBD void store_world(const World &W, const StepParams &p, int64_t w)
+{
+    Lane L;
+    L.B = W.b; L.G = W.g; L.resetNow = W.resetNow; L.rng = W.rng; L.idBase = W.idBase; L.didReset = false;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+        L.A = W.a[i];
+        L.me = i;
+        store_lane(L, p, w);
+        const Columns &C = p.col;
+        const int64_t r = w * 2 + i;
+        C.reset[r] = W.a[i].reset;
+        int32_t *tp = C.team + r * 5; /* generateWorld colours: constants.hpp:18-19 */
+        tp[0] = i;
+        tp[1] = __float_as_int(i ? 128.f : 0.f); tp[2] = __float_as_int(i ? 0.f : 100.f); tp[3] = __float_as_int(i ? 128.f : 255.f);
+        tp[4] = W.idBase + i;
+    }
 }
 
 /* ------------------------------ kernels ----------------------------------- */
-constexpr int kThreads = 128;
-constexpr int kWarpsPerBlock = kThreads / 32;
-constexpr int kSmemBytes = kWarpsPerBlock * 32 * kFeatStride * 4;
+constexpr int kMaxThreads = 128;
+constexpr int kInitThreads = 128;
+__host__ __device__ constexpr int smem_bytes_for(int threads) { return (threads / 32) * kWorldsPerWarp * kFeatStride * 4; }
 
 /* Coalesced emission of both observation rows of the warp's worlds from the image. */
 BBD void emit_obs_rows(const float *warpImg, float *obs, int64_t warpWorld0, int nValid, int lane)
@@ -381,33 +362,48 @@ BBD void emit_obs_rows(const float *warpImg, float *obs, int64_t warpWorld0, int
     }
 }
 
-template <bool kTagMask>
-__global__ void __launch_bounds__(kThreads) bb_step_kernel(const __grid_constant__ StepParams p)
+/* One Manager::step(): thread t = (world t/2, agent t%2).  Any block size that is a
+ * multiple of 32; dynamic shared memory = smem_bytes_for(blockDim.x). */
+__global__ void __launch_bounds__(kMaxThreads) bb_step_kernel(const __grid_constant__ StepParams p)
 {
     extern __shared__ float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float *warpImg = smem + warp * 32 * kFeatStride;
-    const int64_t w = (int64_t)blockIdx.x * kThreads + threadIdx.x;
-    const int64_t warpWorld0 = w - lane;
-    if (w < p.numWorlds) {
-        World W;
-        load_world(W, p, w);
-        step_world_logic<kTagMask>(W, p.sc);                 /* systems 1-17 */
-        write_obs_image(warpImg + lane * kFeatStride, W, p.sc); /* system 18 */
-#pragma unroll
-        for (int i = 0; i < 2; i++) sys_reward(W, i);        /* system 19 */
-        store_world(W, p, w, false);
+    float *warpImg = smem + warp * kWorldsPerWarp * kFeatStride;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t warpWorld0 = (t - lane) >> 1;
+    if (warpWorld0 >= p.numWorlds) return; /* whole warp past the end */
+    const int64_t w = t >> 1;
+    const bool valid = w < p.numWorlds;
+    const int me = (int)(t & 1);
+    Lane L;
+    /* tail lanes shadow the last world so that every shuffle stays warp-wide; they never store */
+    load_lane(L, p, valid ? w : p.numWorlds - 1, me);
+    __syncwarp(); /* all of the pair's loads precede any of its stores */
+    const bool tag = (p.sc.flags & BB_FLAG_TAG_MASK) != 0;
+    const bool fast = tag && L.G.isOneOnOne == 1 && L.G.inbInProgress == 0;
+    const unsigned fastMask = __ballot_sync(kFullMask, fast);
+    if (fast) {
+        pair_step_fast(L, p.sc, fastMask);                   /* systems 1-17 */
+    } else {
+        AgentS other = xor_agent(~fastMask, L.A);
+        slow_step(L, other, p.sc, tag);
     }
     __syncwarp();
+    const Vec3 opos = xorv(kFullMask, L.A.pos);
+    const int32_t oInb = xori(kFullMask, L.A.imInb);
+    write_obs_image(warpImg + (lane >> 1) * kFeatStride, L, opos, oInb, p.sc); /* system 18 */
+    pair_reward(L, opos);                                    /* system 19 */
+    if (valid) store_lane(L, p, w);
+    __syncwarp();
     int64_t remain = p.numWorlds - warpWorld0;
-    int nValid = remain >= 32 ? 32 : (remain > 0 ? (int)remain : 0);
+    int nValid = remain >= kWorldsPerWarp ? kWorldsPerWarp : (int)remain;
     emit_obs_rows(warpImg, p.col.obs, warpWorld0, nValid, lane);
 }
 
 /* Sim::Sim -> generateWorld (sim.cpp:86-96) for every world + the constant columns. */
-__global__ void __launch_bounds__(kThreads) bb_init_kernel(const __grid_constant__ StepParams p)
+__global__ void __launch_bounds__(kInitThreads) bb_init_kernel(const __grid_constant__ StepParams p)
 {
-    const int64_t w = (int64_t)blockIdx.x * kThreads + threadIdx.x;
+    const int64_t w = (int64_t)blockIdx.x * kInitThreads + threadIdx.x;
     if (w >= p.numWorlds) return;
     const Columns &C = p.col;
     World W;
@@ -415,7 +411,7 @@ __global__ void __launch_bounds__(kThreads) bb_init_kernel(const __grid_constant
     W.rng = 0;
     W.didReset = false;
     generate_world(W, p.sc);
-    store_world(W, p, w, true);
+    store_world(W, p, w);
     /* entity columns {gen = 0, id} and hoops */
     C.agentEntity[w * 4 + 0] = 0; C.agentEntity[w * 4 + 1] = agent_id(W, 0);
     C.agentEntity[w * 4 + 2] = 0; C.agentEntity[w * 4 + 3] = agent_id(W, 1);
@@ -484,6 +480,7 @@ struct bb_engine {
     void *colPtr[26];
     bb::StepParams params;
     cudaStream_t hostStream; /* bb_step_host / setters */
+    int blockThreads;
     int64_t launches;
 };
 
@@ -551,15 +548,26 @@ void host_threefry(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t 
     out[1] = x1;
 }
 
+/* Block size: the step is latency-bound at small world counts, so spread the warps
+ * over all 148 SMs x 4 schedulers (1 warp per block) until every SM holds a few,
+ * then grow the block.  BB_BLOCK_THREADS overrides (tuning). */
+int pick_block_threads(int64_t n_worlds)
+{
+    static const int forced = [] { const char *s = getenv("BB_BLOCK_THREADS"); return s ? atoi(s) : 0; }();
+    if (forced == 32 || forced == 64 || forced == 128) return forced;
+    const int64_t warps = (n_worlds * 2 + 31) / 32;
+    if (warps <= 148 * 8) return 32;
+    if (warps <= 148 * 32) return 64;
+    return 128;
+}
+
 int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream)
 {
     bb::StepParams p = e->params;
     p.actionSrc = actions_dev;
-    const int blocks = (int)((e->N + bb::kThreads - 1) / bb::kThreads);
-    if (e->cfg.flags & BB_FLAG_TAG_MASK)
-        bb::bb_step_kernel<true><<<blocks, bb::kThreads, bb::kSmemBytes, stream>>>(p);
-    else
-        bb::bb_step_kernel<false><<<blocks, bb::kThreads, bb::kSmemBytes, stream>>>(p);
+    const int threads = e->blockThreads;
+    const int blocks = (int)((e->N * 2 + threads - 1) / threads);
+    bb::bb_step_kernel<<<blocks, threads, bb::smem_bytes_for(threads), stream>>>(p);
     e->launches++;
     BB_CUDA_OK(cudaGetLastError());
     return 0;
@@ -639,8 +647,7 @@ bb_engine *bb_create(const bb_config *cfg)
     e->params.actionSrc = nullptr;
     e->params.numWorlds = e->N;
 
-    cudaFuncSetAttribute(bb::bb_step_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::kSmemBytes);
-    cudaFuncSetAttribute(bb::bb_step_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::kSmemBytes);
+    e->blockThreads = pick_block_threads(e->N);
     if (cudaStreamCreateWithFlags(&e->hostStream, cudaStreamNonBlocking) != cudaSuccess) {
         set_error("bb_create: cudaStreamCreate failed");
         cudaFree(e->slab);
@@ -648,8 +655,8 @@ bb_engine *bb_create(const bb_config *cfg)
         return nullptr;
     }
 
-    const int blocks = (int)((e->N + bb::kThreads - 1) / bb::kThreads);
-    bb::bb_init_kernel<<<blocks, bb::kThreads>>>(e->params);
+    const int blocks = (int)((e->N + bb::kInitThreads - 1) / bb::kInitThreads);
+    bb::bb_init_kernel<<<blocks, bb::kInitThreads>>>(e->params);
     e->launches++;
     err = cudaDeviceSynchronize();
     if (err != cudaSuccess) {

@@ -1,0 +1,417 @@
+/*
+ * bb_pair.cuh — one world on a lane PAIR (sub-warp of 2): lane 2k owns agent 0,
+ * lane 2k+1 owns agent 1 of the same world.
+ *
+ * Each lane keeps its own agent in registers; ball, GameState, WorldClock and the
+ * RNG counter are REPLICATED in both lanes and advanced identically, so world
+ * state never needs a broadcast.  What one agent needs of the other (position,
+ * orientation, possession flag, a few predicates) crosses with __shfl_xor(.., 1).
+ * Systems run in the task-graph order of /root/reference/src/game.cpp:1463-1526;
+ * where the reference's agent-0-then-agent-1 order is observable (shootSystem:
+ * RNG draw order, ball hand-off) the pair takes two "turns" in that order.
+ *
+ * This fast path covers what the reference actually runs: 1-v-1 worlds
+ * (GameState.isOneOnOne == 1), no inbound in progress, and the FOR-TAG action
+ * mask (game.cpp:525-528).  Any other world (the 5-v-5 / inbound / grab / pass
+ * code that is dead at the reference's constants but still part of its source)
+ * takes slow_step(): both lanes gather the partner's agent and run the serial
+ * thread-per-world restatement of bb_world.cuh redundantly, then keep their own
+ * agent.  Same results, one code path to verify.
+ */
+#pragma once
+#include "bb_world.cuh"
+
+namespace bb {
+
+constexpr unsigned kFullMask = 0xffffffffu;
+
+struct Lane {
+    AgentS A;
+    BallS B;
+    GameS G;
+    int32_t resetNow;
+    uint32_t rng;
+    int32_t idBase;
+    int32_t me;      /* 0 / 1: agent index == team index == defended hoop */
+    bool didReset;
+};
+
+/* Partner exchange.  `m` names the lanes that execute the same exchange (whole
+ * pairs only): the full warp in straight-line code, the ballot of the branch
+ * predicate inside the fast / slow split. */
+BBD float xorf(unsigned m, float v) { return __shfl_xor_sync(m, v, 1); }
+BBD int32_t xori(unsigned m, int32_t v) { return __shfl_xor_sync(m, v, 1); }
+BBD Vec3 xorv(unsigned m, Vec3 v) { return v3(xorf(m, v.x), xorf(m, v.y), xorf(m, v.z)); }
+BBD Quat xorq(unsigned m, Quat q) { Quat r; r.w = xorf(m, q.w); r.x = xorf(m, q.x); r.y = xorf(m, q.y); r.z = xorf(m, q.z); return r; }
+
+BBD int32_t my_id(const Lane &L) { return L.idBase + 3 + L.me; }
+BBD Vec3 sel(bool c, Vec3 a, Vec3 b) { return v3(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z); }
+BBD Quat selq(bool c, Quat a, Quat b) { Quat r; r.w = c ? a.w : b.w; r.x = c ? a.x : b.x; r.y = c ? a.y : b.y; r.z = c ? a.z : b.z; return r; }
+
+/* RNG::sampleUniform + helper.cpp:8-11, on the replicated counter */
+BBD float pair_uniform(Lane &L, const SimConst &c, float lo, float hi)
+{
+    uint32_t a, b;
+    threefry2x32(c.key0, c.key1, L.rng++, 0u, a, b);
+    float u = (float)((a ^ b) >> 8) * 0x1p-24f;
+    return lo + (hi - lo) * u;
+}
+
+/* ------------------------------------------------------------------ slow path */
+
+BBD AgentS xor_agent(unsigned m, const AgentS &A)
+{
+    AgentS o;
+    o.pos = xorv(m, A.pos); o.vel = xorv(m, A.vel); o.q = xorq(m, A.q);
+    o.hasBall = xori(m, A.hasBall); o.ballId = xori(m, A.ballId); o.pointsWorth = xori(m, A.pointsWorth);
+    o.imInb = xori(m, A.imInb); o.allowedToMove = xori(m, A.allowedToMove);
+    o.cooldown = xorf(m, A.cooldown);
+    o.maxSpeed = xorf(m, A.maxSpeed); o.quickness = xorf(m, A.quickness); o.shooting = xorf(m, A.shooting);
+    o.ftPct = xorf(m, A.ftPct); o.reaction = xorf(m, A.reaction);
+    o.target = xorv(m, A.target); o.curShot = xorf(m, A.curShot);
+    o.points = xorf(m, A.points); o.fouls = xorf(m, A.fouls);
+    o.curStep = (uint32_t)xori(m, (int32_t)A.curStep);
+    o.move = xori(m, A.move); o.moveAngle = xori(m, A.moveAngle); o.rotate = xori(m, A.rotate);
+    o.grab = xori(m, A.grab); o.pass = xori(m, A.pass); o.shoot = xori(m, A.shoot);
+    o.canMove = xori(m, A.canMove); o.canGrab = xori(m, A.canGrab); o.canPass = xori(m, A.canPass); o.canShoot = xori(m, A.canShoot);
+    o.reward = xorf(m, A.reward); o.done = xorf(m, A.done);
+    o.reset = xori(m, A.reset);
+    return o;
+}
+
+/* Systems 1-17 through the serial restatement; W lives in local memory (cold path). */
+__device__ __noinline__ void slow_step_serial(World *W, const SimConst *c, bool tagMask)
+{
+#ifndef BB_NO_SLOW
+    World w = *W;
+    if (tagMask) step_world_logic<true>(w, *c);
+    else step_world_logic<false>(w, *c);
+    *W = w;
+#endif
+}
+
+/* `other` = partner's agent (already exchanged by the caller, warp-convergent). */
+BBD void slow_step(Lane &L, const AgentS &other, const SimConst &c, bool tagMask)
+{
+    World W;
+    if (L.me == 0) { W.a[0] = L.A; W.a[1] = other; }
+    else           { W.a[0] = other; W.a[1] = L.A; }
+    W.b = L.B; W.g = L.G; W.resetNow = L.resetNow; W.rng = L.rng; W.idBase = L.idBase; W.didReset = false;
+    slow_step_serial(&W, &c, tagMask);
+    L.A = (L.me == 0) ? W.a[0] : W.a[1];
+    L.B = W.b; L.G = W.g; L.resetNow = W.resetNow; L.rng = W.rng; L.didReset = W.didReset;
+}
+
+/* ------------------------------------------------------------------ fast path */
+
+/* shootSystem (game.cpp:273-407) for actor k, executed identically by both lanes.
+ * apos/dpos: actor / other agent position; amove, avlen: actor's Action.move, |vel|. */
+BBD void pair_shoot_turn(Lane &L, const SimConst &c, int k, Vec3 apos, Vec3 dpos, int32_t amove, float avlen)
+{
+    const bool acting = (L.me == k);
+    const Vec3 hoop = v3(k ? c.hoopX[0] : c.hoopX[1], c.hoopY, 0.f);
+    const float radius = kHoopZone;
+    Vec3 ideal = hoop - apos;
+    float intended = bb_atan2f(ideal.x, ideal.y);
+    float dist_hoop = len(ideal);
+    float dist_sd = kDistDev * dist_hoop;
+    float dev_dist = pair_uniform(L, c, -dist_sd, dist_sd);
+    float dev_def = 0.f;
+    float nearest = len(apos - dpos);
+    if (nearest < 2.0f) {
+        float def_sd = bb_divf(kDefDev, nearest + 0.1f);
+        dev_def = pair_uniform(L, c, -def_sd, def_sd);
+    }
+    float dev_vel = 0.f;
+    if (amove > 0) {
+        float vel_sd = kVelDev * avlen;
+        dev_vel = pair_uniform(L, c, -vel_sd, vel_sd);
+    }
+    float total = dev_dist + dev_def + dev_vel;
+    float dir = intended + total;
+    Vec3 shot = v3(bb_sinf(dir), bb_cosf(dir), 0.f);
+    bool going_in = false;
+    float along = dot(ideal, shot);
+    if (!(along < 0.f)) {
+        float closest_sq = len2(ideal) - along * along;
+        going_in = closest_sq <= radius * radius;
+    }
+    Quat rot = rotation_between(v3(0.f, 1.f, 0.f), shot, c);
+    if (acting) L.A.q = rot;
+    BallS &B = L.B;
+    const int32_t aid = L.idBase + 3 + k;
+    if (B.holder == aid) {
+        int32_t spv = shot_point_value(apos, hoop);
+        if (going_in) { B.goingIn = 1; L.G.scoredBaskets += 1.f; }
+        else if (acting) L.A.reward -= 1.f;
+        B.isGrabbed = 0; B.holder = kPlaceholder;
+        if (acting) { L.A.hasBall = 0; L.A.ballId = kPlaceholder; L.A.imInb = 0; }
+        B.vel = shot * .1f;
+        B.inFlight = 1;
+        B.sbAgent = aid; B.sbTeam = k; B.spv = spv;
+        B.ltAgent = aid; B.ltTeam = k;
+    }
+}
+
+/* updateCurrentShotPercentage (game.cpp:758-809) for the lane's agent */
+BBD void pair_shot_pct(Lane &L, Vec3 opos, const SimConst &c)
+{
+    AgentS &A = L.A;
+    if (A.hasBall == 0) { A.curShot = 0.f; return; }
+    const Vec3 hoop = v3(L.me ? c.hoopX[0] : c.hoopX[1], c.hoopY, 0.f);
+    float dist_hoop = len(hoop - A.pos);
+    float nearest = len(A.pos - opos);
+    float dist_sd = kDistDev * dist_hoop;
+    float def_sd = bb_divf(kDefDev, nearest) + .0001f;
+    float vel_sd = kVelDev * len(A.vel);
+    float final_sd = bb_sqrtf((bb_divf(dist_sd * dist_sd, 3.f) + bb_divf(def_sd * def_sd, 3.f)) + bb_divf(vel_sd * vel_sd, 3.f));
+    float max_ang = bb_atanf(bb_divf(kHoopZone, dist_hoop));
+    float z = bb_divf(max_ang, final_sd);
+    A.curShot = bb_erff(bb_divf(z, bb_sqrtf(2.f)));
+}
+
+/* resetWorld (gen.cpp:216-316) + setupAgentPositions (helper.cpp:108-160), 1-v-1 branch */
+BBD void pair_reset_world(Lane &L, const SimConst &c)
+{
+    GameS &g = L.G;
+    /* gameClock <= 0 && isOneOnOne == 0 is false in a 1-v-1 world: full GameState reset, ids / mode kept */
+    g.inbInProgress = 0; g.liveBall = 1; g.period = 1.0f; g.teamInPoss = 0.0f;
+    g.team0Score = 0.f; g.team1Score = 0.f; g.gameClock = kTimePerPeriod; g.shotClock = 24.0f;
+    g.scoredBaskets = 0.f; g.oobCount = 0.f; g.inboundClock = 0.f;
+    AgentS &A = L.A;
+    const int i = L.me;
+    A.move = A.moveAngle = A.rotate = A.grab = A.pass = A.shoot = 0;
+    A.canMove = A.canGrab = A.canPass = A.canShoot = 0;
+    A.reset = 0; A.imInb = 0; A.allowedToMove = 1;
+    A.done = 1.f; A.curStep = 0;
+    A.q = i ? c.spawnQ[1] : c.spawnQ[0];
+    A.cooldown = 0.f; A.points = 0.f; A.fouls = 0.f;
+    A.vel = v3(0.f, 0.f, 0.f);
+    /* the three draws of helper.cpp:121,122,132, replicated */
+    Vec3 base = v3(c.startX + (0.f * 2.f), c.startY, 0.f);
+    float xd = pair_uniform(L, c, -kStartDev, kStartDev);
+    float yd = pair_uniform(L, c, -kStartDev, kStartDev);
+    Vec3 p0 = base + v3(xd, yd, 0.f);
+    p0.x = clampf(p0.x, 0.f, c.width);
+    p0.y = clampf(p0.y, 0.f, c.height);
+    float ang = pair_uniform(L, c, 0.f, 2.f * kPi);
+    Vec3 off = v3(kDefenderSpawnRadius * bb_cosf(ang), kDefenderSpawnRadius * bb_sinf(ang), 0.f);
+    Vec3 p1 = p0 + off;
+    p1.x = clampf(p1.x, 0.f, c.width);
+    p1.y = clampf(p1.y, 0.f, c.height);
+    if (i == 0) { A.pos = p0; A.hasBall = 1; A.ballId = L.idBase + 2; A.pointsWorth = 2; }
+    else        { A.pos = p1; A.hasBall = 0; A.ballId = kPlaceholder; A.pointsWorth = 2; }
+    A.maxSpeed = kDefaultSpeed - (float)i * kDefenderSlowdown;
+    A.quickness = 1.f; A.shooting = 0.f; A.ftPct = 0.f;
+    A.reaction = (float)i * kDefenderReaction;
+    A.target = A.pos;
+    A.curShot = 0.f;
+    BallS &B = L.B;
+    B.pos = p0;
+    B.inFlight = 0; B.ltAgent = kPlaceholder; B.ltTeam = kPlaceholder;
+    B.sbAgent = kPlaceholder; B.sbTeam = kPlaceholder; B.spv = 2; B.goingIn = 0;
+    B.vel = v3(0.f, 0.f, 0.f);
+    B.isGrabbed = 1; B.holder = L.idBase + 3;
+    L.didReset = true;
+}
+
+/* agentCollisionSystem (game.cpp:537-648), pair (agent0, agent1); p0/q0, p1/q1 in agent order */
+BBD void pair_collision(Lane &L, Vec3 ca, Quat qa, Vec3 cb, Quat qb)
+{
+    const float hw = kShoulderWidth / 2.0f, hd = kAgentDepth / 2.0f;
+    Vec3 fa = rotate_vec(qa, v3(0.f, 1.f, 0.f));
+    Vec3 ra = v3(fa.y, -fa.x, 0.f);
+    Vec3 hwa = ra * hw, hda = fa * hd;
+    Vec3 va[4] = {ca - hda + hwa, ca - hda - hwa, ca + hda - hwa, ca + hda + hwa};
+    Vec3 fb = rotate_vec(qb, v3(0.f, 1.f, 0.f));
+    Vec3 rb = v3(fb.y, -fb.x, 0.f);
+    Vec3 hwb = rb * hw, hdb = fb * hd;
+    Vec3 vb[4] = {cb - hdb + hwb, cb - hdb - hwb, cb + hdb - hwb, cb + hdb + hwb};
+    Vec3 axes[4] = {normalize(ra), normalize(fa), normalize(rb), normalize(fb)};
+    bool colliding = true;
+    float min_overlap = FLT_MAX;
+    Vec3 mtv = v3(0.f, 0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        if (!colliding) continue;
+        Vec3 ax = axes[j];
+        float amin = dot(va[0], ax), amax = amin, bmin = dot(vb[0], ax), bmax = bmin;
+#pragma unroll
+        for (int k = 1; k < 4; k++) {
+            float pa = dot(va[k], ax), pb = dot(vb[k], ax);
+            if (pa < amin) amin = pa;
+            if (pa > amax) amax = pa;
+            if (pb < bmin) bmin = pb;
+            if (pb > bmax) bmax = pb;
+        }
+        if (!(amax > bmin && bmax > amin)) {
+            colliding = false;
+        } else {
+            float overlap = fminf(amax, bmax) - fmaxf(amin, bmin);
+            if (overlap < min_overlap) { min_overlap = overlap; mtv = ax; }
+        }
+    }
+    if (colliding) {
+        if (L.G.teamInPoss == (float)0) {
+            if (L.me == 0) L.A.reward -= 10.f; else L.A.reward += 10.f;
+            L.resetNow = 1;
+        }
+        Vec3 corr = mtv;
+        if (dot(cb - ca, corr) < 0.f) corr = -corr;
+        Vec3 shift = (corr * min_overlap) * 0.5f;
+        if (L.me == 0) L.A.pos = L.A.pos - shift; else L.A.pos = L.A.pos + shift;
+    }
+}
+
+/* hardCodeDefenseSystem (game.cpp:651-755) for the lane's agent */
+BBD void pair_defense(Lane &L, Vec3 opos, int32_t ohas, const SimConst &c)
+{
+    AgentS &D = L.A;
+    const int i = L.me;
+    if (L.G.teamInPoss == (float)i) { D.move = 0; return; }
+    D.grab = 1;
+    /* first agent (index order) holding a ball */
+    const int32_t has0 = i ? ohas : D.hasBall, has1 = i ? D.hasBall : ohas;
+    const Vec3 pos0 = sel(i != 0, opos, D.pos), pos1 = sel(i != 0, D.pos, opos);
+    if (has0 != 1 && has1 != 1) { D.move = 0; return; }
+    Vec3 op = (has0 == 1) ? pos0 : pos1;
+    Vec3 hdv = v3(i ? c.hoopX[1] : c.hoopX[0], c.hoopY, 0.f) - op;
+    Vec3 guard = op;
+    if (len2(hdv) > 1e-6f) guard = op + normalize(hdv) * kGuardDist;
+    float f = D.reaction * kDt;
+    D.target = D.target + (guard - D.target) * f;
+    Vec3 mv = D.target - D.pos;
+    if (len2(mv) < 0.01f) { D.move = 0; return; }
+    Vec3 dir = normalize(mv);
+    const float k = c.invSqrt2;
+    const float dxs[8] = {0.f, 1.f * k, 1.f, 1.f * k, 0.f, -1.f * k, -1.f, -1.f * k};
+    const float dys[8] = {-1.f, -1.f * k, 0.f, 1.f * k, 1.f, 1.f * k, 0.f, -1.f * k};
+    float best = -2.f;
+    int32_t best_k = 0;
+#pragma unroll
+    for (int m = 0; m < 8; m++) {
+        float dd = dir.x * dxs[m] + dir.y * dys[m] + dir.z * 0.f;
+        if (dd > best) { best = dd; best_k = m; }
+    }
+    D.move = 1;
+    D.moveAngle = best_k;
+    Vec3 ov = rotate_vec(D.q, v3(0.f, 1.f, 0.f));
+    float ang = bb_acosf(clampf(dot(ov, dir), -1.f, 1.f));
+    if (ang > kPi / 8.f) {
+        float cr = ov.x * mv.y - ov.y * mv.x;
+        if (cr < 0.f) D.rotate = -1;
+        else if (cr > 0.f) D.rotate = 1;
+        else D.rotate = 0;
+    } else {
+        D.rotate = 0;
+    }
+}
+
+/* rewardSystem (game.cpp:811-870) for the lane's agent */
+BBD void pair_reward(Lane &L, Vec3 opos)
+{
+    AgentS &A = L.A;
+    float dist_other = len(opos - A.pos);
+    if ((float)L.me == L.G.teamInPoss) {
+        if (L.G.gameClock > 5.f) {
+            const int32_t id = my_id(L);
+            if (L.B.sbAgent == id && L.B.goingIn == 1) A.reward += (float)L.B.spv;
+            else if (L.B.sbAgent == id && L.B.goingIn == 0 && L.B.inFlight == 1) A.reward -= 1.f;
+            A.reward += A.curShot;
+        }
+    } else {
+        A.reward -= 1.f;
+        A.reward += bb_expf(-0.4f * dist_other);
+    }
+}
+
+/* Systems 1..17 (game.cpp:1467-1516) for a 1-v-1, tag-mask, no-inbound world. */
+BBD void pair_step_fast(Lane &L, const SimConst &c, const unsigned m)
+{
+    AgentS &A = L.A;
+    BallS &B = L.B;
+    GameS &g = L.G;
+    const int me = L.me;
+    sys_tick(A);                       /* 1 */
+    sys_action_mask<true>(A, g);       /* 2 */
+    sys_move_agent(A, c);              /* 3 */
+    /* 4 grab, 5 pass: can_grab == can_pass == 0 under the tag mask -> both return at once */
+    Vec3 opos = xorv(m, A.pos);
+    {                                  /* 6 shoot: agent 0's turn, then agent 1's */
+        const int32_t wants = (A.canShoot != 0 && A.shoot != 0) ? 1 : 0;
+        const float vlen = len(A.vel);
+        const int32_t ovmove = xori(m, A.move), owants = xori(m, wants);
+        const float ovlen = xorf(m, vlen);
+#pragma unroll 1
+        for (int k = 0; k < 2; k++) {
+            const bool mine = (me == k);
+            if (mine ? wants : owants)
+                pair_shoot_turn(L, c, k, mine ? A.pos : opos, mine ? opos : A.pos, mine ? A.move : ovmove,
+                                mine ? vlen : ovlen);
+        }
+    }
+    {                                  /* 7 moveBall (game.cpp:82-125) */
+        const int32_t holds = (A.hasBall == 1 && B.isGrabbed == 1 && B.holder == my_id(L)) ? 1 : 0;
+        const int32_t oholds = xori(m, holds);
+        if (holds) B.pos = A.pos; else if (oholds) B.pos = opos;
+        if (!(len(B.vel) == 0.f || B.isGrabbed == 1)) {
+            float nx = clampf(B.pos.x + B.vel.x, 0.f, c.width);
+            float ny = clampf(B.pos.y + B.vel.y, 0.f, c.height);
+            float nz = B.pos.z + B.vel.z;
+            B.pos = v3(nx, ny, nz);
+        }
+    }
+    pair_shot_pct(L, opos, c);         /* 8 */
+#pragma unroll
+    for (int h = 0; h < 2; h++) {      /* 9 score (game.cpp:873-953), 1-v-1 branch */
+        float dx = B.pos.x - c.hoopX[h], dy = B.pos.y - c.hoopY;
+        float dist = bb_sqrtf(dx * dx + dy * dy);
+        if (dist <= kHoopZone && (float)B.inFlight == 1.f) {
+            int32_t points = B.spv;
+            if (my_id(L) == B.sbAgent) A.points += (float)((me == h) ? -B.spv : B.spv);
+            if (L.idBase + h == g.team0Hoop) g.team1Score += (float)points;
+            else g.team0Score += (float)points;
+            g.scoredBaskets += 1.f;
+            B.inFlight = 0;
+            B.vel = v3(0.f, 0.f, 0.f);
+            B.sbAgent = kPlaceholder; B.sbTeam = kPlaceholder; B.spv = 2; B.goingIn = 0;
+            L.resetNow = 1;
+        }
+    }
+    const int off = ((float)1 == g.teamInPoss) ? 1 : 0; /* game.cpp:1012-1018, 1072-1078 */
+    {                                  /* 10 outOfBounds (game.cpp:1055-1113), 1-v-1 branch */
+        bool out = B.pos.x < kCourtMinX || B.pos.x > kCourtMaxX || B.pos.y < kCourtMinY || B.pos.y > kCourtMaxY;
+        if (out) { /* inboundingInProgress == 0 on this path */
+            if (me == off) A.reward -= 100.f;
+            L.resetNow = 1;
+        }
+    }
+    {                                  /* 11 updateLastTouch (game.cpp:1034-1051): the later agent wins */
+        const int32_t touch = (len(B.pos - A.pos) <= kAgentSize) ? 1 : 0;
+        const int32_t otouch = xori(m, touch);
+        const int32_t t0 = me ? otouch : touch, t1 = me ? touch : otouch;
+        if (t1) { B.ltAgent = L.idBase + 4; B.ltTeam = 1; }
+        else if (t0) { B.ltAgent = L.idBase + 3; B.ltTeam = 0; }
+    }
+    {                                  /* 12 clock (game.cpp:992-1030) */
+        bool live = (float)g.liveBall > 0.5f;
+        if (live && g.gameClock > 0.f) { g.gameClock -= kDt; g.shotClock -= kDt; }
+        if (g.gameClock <= 0.f && live) {
+            if (me == off) A.reward += 10.f;
+            L.resetNow = 1;
+        }
+        if (g.shotClock < 0.f) g.shotClock = 0.f;
+    }
+    /* 13 inboundViolation: needs inboundingInProgress > 0.5 -> nothing on this path */
+    if (L.resetNow != 0) { pair_reset_world(L, c); L.resetNow = 0; } /* 14 */
+    A.pointsWorth = shot_point_value(A.pos, v3(me ? c.hoopX[0] : c.hoopX[1], c.hoopY, 0.f)); /* 15 */
+    opos = xorv(m, A.pos);
+    {                                  /* 16 collision */
+        Quat oq = xorq(m, A.q);
+        pair_collision(L, sel(me == 0, A.pos, opos), selq(me == 0, A.q, oq), sel(me == 0, opos, A.pos), selq(me == 0, oq, A.q));
+    }
+    opos = xorv(m, A.pos);
+    pair_defense(L, opos, xori(m, A.hasBall), c); /* 17 */
+}
+
+} // namespace bb
