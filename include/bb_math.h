@@ -33,8 +33,12 @@
 
 #if defined(__CUDACC__)
 #define BB_HD __host__ __device__ __forceinline__
+/* the big polynomial kernels are shared subroutines on the device: the step kernel
+ * is instruction-fetch bound, so one copy per kernel beats one copy per call site */
+#define BB_HD_SUB __host__ __device__ __noinline__
 #else
 #define BB_HD static inline
+#define BB_HD_SUB static inline
 #endif
 
 /* ---------------------------------------------------------------- primitives */
@@ -153,31 +157,31 @@ BB_HD double bb_reduce_pio2(double x, int *quadrant)
     return r;
 }
 
-BB_HD float bb_sinf(float x)
+/* sin(x + qoff * pi/2) for qoff = 0 / 1: bb_sinf and bb_cosf share one reduction and
+ * one pair of polynomials (cos x takes the sine rule with the quadrant advanced by 1). */
+BB_HD_SUB double bb_sincos_quadrant(double x, int qoff)
 {
     int q;
-    if (x == 0.0f) return x; /* keep sinf(-0) == -0 like libm */
-    double r = bb_reduce_pio2((double)x, &q);
+    double r = bb_reduce_pio2(x, &q);
+    q += qoff;
     double s = bb_ksin(r), c = bb_kcos(r);
     double v = (q & 1) ? c : s;
     if (q & 2) v = -v;
-    return (float)v;
+    return v;
 }
 
-BB_HD float bb_cosf(float x)
+BB_HD float bb_sinf(float x)
 {
-    int q;
-    double r = bb_reduce_pio2((double)x, &q);
-    double s = bb_ksin(r), c = bb_kcos(r);
-    double v = (q & 1) ? s : c;
-    if ((q + 1) & 2) v = -v;
-    return (float)v;
+    if (x == 0.0f) return x; /* keep sinf(-0) == -0 like libm */
+    return (float)bb_sincos_quadrant((double)x, 0);
 }
+
+BB_HD float bb_cosf(float x) { return (float)bb_sincos_quadrant((double)x, 1); }
 
 /* ----------------------------------------------------------------------- atan */
 
 /* atan for x >= 0 (x may be +inf); fdlibm s_atan.c reduction and coefficients. */
-BB_HD double bb_atan_pos(double x)
+BB_HD_SUB double bb_atan_pos(double x)
 {
     const double aT0 = 3.33333333333329318027e-01, aT1 = -1.99999999998764832476e-01,
                  aT2 = 1.42857142725034663711e-01, aT3 = -1.11111104054623557880e-01,
@@ -266,7 +270,7 @@ BB_HD float bb_acosf(float x)
 
 /* ------------------------------------------------------------------------ exp */
 
-BB_HD double bb_exp(double x)
+BB_HD_SUB double bb_exp(double x)
 {
     const double LOG2E = 1.44269504088896338700e+00;
     const double LN2_HI = 6.93147180369123816490e-01, LN2_LO = 1.90821492927058770002e-10;

@@ -6,7 +6,7 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbball.so")
+LIB_PATH = os.environ.get("BB_LIB_PATH") or os.path.join(_HERE, "libbball.so")  # BB_LIB_PATH: tuning builds
 
 # every symbol include/bb_engine.h declares
 SYMBOLS = [

@@ -10,6 +10,7 @@ LIB_PATH = os.path.join(_HERE, "libbball.so")
 SOURCES = [os.path.join(_HERE, "csrc", "bb_engine.cu")]
 DEPS = SOURCES + [
     os.path.join(_HERE, "csrc", "bb_world.cuh"),
+    os.path.join(_HERE, "csrc", "bb_pair.cuh"),
     os.path.join(_HERE, "..", "include", "bb_math.h"),
     os.path.join(_HERE, "..", "include", "bb_engine.h"),
 ]
@@ -37,16 +38,16 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in DEPS)
 
 
-def build_engine(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+def build_engine(force: bool = False, verbose: bool = False, extra=(), out: str = LIB_PATH) -> str:
+    if not force and out == LIB_PATH and not needs_build():
         return LIB_PATH
-    cmd = [find_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + SOURCES + ["-o", LIB_PATH]
+    cmd = [find_nvcc()] + NVCC_FLAGS + list(extra) + (["-Xptxas", "-v"] if verbose else []) + SOURCES + ["-o", out]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
     if verbose:
         print(res.stderr)
-    return LIB_PATH
+    return out
 
 
 if __name__ == "__main__":

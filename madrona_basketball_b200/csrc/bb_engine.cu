@@ -76,17 +76,17 @@ struct StepParams {
  * puts k, k+4, k+8.. in consecutive words so those gathers are conflict-free.
  * Agent 1's row is a block permutation of agent 0's (self <-> opponent blocks,
  * scores and hoops swapped), so one image serves both rows. */
-constexpr int kFeat = 108;        /* feature slots: 0..103 row-0 image, 104..106 row-1 vec_to, 107 zero */
+/* kFeat = 108 feature slots: 0..103 row-0 image, 104..106 row-1 vec_to, 107 zero */
 constexpr int kFeatStride = 109;  /* odd */
 constexpr int kZeroFeat = 107;
 constexpr int kWorldsPerWarp = 16;
 
-BBD int feat_pos(int k) { return (k & 3) * 27 + (k >> 2); }
+__host__ __device__ inline int feat_pos(int k) { return (k & 3) * 27 + (k >> 2); }
 
 /* obs column -> feature, row of agent 0 */
-BBD int row0_src(int cidx) { return (cidx >= 103 || (cidx >= 26 && cidx <= 29)) ? kZeroFeat : cidx; }
+__host__ __device__ inline int row0_src(int cidx) { return (cidx >= 103 || (cidx >= 26 && cidx <= 29)) ? kZeroFeat : cidx; }
 /* obs column -> feature, row of agent 1 */
-BBD int row1_src(int cidx)
+__host__ __device__ inline int row1_src(int cidx)
 {
     if (cidx >= 103) return kZeroFeat;
     if (cidx == 5) return 6;
@@ -164,9 +164,9 @@ BBD void write_obs_image(float *img, const Lane &L, Vec3 opos, int32_t oInb, con
         Vec3 v01 = A.pos - opos;
         Vec3 v10 = opos - A.pos;
         float l2 = len2(v01);
-        float dist = bb_sqrtf(l2);
+        float dist = f_sqrt(l2);
         Vec3 n01 = v3(0.f, 0.f, 0.f), n10 = v3(0.f, 0.f, 0.f);
-        if (l2 > 1e-6f) { float inv = bb_divf(1.f, dist); n01 = v01 * inv; n10 = v10 * inv; }
+        if (l2 > 1e-6f) { float inv = f_div(1.f, dist); n01 = v01 * inv; n10 = v10 * inv; }
         put3(img, 64, n01); put(img, 67, dist);
         put3(img, 104, n10);
         /* one-hots (game.cpp:1441-1452): ball holder; inbounder = last agent with imInbounding */
@@ -342,14 +342,18 @@ constexpr int kMaxThreads = 128;
 constexpr int kInitThreads = 128;
 __host__ __device__ constexpr int smem_bytes_for(int threads) { return (threads / 32) * kWorldsPerWarp * kFeatStride * 4; }
 
+/* image word of every observation column, rows of agent 0 / agent 1 (filled by bb_create) */
+__constant__ uint8_t kEmitWord[2][128];
+
 /* Coalesced emission of both observation rows of the warp's worlds from the image. */
 BBD void emit_obs_rows(const float *warpImg, float *obs, int64_t warpWorld0, int nValid, int lane)
 {
     int off[2][4];
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-        off[0][i] = feat_pos(row0_src(lane * 4 + i));
-        off[1][i] = feat_pos(row1_src(lane * 4 + i));
+    {
+        const uchar4 o0 = reinterpret_cast<const uchar4 *>(kEmitWord[0])[lane];
+        const uchar4 o1 = reinterpret_cast<const uchar4 *>(kEmitWord[1])[lane];
+        off[0][0] = o0.x; off[0][1] = o0.y; off[0][2] = o0.z; off[0][3] = o0.w;
+        off[1][0] = o1.x; off[1][1] = o1.y; off[1][2] = o1.z; off[1][3] = o1.w;
     }
     float4 *dst = reinterpret_cast<float4 *>(obs + warpWorld0 * 256) + lane;
 #pragma unroll 4
@@ -362,16 +366,21 @@ BBD void emit_obs_rows(const float *warpImg, float *obs, int64_t warpWorld0, int
     }
 }
 
-/* One Manager::step(): thread t = (world t/2, agent t%2).  Any block size that is a
- * multiple of 32; dynamic shared memory = smem_bytes_for(blockDim.x). */
-__global__ void __launch_bounds__(kMaxThreads) bb_step_kernel(const __grid_constant__ StepParams p)
+#ifndef BB_MIN_BLOCKS_128
+#define BB_MIN_BLOCKS_128 4 /* resident 128-thread blocks per SM the register budget is cut for */
+#endif
+/* One Manager::step(): thread t = (world t/2, agent t%2).  blockDim.x is any multiple of
+ * 32 up to kMaxT; dynamic shared memory = smem_bytes_for(blockDim.x).  kSync: see phase_sync. */
+template <int kMaxT, bool kSync>
+__global__ void __launch_bounds__(kMaxT, BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_kernel(const __grid_constant__ StepParams p)
 {
     extern __shared__ float smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float *warpImg = smem + warp * kWorldsPerWarp * kFeatStride;
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t warpWorld0 = (t - lane) >> 1;
-    if (warpWorld0 >= p.numWorlds) return; /* whole warp past the end */
+    const bool warpLive = warpWorld0 < p.numWorlds;
+    if (!kSync && !warpLive) return; /* whole warp past the end (with barriers it shadows the last world) */
     const int64_t w = t >> 1;
     const bool valid = w < p.numWorlds;
     const int me = (int)(t & 1);
@@ -380,21 +389,17 @@ __global__ void __launch_bounds__(kMaxThreads) bb_step_kernel(const __grid_const
     load_lane(L, p, valid ? w : p.numWorlds - 1, me);
     __syncwarp(); /* all of the pair's loads precede any of its stores */
     const bool tag = (p.sc.flags & BB_FLAG_TAG_MASK) != 0;
-    const bool fast = tag && L.G.isOneOnOne == 1 && L.G.inbInProgress == 0;
-    const unsigned fastMask = __ballot_sync(kFullMask, fast);
-    if (fast) {
-        pair_step_fast(L, p.sc, fastMask);                   /* systems 1-17 */
-    } else {
-        AgentS other = xor_agent(~fastMask, L.A);
-        slow_step(L, other, p.sc, tag);
-    }
+    const bool fast = __all_sync(kFullMask, tag && L.G.isOneOnOne == 1 && L.G.inbInProgress == 0);
+    if (fast) pair_step_fast<kSync>(L, p.sc);                /* systems 1-17 */
+    else { Lane T = L; slow_step(&T, &p.sc, tag, kSync); L = T; } /* only the copy's address escapes */
     __syncwarp();
-    const Vec3 opos = xorv(kFullMask, L.A.pos);
-    const int32_t oInb = xori(kFullMask, L.A.imInb);
+    const Vec3 opos = xorv(L.A.pos);
+    const int32_t oInb = xori(L.A.imInb);
     write_obs_image(warpImg + (lane >> 1) * kFeatStride, L, opos, oInb, p.sc); /* system 18 */
     pair_reward(L, opos);                                    /* system 19 */
     if (valid) store_lane(L, p, w);
     __syncwarp();
+    if (!warpLive) return;
     int64_t remain = p.numWorlds - warpWorld0;
     int nValid = remain >= kWorldsPerWarp ? kWorldsPerWarp : (int)remain;
     emit_obs_rows(warpImg, p.col.obs, warpWorld0, nValid, lane);
@@ -480,7 +485,7 @@ struct bb_engine {
     void *colPtr[26];
     bb::StepParams params;
     cudaStream_t hostStream; /* bb_step_host / setters */
-    int blockThreads;
+    int blockThreads, phaseSync;
     int64_t launches;
 };
 
@@ -548,17 +553,22 @@ void host_threefry(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t 
     out[1] = x1;
 }
 
-/* Block size: the step is latency-bound at small world counts, so spread the warps
- * over all 148 SMs x 4 schedulers (1 warp per block) until every SM holds a few,
- * then grow the block.  BB_BLOCK_THREADS overrides (tuning). */
-int pick_block_threads(int64_t n_worlds)
+/* Launch shape.  Small world counts are latency-bound: spread the warps over all 148 SMs x 4
+ * schedulers (1 warp per block) until every SM holds a few.  Large counts are instruction-fetch /
+ * HBM bound: big blocks whose warps re-align at phase barriers.  BB_BLOCK_THREADS (32..512) and
+ * BB_PHASE_SYNC (0/1) override for tuning. */
+void pick_launch_shape(int64_t n_worlds, int *threads, int *sync)
 {
-    static const int forced = [] { const char *s = getenv("BB_BLOCK_THREADS"); return s ? atoi(s) : 0; }();
-    if (forced == 32 || forced == 64 || forced == 128) return forced;
     const int64_t warps = (n_worlds * 2 + 31) / 32;
-    if (warps <= 148 * 8) return 32;
-    if (warps <= 148 * 32) return 64;
-    return 128;
+    if (warps <= 148 * 8) { *threads = 32; *sync = 0; }
+    else if (warps <= 148 * 32) { *threads = 64; *sync = 0; }
+    else { *threads = 128; *sync = 0; }
+    if (const char *s = getenv("BB_BLOCK_THREADS")) {
+        int v = atoi(s);
+        if (v >= 32 && v <= 512 && v % 32 == 0) *threads = v;
+    }
+    if (const char *s = getenv("BB_PHASE_SYNC")) *sync = atoi(s) != 0;
+    if (*threads == 32) *sync = 0;
 }
 
 int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream)
@@ -567,7 +577,14 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream)
     p.actionSrc = actions_dev;
     const int threads = e->blockThreads;
     const int blocks = (int)((e->N * 2 + threads - 1) / threads);
-    bb::bb_step_kernel<<<blocks, threads, bb::smem_bytes_for(threads), stream>>>(p);
+    const int smem = bb::smem_bytes_for(threads);
+    if (threads <= 128) {
+        if (e->phaseSync) bb::bb_step_kernel<128, true><<<blocks, threads, smem, stream>>>(p);
+        else bb::bb_step_kernel<128, false><<<blocks, threads, smem, stream>>>(p);
+    } else {
+        if (e->phaseSync) bb::bb_step_kernel<512, true><<<blocks, threads, smem, stream>>>(p);
+        else bb::bb_step_kernel<512, false><<<blocks, threads, smem, stream>>>(p);
+    }
     e->launches++;
     BB_CUDA_OK(cudaGetLastError());
     return 0;
@@ -647,7 +664,19 @@ bb_engine *bb_create(const bb_config *cfg)
     e->params.actionSrc = nullptr;
     e->params.numWorlds = e->N;
 
-    e->blockThreads = pick_block_threads(e->N);
+    pick_launch_shape(e->N, &e->blockThreads, &e->phaseSync);
+    if (bb::smem_bytes_for(512) > 48 * 1024) {
+        cudaFuncSetAttribute(bb::bb_step_kernel<512, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::smem_bytes_for(512));
+        cudaFuncSetAttribute(bb::bb_step_kernel<512, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::smem_bytes_for(512));
+    }
+    {
+        uint8_t words[2][128];
+        for (int cidx = 0; cidx < 128; cidx++) {
+            words[0][cidx] = (uint8_t)bb::feat_pos(bb::row0_src(cidx));
+            words[1][cidx] = (uint8_t)bb::feat_pos(bb::row1_src(cidx));
+        }
+        cudaMemcpyToSymbol(bb::kEmitWord, words, sizeof words);
+    }
     if (cudaStreamCreateWithFlags(&e->hostStream, cudaStreamNonBlocking) != cudaSuccess) {
         set_error("bb_create: cudaStreamCreate failed");
         cudaFree(e->slab);

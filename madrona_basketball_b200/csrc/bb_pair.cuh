@@ -14,9 +14,9 @@
  * (GameState.isOneOnOne == 1), no inbound in progress, and the FOR-TAG action
  * mask (game.cpp:525-528).  Any other world (the 5-v-5 / inbound / grab / pass
  * code that is dead at the reference's constants but still part of its source)
- * takes slow_step(): both lanes gather the partner's agent and run the serial
- * thread-per-world restatement of bb_world.cuh redundantly, then keep their own
- * agent.  Same results, one code path to verify.
+ * sends its whole WARP through slow_step(): both lanes gather the partner's agent
+ * and run the serial thread-per-world restatement of bb_world.cuh redundantly,
+ * then keep their own agent.  Same results, one code path to verify.
  */
 #pragma once
 #include "bb_world.cuh"
@@ -36,13 +36,12 @@ struct Lane {
     bool didReset;
 };
 
-/* Partner exchange.  `m` names the lanes that execute the same exchange (whole
- * pairs only): the full warp in straight-line code, the ballot of the branch
- * predicate inside the fast / slow split. */
-BBD float xorf(unsigned m, float v) { return __shfl_xor_sync(m, v, 1); }
-BBD int32_t xori(unsigned m, int32_t v) { return __shfl_xor_sync(m, v, 1); }
-BBD Vec3 xorv(unsigned m, Vec3 v) { return v3(xorf(m, v.x), xorf(m, v.y), xorf(m, v.z)); }
-BBD Quat xorq(unsigned m, Quat q) { Quat r; r.w = xorf(m, q.w); r.x = xorf(m, q.x); r.y = xorf(m, q.y); r.z = xorf(m, q.z); return r; }
+/* Partner exchange.  Always warp-wide: the fast / slow choice is made per WARP
+ * (the slow path is valid for every world), so all 32 lanes reach every exchange. */
+BBD float xorf(float v) { return __shfl_xor_sync(kFullMask, v, 1); }
+BBD int32_t xori(int32_t v) { return __shfl_xor_sync(kFullMask, v, 1); }
+BBD Vec3 xorv(Vec3 v) { return v3(xorf(v.x), xorf(v.y), xorf(v.z)); }
+BBD Quat xorq(Quat q) { Quat r; r.w = xorf(q.w); r.x = xorf(q.x); r.y = xorf(q.y); r.z = xorf(q.z); return r; }
 
 BBD int32_t my_id(const Lane &L) { return L.idBase + 3 + L.me; }
 BBD Vec3 sel(bool c, Vec3 a, Vec3 b) { return v3(c ? a.x : b.x, c ? a.y : b.y, c ? a.z : b.z); }
@@ -51,55 +50,55 @@ BBD Quat selq(bool c, Quat a, Quat b) { Quat r; r.w = c ? a.w : b.w; r.x = c ? a
 /* RNG::sampleUniform + helper.cpp:8-11, on the replicated counter */
 BBD float pair_uniform(Lane &L, const SimConst &c, float lo, float hi)
 {
-    uint32_t a, b;
-    threefry2x32(c.key0, c.key1, L.rng++, 0u, a, b);
-    float u = (float)((a ^ b) >> 8) * 0x1p-24f;
+    float u = rng_uniform01(c.key0, c.key1, L.rng++);
     return lo + (hi - lo) * u;
 }
 
 /* ------------------------------------------------------------------ slow path */
 
-BBD AgentS xor_agent(unsigned m, const AgentS &A)
+BBD AgentS xor_agent(const AgentS &A)
 {
     AgentS o;
-    o.pos = xorv(m, A.pos); o.vel = xorv(m, A.vel); o.q = xorq(m, A.q);
-    o.hasBall = xori(m, A.hasBall); o.ballId = xori(m, A.ballId); o.pointsWorth = xori(m, A.pointsWorth);
-    o.imInb = xori(m, A.imInb); o.allowedToMove = xori(m, A.allowedToMove);
-    o.cooldown = xorf(m, A.cooldown);
-    o.maxSpeed = xorf(m, A.maxSpeed); o.quickness = xorf(m, A.quickness); o.shooting = xorf(m, A.shooting);
-    o.ftPct = xorf(m, A.ftPct); o.reaction = xorf(m, A.reaction);
-    o.target = xorv(m, A.target); o.curShot = xorf(m, A.curShot);
-    o.points = xorf(m, A.points); o.fouls = xorf(m, A.fouls);
-    o.curStep = (uint32_t)xori(m, (int32_t)A.curStep);
-    o.move = xori(m, A.move); o.moveAngle = xori(m, A.moveAngle); o.rotate = xori(m, A.rotate);
-    o.grab = xori(m, A.grab); o.pass = xori(m, A.pass); o.shoot = xori(m, A.shoot);
-    o.canMove = xori(m, A.canMove); o.canGrab = xori(m, A.canGrab); o.canPass = xori(m, A.canPass); o.canShoot = xori(m, A.canShoot);
-    o.reward = xorf(m, A.reward); o.done = xorf(m, A.done);
-    o.reset = xori(m, A.reset);
+    o.pos = xorv(A.pos); o.vel = xorv(A.vel); o.q = xorq(A.q);
+    o.hasBall = xori(A.hasBall); o.ballId = xori(A.ballId); o.pointsWorth = xori(A.pointsWorth);
+    o.imInb = xori(A.imInb); o.allowedToMove = xori(A.allowedToMove);
+    o.cooldown = xorf(A.cooldown);
+    o.maxSpeed = xorf(A.maxSpeed); o.quickness = xorf(A.quickness); o.shooting = xorf(A.shooting);
+    o.ftPct = xorf(A.ftPct); o.reaction = xorf(A.reaction);
+    o.target = xorv(A.target); o.curShot = xorf(A.curShot);
+    o.points = xorf(A.points); o.fouls = xorf(A.fouls);
+    o.curStep = (uint32_t)xori((int32_t)A.curStep);
+    o.move = xori(A.move); o.moveAngle = xori(A.moveAngle); o.rotate = xori(A.rotate);
+    o.grab = xori(A.grab); o.pass = xori(A.pass); o.shoot = xori(A.shoot);
+    o.canMove = xori(A.canMove); o.canGrab = xori(A.canGrab); o.canPass = xori(A.canPass); o.canShoot = xori(A.canShoot);
+    o.reward = xorf(A.reward); o.done = xorf(A.done);
+    o.reset = xori(A.reset);
     return o;
 }
 
-/* Systems 1-17 through the serial restatement; W lives in local memory (cold path). */
-__device__ __noinline__ void slow_step_serial(World *W, const SimConst *c, bool tagMask)
+/* Systems 1-17 through the serial restatement, for a whole warp (cold path, kept out
+ * of line so that it costs the fast path no registers and no instruction-cache lines):
+ * every lane gathers its partner's agent, runs the thread-per-world code on the
+ * complete world, and keeps its own agent.  Both lanes of a pair compute the same
+ * world, so the replicated ball / GameState / RNG stay identical. */
+__device__ __noinline__ void slow_step(Lane *Lp, const SimConst *c, bool tagMask, bool sync)
 {
+    if (sync) { /* the barriers the fast path of the other warps passes (kPhases) */
+        __syncthreads(); __syncthreads(); __syncthreads(); __syncthreads(); __syncthreads(); __syncthreads();
+    }
 #ifndef BB_NO_SLOW
-    World w = *W;
-    if (tagMask) step_world_logic<true>(w, *c);
-    else step_world_logic<false>(w, *c);
-    *W = w;
-#endif
-}
-
-/* `other` = partner's agent (already exchanged by the caller, warp-convergent). */
-BBD void slow_step(Lane &L, const AgentS &other, const SimConst &c, bool tagMask)
-{
+    Lane L = *Lp;
+    AgentS other = xor_agent(L.A);
     World W;
     if (L.me == 0) { W.a[0] = L.A; W.a[1] = other; }
     else           { W.a[0] = other; W.a[1] = L.A; }
     W.b = L.B; W.g = L.G; W.resetNow = L.resetNow; W.rng = L.rng; W.idBase = L.idBase; W.didReset = false;
-    slow_step_serial(&W, &c, tagMask);
+    if (tagMask) step_world_logic<true>(W, *c);
+    else step_world_logic<false>(W, *c);
     L.A = (L.me == 0) ? W.a[0] : W.a[1];
     L.B = W.b; L.G = W.g; L.resetNow = W.resetNow; L.rng = W.rng; L.didReset = W.didReset;
+    *Lp = L;
+#endif
 }
 
 /* ------------------------------------------------------------------ fast path */
@@ -119,7 +118,7 @@ BBD void pair_shoot_turn(Lane &L, const SimConst &c, int k, Vec3 apos, Vec3 dpos
     float dev_def = 0.f;
     float nearest = len(apos - dpos);
     if (nearest < 2.0f) {
-        float def_sd = bb_divf(kDefDev, nearest + 0.1f);
+        float def_sd = f_div(kDefDev, nearest + 0.1f);
         dev_def = pair_uniform(L, c, -def_sd, def_sd);
     }
     float dev_vel = 0.f;
@@ -162,12 +161,12 @@ BBD void pair_shot_pct(Lane &L, Vec3 opos, const SimConst &c)
     float dist_hoop = len(hoop - A.pos);
     float nearest = len(A.pos - opos);
     float dist_sd = kDistDev * dist_hoop;
-    float def_sd = bb_divf(kDefDev, nearest) + .0001f;
+    float def_sd = f_div(kDefDev, nearest) + .0001f;
     float vel_sd = kVelDev * len(A.vel);
-    float final_sd = bb_sqrtf((bb_divf(dist_sd * dist_sd, 3.f) + bb_divf(def_sd * def_sd, 3.f)) + bb_divf(vel_sd * vel_sd, 3.f));
-    float max_ang = bb_atanf(bb_divf(kHoopZone, dist_hoop));
-    float z = bb_divf(max_ang, final_sd);
-    A.curShot = bb_erff(bb_divf(z, bb_sqrtf(2.f)));
+    float final_sd = f_sqrt((f_div(dist_sd * dist_sd, 3.f) + f_div(def_sd * def_sd, 3.f)) + f_div(vel_sd * vel_sd, 3.f));
+    float max_ang = bb_atanf(f_div(kHoopZone, dist_hoop));
+    float z = f_div(max_ang, final_sd);
+    A.curShot = bb_erff(f_div(z, f_sqrt(2.f)));
 }
 
 /* resetWorld (gen.cpp:216-316) + setupAgentPositions (helper.cpp:108-160), 1-v-1 branch */
@@ -325,8 +324,17 @@ BBD void pair_reward(Lane &L, Vec3 opos)
     }
 }
 
+/* Phase alignment.  The step is ~3000 straight-line instructions executed once per warp,
+ * more than the SM's 32 KB instruction cache holds; warps of one block that drift apart
+ * each stream the whole kernel through that cache.  With kSync the block re-aligns at
+ * kPhases points, so its warps fetch the same ~8 KB of code at the same time.  Every
+ * warp of the block must pass the same number of barriers on either path. */
+constexpr int kPhases = 6;
+template <bool kSync> BBD void phase_sync() { if (kSync) __syncthreads(); }
+
 /* Systems 1..17 (game.cpp:1467-1516) for a 1-v-1, tag-mask, no-inbound world. */
-BBD void pair_step_fast(Lane &L, const SimConst &c, const unsigned m)
+template <bool kSync>
+BBD void pair_step_fast(Lane &L, const SimConst &c)
 {
     AgentS &A = L.A;
     BallS &B = L.B;
@@ -336,12 +344,13 @@ BBD void pair_step_fast(Lane &L, const SimConst &c, const unsigned m)
     sys_action_mask<true>(A, g);       /* 2 */
     sys_move_agent(A, c);              /* 3 */
     /* 4 grab, 5 pass: can_grab == can_pass == 0 under the tag mask -> both return at once */
-    Vec3 opos = xorv(m, A.pos);
+    phase_sync<kSync>();
+    Vec3 opos = xorv(A.pos);
     {                                  /* 6 shoot: agent 0's turn, then agent 1's */
         const int32_t wants = (A.canShoot != 0 && A.shoot != 0) ? 1 : 0;
         const float vlen = len(A.vel);
-        const int32_t ovmove = xori(m, A.move), owants = xori(m, wants);
-        const float ovlen = xorf(m, vlen);
+        const int32_t ovmove = xori(A.move), owants = xori(wants);
+        const float ovlen = xorf(vlen);
 #pragma unroll 1
         for (int k = 0; k < 2; k++) {
             const bool mine = (me == k);
@@ -350,9 +359,10 @@ BBD void pair_step_fast(Lane &L, const SimConst &c, const unsigned m)
                                 mine ? vlen : ovlen);
         }
     }
+    phase_sync<kSync>();
     {                                  /* 7 moveBall (game.cpp:82-125) */
         const int32_t holds = (A.hasBall == 1 && B.isGrabbed == 1 && B.holder == my_id(L)) ? 1 : 0;
-        const int32_t oholds = xori(m, holds);
+        const int32_t oholds = xori(holds);
         if (holds) B.pos = A.pos; else if (oholds) B.pos = opos;
         if (!(len(B.vel) == 0.f || B.isGrabbed == 1)) {
             float nx = clampf(B.pos.x + B.vel.x, 0.f, c.width);
@@ -362,10 +372,11 @@ BBD void pair_step_fast(Lane &L, const SimConst &c, const unsigned m)
         }
     }
     pair_shot_pct(L, opos, c);         /* 8 */
+    phase_sync<kSync>();
 #pragma unroll
     for (int h = 0; h < 2; h++) {      /* 9 score (game.cpp:873-953), 1-v-1 branch */
         float dx = B.pos.x - c.hoopX[h], dy = B.pos.y - c.hoopY;
-        float dist = bb_sqrtf(dx * dx + dy * dy);
+        float dist = f_sqrt(dx * dx + dy * dy);
         if (dist <= kHoopZone && (float)B.inFlight == 1.f) {
             int32_t points = B.spv;
             if (my_id(L) == B.sbAgent) A.points += (float)((me == h) ? -B.spv : B.spv);
@@ -388,7 +399,7 @@ BBD void pair_step_fast(Lane &L, const SimConst &c, const unsigned m)
     }
     {                                  /* 11 updateLastTouch (game.cpp:1034-1051): the later agent wins */
         const int32_t touch = (len(B.pos - A.pos) <= kAgentSize) ? 1 : 0;
-        const int32_t otouch = xori(m, touch);
+        const int32_t otouch = xori(touch);
         const int32_t t0 = me ? otouch : touch, t1 = me ? touch : otouch;
         if (t1) { B.ltAgent = L.idBase + 4; B.ltTeam = 1; }
         else if (t0) { B.ltAgent = L.idBase + 3; B.ltTeam = 0; }
@@ -405,13 +416,16 @@ BBD void pair_step_fast(Lane &L, const SimConst &c, const unsigned m)
     /* 13 inboundViolation: needs inboundingInProgress > 0.5 -> nothing on this path */
     if (L.resetNow != 0) { pair_reset_world(L, c); L.resetNow = 0; } /* 14 */
     A.pointsWorth = shot_point_value(A.pos, v3(me ? c.hoopX[0] : c.hoopX[1], c.hoopY, 0.f)); /* 15 */
-    opos = xorv(m, A.pos);
+    phase_sync<kSync>();
+    opos = xorv(A.pos);
     {                                  /* 16 collision */
-        Quat oq = xorq(m, A.q);
+        Quat oq = xorq(A.q);
         pair_collision(L, sel(me == 0, A.pos, opos), selq(me == 0, A.q, oq), sel(me == 0, opos, A.pos), selq(me == 0, oq, A.q));
     }
-    opos = xorv(m, A.pos);
-    pair_defense(L, opos, xori(m, A.hasBall), c); /* 17 */
+    phase_sync<kSync>();
+    opos = xorv(A.pos);
+    pair_defense(L, opos, xori(A.hasBall), c); /* 17 */
+    phase_sync<kSync>();
 }
 
 } // namespace bb

@@ -63,6 +63,19 @@ struct Quat { float w, x, y, z; };
 
 #define BBD __device__ __forceinline__
 
+/* IEEE sqrt / divide of the reference's float code.  -DBB_SUB_DIVSQRT=1 turns the ~15-instruction
+ * inline sequences into two shared subroutines (instruction-cache footprint vs call latency). */
+#ifndef BB_SUB_DIVSQRT
+#define BB_SUB_DIVSQRT 0
+#endif
+#if BB_SUB_DIVSQRT
+__device__ __noinline__ float f_sqrt(float x) { return bb_sqrtf(x); }
+__device__ __noinline__ float f_div(float a, float b) { return bb_divf(a, b); }
+#else
+BBD float f_sqrt(float x) { return bb_sqrtf(x); }
+BBD float f_div(float a, float b) { return bb_divf(a, b); }
+#endif
+
 BBD Vec3 v3(float x, float y, float z) { Vec3 r; r.x = x; r.y = y; r.z = z; return r; }
 BBD Vec3 operator+(Vec3 a, Vec3 b) { return v3(a.x + b.x, a.y + b.y, a.z + b.z); }
 BBD Vec3 operator-(Vec3 a, Vec3 b) { return v3(a.x - b.x, a.y - b.y, a.z - b.z); }
@@ -71,9 +84,9 @@ BBD Vec3 operator*(Vec3 a, float s) { return v3(a.x * s, a.y * s, a.z * s); }
 BBD float dot(Vec3 a, Vec3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 BBD Vec3 cross(Vec3 a, Vec3 b) { return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 BBD float len2(Vec3 a) { return a.x * a.x + a.y * a.y + a.z * a.z; }
-BBD float len(Vec3 a) { return bb_sqrtf(len2(a)); }
+BBD float len(Vec3 a) { return f_sqrt(len2(a)); }
 /* Vector3::normalize = *this * (1 / sqrt(length2)) */
-BBD Vec3 normalize(Vec3 a) { float inv = bb_divf(1.f, bb_sqrtf(len2(a))); return a * inv; }
+BBD Vec3 normalize(Vec3 a) { float inv = f_div(1.f, f_sqrt(len2(a))); return a * inv; }
 BBD float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 
 BBD Quat qmul(Quat a, Quat b)
@@ -175,12 +188,18 @@ BBD void threefry2x32(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32
     o0 = x0; o1 = x1;
 }
 
+/* RNG::sampleUniform for draw `count` of the world key: one shared subroutine */
+__device__ __noinline__ float rng_uniform01(uint32_t k0, uint32_t k1, uint32_t count)
+{
+    uint32_t a, b;
+    threefry2x32(k0, k1, count, 0u, a, b);
+    return (float)((a ^ b) >> 8) * 0x1p-24f;
+}
+
 /* RNG::sampleUniform then helper.cpp:8-11 */
 BBD float sample_uniform(World &W, const SimConst &c, float lo, float hi)
 {
-    uint32_t a, b;
-    threefry2x32(c.key0, c.key1, W.rng++, 0u, a, b);
-    float u = (float)((a ^ b) >> 8) * 0x1p-24f;
+    float u = rng_uniform01(c.key0, c.key1, W.rng++);
     return lo + (hi - lo) * u;
 }
 
@@ -400,7 +419,7 @@ BBD void sys_move_agent(AgentS &A, const SimConst &c)
     A.vel = A.vel + delta;
     if (A.hasBall == 1) maxS *= kBallSlowdown;
     float L = len(A.vel);
-    if (L > maxS) A.vel = A.vel * bb_divf(maxS, L);
+    if (L > maxS) A.vel = A.vel * f_div(maxS, L);
     float dx = A.vel.x * kDt, dy = A.vel.y * kDt;
     A.pos.x = clampf(A.pos.x + dx, 0.f, c.width);
     A.pos.y = clampf(A.pos.y + dy, 0.f, c.height);
@@ -468,7 +487,7 @@ BBD void sys_shoot(World &W, int i, const SimConst &c)
     float dev_def = 0.f;
     float nearest = len(A.pos - W.a[1 - i].pos); /* the only agent on the other team */
     if (nearest < 2.0f) {
-        float def_sd = bb_divf(kDefDev, nearest + 0.1f);
+        float def_sd = f_div(kDefDev, nearest + 0.1f);
         dev_def = sample_uniform(W, c, -def_sd, def_sd);
     }
     float dev_vel = 0.f;
@@ -522,12 +541,12 @@ BBD void sys_shot_pct(World &W, int i, const SimConst &c)
     float dist_hoop = len(hoop_pos(c, 1 - i) - A.pos);
     float nearest = len(A.pos - W.a[1 - i].pos);
     float dist_sd = kDistDev * dist_hoop;
-    float def_sd = bb_divf(kDefDev, nearest) + .0001f;
+    float def_sd = f_div(kDefDev, nearest) + .0001f;
     float vel_sd = kVelDev * len(A.vel);
-    float final_sd = bb_sqrtf((bb_divf(dist_sd * dist_sd, 3.f) + bb_divf(def_sd * def_sd, 3.f)) + bb_divf(vel_sd * vel_sd, 3.f));
-    float max_ang = bb_atanf(bb_divf(kHoopZone, dist_hoop));
-    float z = bb_divf(max_ang, final_sd);
-    A.curShot = bb_erff(bb_divf(z, bb_sqrtf(2.f)));
+    float final_sd = f_sqrt((f_div(dist_sd * dist_sd, 3.f) + f_div(def_sd * def_sd, 3.f)) + f_div(vel_sd * vel_sd, 3.f));
+    float max_ang = bb_atanf(f_div(kHoopZone, dist_hoop));
+    float z = f_div(max_ang, final_sd);
+    A.curShot = bb_erff(f_div(z, f_sqrt(2.f)));
 }
 
 /* game.cpp:873-953 */
@@ -537,7 +556,7 @@ BBD void sys_score(World &W, int h, const SimConst &c)
     GameS &g = W.g;
     const Vec3 hp = hoop_pos(c, h);
     float dx = B.pos.x - hp.x, dy = B.pos.y - hp.y;
-    float dist = bb_sqrtf(dx * dx + dy * dy);
+    float dist = f_sqrt(dx * dx + dy * dy);
     if (dist <= kHoopZone && (float)B.inFlight == 1.f) {
         int32_t points = B.spv;
         int32_t inb_team = h; /* agent h defends hoop h */
