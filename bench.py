@@ -102,15 +102,37 @@ class ClockSampler:
 
 
 def time_cpu_arm(worlds: int, steps: int, warmup: int, threads: int):
-    """Times the oracle (CPU restatement of the reference's step) on `threads` host threads."""
+    """Times the oracle (CPU restatement of the reference's step) on `threads` host threads.
+
+    The glibc-libm build of the oracle is the one timed: it is the arithmetic the reference's CPU
+    executor would run (the deterministic-math build exists for bit-exact GPU parity and is ~10 % slower)."""
     import oracle
 
-    orc = oracle.Oracle(worlds, start_x=31.515 / 2.0, start_y=16.764 / 2.0)
+    oracle.build()
+    orc = oracle.Oracle(worlds, start_x=31.515 / 2.0, start_y=16.764 / 2.0, libm=True)
     orc.run_synthetic(SEED, 0, warmup, 0, threads)
     t0 = time.perf_counter()
     orc.run_synthetic(SEED, warmup, steps, 0, threads)
     dt = time.perf_counter() - t0
     return worlds * steps / dt, dt
+
+
+def time_cpu_arm_for(worlds: int, seconds: float, threads: int):
+    """Bounded sample: a short probe sizes the run to about `seconds` of CPU work."""
+    rate, _ = time_cpu_arm(worlds, 100, 10, threads)
+    steps = max(200, int(rate * seconds / worlds))
+    value, dt = time_cpu_arm(worlds, steps, 10, threads)
+    return value, dt, steps
+
+
+def ncu_traffic(key: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of bb_step_kernel from the committed
+    `ncu --set full` capture (profiles/traffic.json; written by tools/ncu_summary.py runs)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(key)
+    except Exception:
+        return None
 
 
 def run_reference(args):
@@ -223,19 +245,21 @@ def run_engine(args):
     warm_value = total_worlds * K / (float(t.item()) * 1e-3)
 
     # ---------------------------------------------------------------- e2e: host buffers through the C ABI
-    h_act = torch.empty((n, 2, 6), dtype=torch.int32).pin_memory()
+    # Every step takes its own action batch from pinned host memory (a ring of pre-filled pinned
+    # buffers: the producer is not what is measured) and returns reward + done into pinned host memory.
+    ring = min(K + Wm, 32)
+    h_act = [actions[s].cpu().pin_memory() for s in range(ring)]
     h_rew = torch.empty((n, 2), dtype=torch.float32).pin_memory()
     h_done = torch.empty((n, 2), dtype=torch.float32).pin_memory()
-    h_actions_all = actions[Wm:Wm + min(K, 64)].cpu()  # host-side source batches (cycled)
-    np_act, np_rew, np_done = h_act.numpy(), h_rew.numpy(), h_done.numpy()
+    np_act = [a.numpy() for a in h_act]
+    np_rew, np_done = h_rew.numpy(), h_done.numpy()
     for s in range(Wm):
-        sim.step_host(np_act, np_rew, np_done)
+        sim.step_host(np_act[s % ring], np_rew, np_done)
     barrier()
     with sampler:
         t0 = time.perf_counter()
         for s in range(K):
-            h_act.copy_(h_actions_all[s % h_actions_all.shape[0]])   # this step's inputs, in pinned host memory
-            sim.step_host(np_act, np_rew, np_done)                    # H2D + step + D2H, synchronous
+            sim.step_host(np_act[(Wm + s) % ring], np_rew, np_done)  # actions over PCIe, step, reward+done back; synchronous
         barrier()
         e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -249,7 +273,7 @@ def run_engine(args):
     avg_kernel_s = (dev_ms / K) * 1e-3
     achieved = n * BYTES_PER_WORLD_STEP / avg_kernel_s / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "bb_step_kernel", "worlds_per_launch": n,
+                "traffic": ncu_traffic(f"bb_step_kernel@{n}"), "kernel": "bb_step_kernel", "worlds_per_launch": n,
                 "algorithmic_bytes_per_launch": n * BYTES_PER_WORLD_STEP, "peak_source": peak_src,
                 "note": "8192 worlds (15 MB) is latency/launch-bound by construction; see roofline_hbm_bound"}
 
@@ -278,16 +302,15 @@ def run_engine(args):
         avg = sum(ms) / len(ms) * 1e-3
         ach = LARGE_WORLDS * BYTES_PER_WORLD_STEP / avg / 1e9
         roofline_large = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                          "traffic": None, "worlds_per_launch": LARGE_WORLDS, "ms_per_launch": avg * 1e3,
+                          "traffic": ncu_traffic(f"bb_step_kernel@{LARGE_WORLDS}"), "worlds_per_launch": LARGE_WORLDS, "ms_per_launch": avg * 1e3,
                           "world_steps_per_s": LARGE_WORLDS / avg,
                           "note": "working set 1.9 GB > L2, so no flush needed; same kernel as the bench workload"}
         del bsim, big, bact
         threads = os.cpu_count() or 1
-        cpu_steps = args.cpu_steps
-        cv, cdt = time_cpu_arm(args.worlds_per_gpu, cpu_steps, 5, threads)
+        cv, cdt, cpu_steps = time_cpu_arm_for(args.worlds_per_gpu, args.cpu_seconds, threads)
         cpu_baseline = {"value": cv, "unit": UNIT, "cores": threads, "kind": "port",
-                        "sample": f"{args.worlds_per_gpu} worlds x {cpu_steps} steps, {cdt:.1f} s of CPU work; oracle/ restatement "
-                                  "(the reference's Madrona CPU executor cannot be built: submodule absent)"}
+                        "sample": f"{args.worlds_per_gpu} worlds x {cpu_steps} steps, {cdt:.1f} s of CPU work on {threads} threads; oracle/ "
+                                  "restatement on glibc libm (the reference's Madrona CPU executor cannot be built: submodule absent)"}
 
     clocks = sampler.report()
     if rank == 0:
@@ -300,7 +323,8 @@ def run_engine(args):
                        "l2": "flushed before every timed step (256 MiB memset outside the per-step CUDA events)",
                        "parallelism": f"world-sharded x{n_gpus}, no collective in the step"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "what": "bb_step_host: pinned-host actions H2D, step, reward+done D2H, synchronous per step"},
+                    "what": "bb_step_host per step: action rows read from pinned host memory over PCIe, fused step, "
+                            "reward+done written back to pinned host memory, host waits for completion"},
             "gpu_launches": int(gpu_launches),
             "clocks": clocks,
             "roofline": roofline,
@@ -323,7 +347,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="engine", choices=["engine", "reference"])
     ap.add_argument("--worlds-per-gpu", type=int, default=WORLDS_PER_GPU)
-    ap.add_argument("--cpu-steps", type=int, default=1000)
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="CPU work of the cpu_baseline sample")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

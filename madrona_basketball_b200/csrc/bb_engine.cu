@@ -63,7 +63,9 @@ static const int kColBytes[26] = {8, 56, 48, 32, 24, 1024, 8, 8, 16, 24, 32, 40,
 struct StepParams {
     Columns col;
     SimConst sc;
-    const int32_t *actionSrc; /* optional external Action source, [N,2,6] */
+    const int32_t *actionSrc; /* optional external Action source, [N,2,6] (device, or mapped pinned host) */
+    float *rewardOut;         /* optional mirrors of Reward / Done, [N,2] (mapped pinned host): bb_step_host */
+    float *doneOut;
     int64_t numWorlds;
 };
 
@@ -286,6 +288,8 @@ BBD void store_lane(const Lane &L, const StepParams &p, int64_t w)
         C.curStep[r] = A.curStep;
         C.reward[r] = A.reward;
         C.done[r] = A.done;
+        if (p.rewardOut) p.rewardOut[r] = A.reward;
+        if (p.doneOut) p.doneOut[r] = A.done;
     }
     {
         float *tp = C.attributes + r * 9;
@@ -562,7 +566,7 @@ void pick_launch_shape(int64_t n_worlds, int *threads, int *sync)
     const int64_t warps = (n_worlds * 2 + 31) / 32;
     if (warps <= 148 * 8) { *threads = 32; *sync = 0; }
     else if (warps <= 148 * 32) { *threads = 64; *sync = 0; }
-    else { *threads = 128; *sync = 0; }
+    else { *threads = 128; *sync = 1; }
     if (const char *s = getenv("BB_BLOCK_THREADS")) {
         int v = atoi(s);
         if (v >= 32 && v <= 512 && v % 32 == 0) *threads = v;
@@ -571,10 +575,13 @@ void pick_launch_shape(int64_t n_worlds, int *threads, int *sync)
     if (*threads == 32) *sync = 0;
 }
 
-int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream)
+int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, float *reward_out = nullptr,
+                float *done_out = nullptr)
 {
     bb::StepParams p = e->params;
     p.actionSrc = actions_dev;
+    p.rewardOut = reward_out;
+    p.doneOut = done_out;
     const int threads = e->blockThreads;
     const int blocks = (int)((e->N * 2 + threads - 1) / threads);
     const int smem = bb::smem_bytes_for(threads);
@@ -662,6 +669,8 @@ bb_engine *bb_create(const bb_config *cfg)
     e->params.sc.key0 = key[0];
     e->params.sc.key1 = key[1];
     e->params.actionSrc = nullptr;
+    e->params.rewardOut = nullptr;
+    e->params.doneOut = nullptr;
     e->params.numWorlds = e->N;
 
     pick_launch_shape(e->N, &e->blockThreads, &e->phaseSync);
@@ -715,15 +724,32 @@ int bb_step_with_actions(bb_engine *e, const int32_t *actions_dev, void *cuda_st
     return launch_step(e, actions_dev, (cudaStream_t)cuda_stream);
 }
 
+/* Device alias of a pinned (page-locked, mapped) host buffer, or NULL for pageable memory.
+ * Queried every call (about a microsecond): a cached answer could outlive the buffer. */
+static void *mapped_alias(const void *host)
+{
+    if (!host) return nullptr;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, host) == cudaSuccess && at.type == cudaMemoryTypeHost) return at.devicePointer;
+    cudaGetLastError();
+    return nullptr;
+}
+
 int bb_step_host(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host, float *obs_host)
 {
     cudaStream_t s = e->hostStream;
     const bb::Columns &C = e->params.col;
-    if (actions_host)
+    /* Pinned buffers: the kernel itself moves the bytes over PCIe (reads the action rows from, and
+     * mirrors reward / done into, the mapped host pages) -- one launch + one wait per step instead of
+     * three DMA operations around it.  Pageable buffers: staged copies. */
+    const int32_t *act_dev = (const int32_t *)mapped_alias(actions_host);
+    float *rew_dev = (float *)mapped_alias(reward_host);
+    float *done_dev = (float *)mapped_alias(done_host);
+    if (actions_host && !act_dev)
         BB_CUDA_OK(cudaMemcpyAsync(C.action, actions_host, (size_t)e->N * 48, cudaMemcpyHostToDevice, s));
-    if (launch_step(e, nullptr, s) != 0) return -1;
-    if (reward_host) BB_CUDA_OK(cudaMemcpyAsync(reward_host, C.reward, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
-    if (done_host) BB_CUDA_OK(cudaMemcpyAsync(done_host, C.done, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
+    if (launch_step(e, act_dev, s, rew_dev, done_dev) != 0) return -1;
+    if (reward_host && !rew_dev) BB_CUDA_OK(cudaMemcpyAsync(reward_host, C.reward, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
+    if (done_host && !done_dev) BB_CUDA_OK(cudaMemcpyAsync(done_host, C.done, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
     if (obs_host) BB_CUDA_OK(cudaMemcpyAsync(obs_host, C.obs, (size_t)e->N * 1024, cudaMemcpyDeviceToHost, s));
     BB_CUDA_OK(cudaStreamSynchronize(s));
     return 0;
