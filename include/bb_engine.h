@@ -131,6 +131,11 @@ int bb_fill_actions(bb_engine *e, int32_t *actions_dev, uint32_t seed, int64_t s
  * (slots 0..18, then 100..106); out_dev is device memory, u64 [N]. */
 int bb_checksum(bb_engine *e, uint64_t *out_dev, void *cuda_stream);
 
+/* Test hook: evaluates one libm call site of the step path ON THE DEVICE with
+ * the arithmetic spec include/bb_math.h; fn: 0 sinf, 1 cosf, 2 atanf, 3 atan2f(x, y), 4 acosf,
+ * 5 expf, 6 erff.  x / y / out are device pointers, f32 [n] (y only read for atan2f). */
+int bb_math_eval(int fn, const float *x_dev, const float *y_dev, float *out_dev, int64_t n, void *cuda_stream);
+
 /* Number of kernels this engine has launched since creation (bench.py's
  * gpu_launches claim). */
 int64_t bb_launch_count(const bb_engine *e);

@@ -12,7 +12,7 @@ LIB_PATH = os.environ.get("BB_LIB_PATH") or os.path.join(_HERE, "libbball.so")  
 SYMBOLS = [
     "bb_create", "bb_destroy", "bb_step", "bb_step_with_actions", "bb_step_host", "bb_export",
     "bb_set_action", "bb_trigger_reset", "bb_fill_actions", "bb_checksum", "bb_launch_count",
-    "bb_num_worlds", "bb_last_error",
+    "bb_num_worlds", "bb_last_error", "bb_math_eval",
 ]
 
 
@@ -64,6 +64,8 @@ def load() -> ctypes.CDLL:
     lib.bb_fill_actions.argtypes = [vp, vp, u32, i64, i64, vp]
     lib.bb_checksum.restype = ctypes.c_int
     lib.bb_checksum.argtypes = [vp, vp, vp]
+    lib.bb_math_eval.restype = ctypes.c_int
+    lib.bb_math_eval.argtypes = [ctypes.c_int, vp, vp, vp, i64, vp]
     lib.bb_launch_count.restype = i64
     lib.bb_launch_count.argtypes = [vp]
     lib.bb_num_worlds.restype = i64

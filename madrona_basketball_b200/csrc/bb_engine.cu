@@ -446,6 +446,24 @@ __global__ void bb_fill_actions_kernel(int32_t *actions, int64_t numWorlds, uint
     dst[2] = make_int2((int32_t)((b >> 1) & 1u), (int32_t)((b >> 2) & 1u));
 }
 
+/* test hook: the spec's libm call sites evaluated on the device (bb_math_eval) */
+__global__ void bb_math_eval_kernel(int fn, const float *x, const float *y, float *out, int64_t n)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float r = 0.f;
+    switch (fn) {
+    case 0: r = bb_sinf(x[i]); break;
+    case 1: r = bb_cosf(x[i]); break;
+    case 2: r = bb_atanf(x[i]); break;
+    case 3: r = bb_atan2f(x[i], y[i]); break;
+    case 4: r = bb_acosf(x[i]); break;
+    case 5: r = bb_expf(x[i]); break;
+    case 6: r = bb_erff(x[i]); break;
+    }
+    out[i] = r;
+}
+
 struct ChecksumParams {
     const uint32_t *col[26];
     int words[26];
@@ -829,6 +847,15 @@ int bb_checksum(bb_engine *e, uint64_t *out_dev, void *cuda_stream)
     }
     bb::bb_checksum_kernel<<<(int)((e->N + 127) / 128), 128, 0, (cudaStream_t)cuda_stream>>>(cp, e->N, out_dev);
     e->launches++;
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int bb_math_eval(int fn, const float *x_dev, const float *y_dev, float *out_dev, int64_t n, void *cuda_stream)
+{
+    if (fn < 0 || fn > 6 || n < 0) { set_error("bb_math_eval: bad arguments"); return -1; }
+    if (n == 0) return 0;
+    bb::bb_math_eval_kernel<<<(int)((n + 255) / 256), 256, 0, (cudaStream_t)cuda_stream>>>(fn, x_dev, y_dev ? y_dev : x_dev, out_dev, n);
     BB_CUDA_OK(cudaGetLastError());
     return 0;
 }

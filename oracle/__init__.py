@@ -75,8 +75,21 @@ def _load(libm: bool) -> ctypes.CDLL:
     lib.orc_threefry2x32.argtypes = [ctypes.c_uint32] * 4 + [ctypes.POINTER(ctypes.c_uint32)]
     lib.orc_rng_uniform.restype = ctypes.c_float
     lib.orc_rng_uniform.argtypes = [ctypes.c_uint32, ctypes.c_uint32]
+    lib.orc_math_eval.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]
     _LIBS[name] = lib
     return lib
+
+
+MATH_FNS = {"sinf": 0, "cosf": 1, "atanf": 2, "atan2f": 3, "acosf": 4, "expf": 5, "erff": 6}
+
+
+def math_eval(fn: str, x: np.ndarray, y: np.ndarray | None = None, libm: bool = False) -> np.ndarray:
+    """Elementwise evaluation of one libm call site in the spec or the glibc build."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    y = np.ascontiguousarray(y if y is not None else x, dtype=np.float32)
+    out = np.empty_like(x)
+    _load(libm).orc_math_eval(MATH_FNS[fn], x.ctypes.data, y.ctypes.data, out.ctypes.data, x.size)
+    return out
 
 
 def threefry2x32(k0: int, k1: int, c0: int, c1: int):

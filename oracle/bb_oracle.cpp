@@ -1527,4 +1527,23 @@ float orc_rng_uniform(uint32_t seed, uint32_t draw_index)
     return rng.sampleUniform();
 }
 
+/* fn: 0 sinf, 1 cosf, 2 atanf, 3 atan2f(x, y), 4 acosf, 5 expf, 6 erff -- whichever arithmetic this
+ * build uses (include/bb_math.h spec, or glibc with -DBB_USE_LIBM). */
+void orc_math_eval(int fn, const float *x, const float *y, float *out, int64_t n)
+{
+    for (int64_t i = 0; i < n; i++) {
+        float r = 0.f;
+        switch (fn) {
+        case 0: r = m_sinf(x[i]); break;
+        case 1: r = m_cosf(x[i]); break;
+        case 2: r = m_atanf(x[i]); break;
+        case 3: r = m_atan2f(x[i], y[i]); break;
+        case 4: r = m_acosf(x[i]); break;
+        case 5: r = m_expf(x[i]); break;
+        case 6: r = m_erff(x[i]); break;
+        }
+        out[i] = r;
+    }
+}
+
 } // extern "C"

@@ -84,6 +84,9 @@ void orc_checksum(orc_sim *sim, uint64_t *out_per_world);
 /* Known-answer hooks for tests. */
 void orc_threefry2x32(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t out[2]);
 float orc_rng_uniform(uint32_t seed, uint32_t draw_index);
+/* Elementwise libm call sites of SURVEY App. E in this build's arithmetic.
+ * fn: 0 sinf, 1 cosf, 2 atanf, 3 atan2f(x, y), 4 acosf, 5 expf, 6 erff. */
+void orc_math_eval(int fn, const float *x, const float *y, float *out, int64_t n);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,116 @@
+"""CPU checks of the drop-in boundary: the C-ABI library loads and exports every symbol
+include/bb_engine.h declares, the Python mirror has the reference's surface
+(src/bindings.cpp:14-101), and nothing computes without a GPU (no fallback)."""
+import ctypes
+import inspect
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "bb_engine.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(bb_[a-z_0-9]+)\s*\(", text)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from madrona_basketball_b200 import build, _lib
+
+    build.build_engine()      # no-op when libbball.so is newer than its sources
+    return _lib.load()
+
+
+def test_library_exports_every_declared_symbol(lib):
+    from madrona_basketball_b200 import _lib
+
+    declared = _declared_symbols()
+    assert len(declared) >= 13
+    for sym in declared:
+        assert hasattr(lib, sym), f"libbball.so lacks {sym}"
+    assert sorted(_lib.SYMBOLS) == declared   # the ctypes table covers the whole header
+
+
+def test_library_is_sm100a_native_code():
+    """The .so must carry sm_100a SASS for the step kernel (no PTX-only / other-arch build)."""
+    import shutil
+    import subprocess
+
+    from madrona_basketball_b200 import _lib
+
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    out = subprocess.run([cuobjdump, "-lelf", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in out, out
+
+
+def test_slot_numbers_follow_export_id_enum():
+    """types.hpp:10-42 ExportID order == bb_slot == the Python table."""
+    from madrona_basketball_b200.manager import SLOTS
+
+    text = open(os.path.join(ROOT, "include", "bb_engine.h")).read()
+    enum = dict((m.group(1), int(m.group(2))) for m in re.finditer(r"BB_SLOT_([A-Z_]+) = (\d+)", text))
+    order = ["RESET", "GAME_STATE", "ACTION", "ACTION_MASK", "AGENT_POS", "OBSERVATIONS", "REWARD", "DONE",
+             "AGENT_ENTITY_ID", "AGENT_POSSESSION", "ORIENTATION", "TEAM_DATA", "AGENT_STATS", "BASKETBALL_POS",
+             "BALL_PHYSICS", "BALL_ENTITY_ID", "BALL_GRABBED", "BALL_VELOCITY", "HOOP_POS"]
+    assert [enum[k] for k in order] == list(range(19))
+    assert SLOTS["agent_team"] == enum["TEAM_DATA"] and SLOTS["observations"] == enum["OBSERVATIONS"]
+
+
+def test_python_surface_matches_bindings_cpp():
+    """Class name, constructor keywords and the 22 methods of src/bindings.cpp:17-99."""
+    import madrona_basketball as mba
+    from madrona_basketball.madrona import ExecMode
+
+    assert ExecMode.CPU is not ExecMode.CUDA and mba.madrona.ExecMode is ExecMode
+    cls = mba.SimpleGridworldSimulator
+    params = list(inspect.signature(cls.__init__).parameters)
+    assert params[1:9] == ["discrete_x", "discrete_y", "start_x", "start_y", "max_episode_length", "exec_mode",
+                           "num_worlds", "gpu_id"]
+    assert inspect.signature(cls.__init__).parameters["gpu_id"].default == -1
+    methods = ["step", "set_action", "trigger_reset", "reset_tensor", "action_tensor", "observations_tensor",
+               "agent_pos_tensor", "reward_tensor", "done_tensor", "basketball_pos_tensor", "ball_physics_tensor",
+               "ball_grabbed_tensor", "agent_possession_tensor", "agent_entity_id_tensor", "ball_entity_id_tensor",
+               "agent_team_tensor", "game_state_tensor", "orientation_tensor", "hoop_pos_tensor",
+               "agent_stats_tensor", "action_mask_tensor", "ball_velocity_tensor"]
+    for m in methods:
+        assert callable(getattr(cls, m)), m
+    # nanobind exposes set_action(world_idx, agent_idx, move_speed, move_angle, rotate, grab, pass, shoot)
+    sa = list(inspect.signature(cls.set_action).parameters)
+    assert sa[1:7] == ["world_idx", "agent_idx", "move_speed", "move_angle", "rotate", "grab"]
+
+
+def test_no_cpu_path_behind_the_boundary(lib):
+    """ExecMode.CPU is refused, and on a box without a GPU bb_create fails loudly instead of falling back."""
+    import torch
+
+    import madrona_basketball as mba
+    from madrona_basketball_b200 import _lib
+
+    args = dict(discrete_x=32, discrete_y=17, start_x=15.7575, start_y=8.382, max_episode_length=39600, num_worlds=4)
+    with pytest.raises(RuntimeError, match="CUDA-only"):
+        mba.SimpleGridworldSimulator(exec_mode=mba.madrona.ExecMode.CPU, **args)
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no CUDA device|bb_create"):
+            mba.SimpleGridworldSimulator(exec_mode=mba.madrona.ExecMode.CUDA, gpu_id=0, **args)
+        assert "no CPU path" in _lib.last_error() or "CUDA" in _lib.last_error()
+    cfg = _lib.BBConfig(0, 32, 17, 15.7575, 8.382, 39600, 0, 0, 1)
+    assert not lib.bb_create(ctypes.byref(cfg))       # num_worlds must be positive
+    assert "num_worlds" in _lib.last_error()
+
+
+def test_product_package_never_imports_the_oracle():
+    """The oracle is test infrastructure: nothing under madrona_basketball_b200/ (or the drop-in
+    alias package) may reference it."""
+    for pkg in ("madrona_basketball_b200", "madrona_basketball"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, pkg)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                    text = open(os.path.join(dirpath, f)).read()
+                    assert not re.search(r"^\s*(import|from)\s+oracle\b", text, flags=re.M), (dirpath, f)
+                    assert "liboracle" not in text and "bb_oracle" not in text, (dirpath, f)
