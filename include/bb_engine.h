@@ -103,6 +103,22 @@ int bb_step_with_actions(bb_engine *e, const int32_t *actions_dev, void *cuda_st
 int bb_step_host(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host,
                  float *obs_host);
 
+/* Persistent-server variant of bb_step_host for latency-bound host-driven loops (no reference
+ * counterpart).  bb_serve_begin leaves one resident kernel on the device; each bb_serve_step rings
+ * a doorbell in mapped pinned memory, the kernel runs one Manager::step() (action rows read from
+ * `actions_host`, reward / done / observations mirrored into the non-NULL host buffers, device
+ * columns updated as in bb_step) and publishes completion back; the call returns when the results
+ * are in host memory.  No kernel launch and no stream wait per step.  All buffers must be pinned
+ * (cudaHostAlloc / torch pin_memory).  Between begin and end do not call bb_step* / setters, and
+ * do not write the exported columns from other streams while a step is in flight.  The server
+ * leaves the GPU by itself after 2 s without a step (BB_SERVE_IDLE_MS) and is restarted
+ * transparently by the next bb_serve_step; device-wide synchronisation (cudaDeviceSynchronize,
+ * cudaFree) stalls until then, so call bb_serve_end first. */
+int bb_serve_begin(bb_engine *e);
+int bb_serve_step(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host,
+                  float *obs_host);
+int bb_serve_end(bb_engine *e);
+
 /* Manager::*Tensor() (mgr.cpp:317-445) / Impl::exportTensor (mgr.cpp:121-126):
  * device pointer + declared dtype/shape of a column.  The engine owns the memory
  * for its lifetime; callers may read and write through the pointer between steps

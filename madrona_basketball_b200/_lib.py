@@ -12,7 +12,7 @@ LIB_PATH = os.environ.get("BB_LIB_PATH") or os.path.join(_HERE, "libbball.so")  
 SYMBOLS = [
     "bb_create", "bb_destroy", "bb_step", "bb_step_with_actions", "bb_step_host", "bb_export",
     "bb_set_action", "bb_trigger_reset", "bb_fill_actions", "bb_checksum", "bb_launch_count",
-    "bb_num_worlds", "bb_last_error", "bb_math_eval",
+    "bb_num_worlds", "bb_last_error", "bb_math_eval", "bb_serve_begin", "bb_serve_step", "bb_serve_end",
 ]
 
 
@@ -53,6 +53,12 @@ def load() -> ctypes.CDLL:
     lib.bb_step_with_actions.argtypes = [vp, vp, vp]
     lib.bb_step_host.restype = ctypes.c_int
     lib.bb_step_host.argtypes = [vp, vp, vp, vp, vp]
+    lib.bb_serve_begin.restype = ctypes.c_int
+    lib.bb_serve_begin.argtypes = [vp]
+    lib.bb_serve_step.restype = ctypes.c_int
+    lib.bb_serve_step.argtypes = [vp, vp, vp, vp, vp]
+    lib.bb_serve_end.restype = ctypes.c_int
+    lib.bb_serve_end.argtypes = [vp]
     lib.bb_export.restype = ctypes.c_int
     lib.bb_export.argtypes = [vp, ctypes.c_int, ctypes.POINTER(vp), ctypes.POINTER(ctypes.c_int),
                               ctypes.POINTER(i64), ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int)]

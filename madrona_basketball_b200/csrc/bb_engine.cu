@@ -60,13 +60,21 @@ struct Columns {
 static const int kColBytes[26] = {8, 56, 48, 32, 24, 1024, 8, 8, 16, 24, 32, 40, 16, 12, 28, 8, 8, 12, 24,
                                   24, 16, 8, 72, 8, 4, 4};
 
+/* Per-step I/O redirection (all optional). */
+struct StepIo {
+    const int32_t *actionSrc; /* external Action source, [N,2,6] (device, or mapped pinned host) */
+    float *rewardOut;         /* mirrors of Reward / Done, [N,2] (mapped pinned host): host-buffer steps */
+    float *doneOut;
+    float *obsOut;            /* mirror of Observations, [N,2,128] (mapped pinned host) */
+    int actionsVolatile;      /* persistent server: the host rewrites actionSrc between steps -> ld.cv */
+};
+
 struct StepParams {
     Columns col;
     SimConst sc;
-    const int32_t *actionSrc; /* optional external Action source, [N,2,6] (device, or mapped pinned host) */
-    float *rewardOut;         /* optional mirrors of Reward / Done, [N,2] (mapped pinned host): bb_step_host */
-    float *doneOut;
+    StepIo io;
     int64_t numWorlds;
+    int prefetchBlocks;       /* > 0: block b pulls the state rows of block b + prefetchBlocks into L2 */
 };
 
 /* ------------------------------ obs image --------------------------------- *
@@ -188,7 +196,7 @@ BBD void write_obs_image(float *img, const Lane &L, Vec3 opos, int32_t oInb, con
 
 /* Lane (w, me): its agent's rows + the world's ball / GameState / clock / RNG rows
  * (the pair reads the same world addresses: one broadcast transaction). */
-BBD void load_lane(Lane &L, const StepParams &p, int64_t w, int me)
+BBD void load_lane(Lane &L, const StepParams &p, const StepIo &io, int64_t w, int me)
 {
     const Columns &C = p.col;
     const int64_t r = w * 2 + me; /* agent row */
@@ -197,8 +205,10 @@ BBD void load_lane(Lane &L, const StepParams &p, int64_t w, int me)
     L.me = me;
     L.didReset = false;
     {
-        const int2 *ap = reinterpret_cast<const int2 *>((p.actionSrc ? p.actionSrc : C.action) + r * 6);
-        int2 a0 = ap[0], a1 = ap[1], a2 = ap[2];
+        const int2 *ap = reinterpret_cast<const int2 *>((io.actionSrc ? io.actionSrc : C.action) + r * 6);
+        int2 a0, a1, a2;
+        if (io.actionsVolatile) { a0 = __ldcv(ap); a1 = __ldcv(ap + 1); a2 = __ldcv(ap + 2); }
+        else { a0 = ap[0]; a1 = ap[1]; a2 = ap[2]; }
         A.move = a0.x; A.moveAngle = a0.y; A.rotate = a1.x; A.grab = a1.y; A.pass = a2.x; A.shoot = a2.y;
     }
     A.reset = C.reset[r];
@@ -254,7 +264,7 @@ BBD void load_lane(Lane &L, const StepParams &p, int64_t w, int me)
     /* mask / reward / done are fully rewritten by tick and actionMask */
 }
 
-BBD void store_lane(const Lane &L, const StepParams &p, int64_t w)
+BBD void store_lane(const Lane &L, const StepParams &p, const StepIo &io, int64_t w)
 {
     const Columns &C = p.col;
     const int me = L.me;
@@ -288,8 +298,8 @@ BBD void store_lane(const Lane &L, const StepParams &p, int64_t w)
         C.curStep[r] = A.curStep;
         C.reward[r] = A.reward;
         C.done[r] = A.done;
-        if (p.rewardOut) p.rewardOut[r] = A.reward;
-        if (p.doneOut) p.doneOut[r] = A.done;
+        if (io.rewardOut) io.rewardOut[r] = A.reward;
+        if (io.doneOut) io.doneOut[r] = A.done;
     }
     {
         float *tp = C.attributes + r * 9;
@@ -330,7 +340,7 @@ BBD void store_world(const World &W, const StepParams &p, int64_t w)
     for (int i = 0; i < 2; i++) {
         L.A = W.a[i];
         L.me = i;
-        store_lane(L, p, w);
+        store_lane(L, p, p.io, w);
         const Columns &C = p.col;
         const int64_t r = w * 2 + i;
         C.reset[r] = W.a[i].reset;
@@ -339,6 +349,42 @@ BBD void store_world(const World &W, const StepParams &p, int64_t w)
         tp[1] = __float_as_int(i ? 128.f : 0.f); tp[2] = __float_as_int(i ? 0.f : 100.f); tp[3] = __float_as_int(i ? 128.f : 255.f);
         tp[4] = W.idBase + i;
     }
+}
+
+/* L2 prefetch of the rows a later block will load (HBM-bound regime).  Every column is contiguous
+ * over worlds, so the rows of `worlds` consecutive worlds are one 16-byte-aligned segment per column:
+ * lane c of the calling warp issues one cp.async.bulk.prefetch.L2 for column c.  By the time the
+ * block that owns those worlds starts, its up-front loads would hit L2 instead of DRAM.  Tuning knob
+ * only (BB_PREFETCH_BLOCKS): on B200 it costs more than it hides, see bb_create. */
+BBD void prefetch_state_rows(const StepParams &p, int64_t world0, int worlds, int lane)
+{
+    const Columns &C = p.col;
+    const void *base = nullptr;
+    int bpw = 0; /* bytes per world */
+    switch (lane) {
+    case 0: base = p.io.actionSrc ? (const void *)p.io.actionSrc : (const void *)C.action; bpw = 48; break;
+    case 1: base = C.reset; bpw = 8; break;
+    case 2: base = C.gameState; bpw = 56; break;
+    case 3: base = C.agentPos; bpw = 24; break;
+    case 4: base = C.agentVel; bpw = 24; break;
+    case 5: base = C.orientation; bpw = 32; break;
+    case 6: base = C.possession; bpw = 24; break;
+    case 7: base = C.inbounding; bpw = 16; break;
+    case 8: base = C.cooldown; bpw = 8; break;
+    case 9: base = C.stats; bpw = 16; break;
+    case 10: base = C.curStep; bpw = 8; break;
+    case 11: base = C.attributes; bpw = 72; break;
+    case 12: base = C.ballPos; bpw = 12; break;
+    case 13: base = C.ballVel; bpw = 12; break;
+    case 14: base = C.ballPhysics; bpw = 28; break;
+    case 15: base = C.grabbed; bpw = 8; break;
+    case 16: base = C.worldClock; bpw = 4; break;
+    case 17: base = C.rngCount; bpw = 4; break;
+    default: return;
+    }
+    const char *src = (const char *)base + world0 * bpw;
+    const uint32_t bytes = (uint32_t)(worlds * bpw);
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 
 /* ------------------------------ kernels ----------------------------------- */
@@ -373,24 +419,17 @@ BBD void emit_obs_rows(const float *warpImg, float *obs, int64_t warpWorld0, int
 #ifndef BB_MIN_BLOCKS_128
 #define BB_MIN_BLOCKS_128 4 /* resident 128-thread blocks per SM the register budget is cut for */
 #endif
-/* One Manager::step(): thread t = (world t/2, agent t%2).  blockDim.x is any multiple of
- * 32 up to kMaxT; dynamic shared memory = smem_bytes_for(blockDim.x).  kSync: see phase_sync. */
-template <int kMaxT, bool kSync>
-__global__ void __launch_bounds__(kMaxT, BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_kernel(const __grid_constant__ StepParams p)
+/* One Manager::step() for the 16 worlds [warpWorld0, warpWorld0 + 16) on the calling warp:
+ * lane = (world (lane >> 1), agent (lane & 1)).  warpImg: this warp's observation image. */
+template <bool kSync>
+BBD void step_tile(const StepParams &p, const StepIo &io, float *warpImg, int64_t warpWorld0, int lane)
 {
-    extern __shared__ float smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float *warpImg = smem + warp * kWorldsPerWarp * kFeatStride;
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t warpWorld0 = (t - lane) >> 1;
-    const bool warpLive = warpWorld0 < p.numWorlds;
-    if (!kSync && !warpLive) return; /* whole warp past the end (with barriers it shadows the last world) */
-    const int64_t w = t >> 1;
+    const int64_t w = warpWorld0 + (lane >> 1);
     const bool valid = w < p.numWorlds;
-    const int me = (int)(t & 1);
+    const int me = lane & 1;
     Lane L;
     /* tail lanes shadow the last world so that every shuffle stays warp-wide; they never store */
-    load_lane(L, p, valid ? w : p.numWorlds - 1, me);
+    load_lane(L, p, io, valid ? w : p.numWorlds - 1, me);
     __syncwarp(); /* all of the pair's loads precede any of its stores */
     const bool tag = (p.sc.flags & BB_FLAG_TAG_MASK) != 0;
     const bool fast = __all_sync(kFullMask, tag && L.G.isOneOnOne == 1 && L.G.inbInProgress == 0);
@@ -401,12 +440,140 @@ __global__ void __launch_bounds__(kMaxT, BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_ste
     const int32_t oInb = xori(L.A.imInb);
     write_obs_image(warpImg + (lane >> 1) * kFeatStride, L, opos, oInb, p.sc); /* system 18 */
     pair_reward(L, opos);                                    /* system 19 */
-    if (valid) store_lane(L, p, w);
+    if (valid) store_lane(L, p, io, w);
     __syncwarp();
-    if (!warpLive) return;
+    if (warpWorld0 >= p.numWorlds) return;
     int64_t remain = p.numWorlds - warpWorld0;
     int nValid = remain >= kWorldsPerWarp ? kWorldsPerWarp : (int)remain;
     emit_obs_rows(warpImg, p.col.obs, warpWorld0, nValid, lane);
+    if (io.obsOut) emit_obs_rows(warpImg, io.obsOut, warpWorld0, nValid, lane);
+}
+
+/* One Manager::step(): thread t = (world t/2, agent t%2).  blockDim.x is any multiple of
+ * 32 up to kMaxT; dynamic shared memory = smem_bytes_for(blockDim.x).  kSync: see phase_sync. */
+template <int kMaxT, bool kSync>
+__global__ void __launch_bounds__(kMaxT, BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_kernel(const __grid_constant__ StepParams p)
+{
+    extern __shared__ float smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float *warpImg = smem + warp * kWorldsPerWarp * kFeatStride;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t warpWorld0 = (t - lane) >> 1;
+    if (!kSync && warpWorld0 >= p.numWorlds) return; /* whole warp past the end (with barriers it shadows the last world) */
+    if (p.prefetchBlocks > 0 && warp == 0) { /* worlds per block = blockDim.x / 2, a multiple of 16 */
+        const int wpb = blockDim.x >> 1;
+        const int64_t w0 = ((int64_t)blockIdx.x + p.prefetchBlocks) * wpb;
+        if (w0 + wpb <= p.numWorlds) prefetch_state_rows(p, w0, wpb, lane);
+    }
+    step_tile<kSync>(p, p.io, warpImg, warpWorld0, lane);
+}
+
+/* ------------------------------ persistent server -------------------------- *
+ * Host-driven stepping without a kernel launch or a stream wait per step (bb_serve_*): the kernel
+ * stays resident, block 0 polls a doorbell in mapped pinned host memory, every block then runs
+ * step_tile() for its tiles (reading the action rows from, and mirroring reward / done / observations
+ * into, host memory over PCIe), and the last block to finish publishes the sequence number back to
+ * the host.  All blocks must be co-resident (grid <= occupancy x SMs; tiles are strided over it).
+ * The server exits by itself after idleTimeoutNs without a doorbell, so a vanished host cannot wedge
+ * the GPU. */
+struct ServeHostCtl { /* mapped pinned host memory */
+    /* host -> device doorbell: four 64-bit words {actions, reward, done, obs}, each the buffer's device
+     * alias (< 2^48) tagged in its top 16 bits with the low 16 bits of the sequence number to run.
+     * Each word is written and read atomically, and the step starts only when all four carry the
+     * wanted tag, so one poll (one PCIe round trip) fetches doorbell and buffers together.
+     * word[0] == kServeExitWord: leave. */
+    unsigned long long word[4];
+    int32_t complete;        /* device -> host: last completed sequence number */
+    int32_t alive;           /* device -> host: 1 while the server runs */
+    unsigned long long tSeen, tDone; /* %globaltimer when block 0 saw the doorbell / the last block finished (tuning) */
+};
+constexpr unsigned long long kServeExitWord = ~0ull;
+constexpr unsigned long long kServePtrMask = (1ull << 48) - 1;
+struct ServeDevCtl { /* device memory */
+    int32_t seq;
+    unsigned int doneCount;
+    StepIo io;
+};
+constexpr int32_t kServeExit = -1;
+
+BBD int32_t ld_acquire_sys(const int32_t *p) { int32_t v; asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+BBD int32_t ld_acquire_gpu(const int32_t *p) { int32_t v; asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+BBD void st_release_gpu(int32_t *p, int32_t v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+BBD void st_release_sys(int32_t *p, int32_t v) { asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+BBD uint64_t global_timer_ns() { uint64_t t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
+constexpr int kServeThreads = 32;
+__global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_constant__ StepParams p, ServeHostCtl *hc, ServeDevCtl *dc,
+                                                                  int32_t startSeq, uint64_t idleTimeoutNs)
+{
+    extern __shared__ float smem[];
+    __shared__ int32_t sSeq;
+    __shared__ StepIo sIo;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int warpsPerBlock = blockDim.x >> 5;
+    float *warpImg = smem + warp * kWorldsPerWarp * kFeatStride;
+    const int64_t numTiles = (p.numWorlds + kWorldsPerWarp - 1) / kWorldsPerWarp;
+    int32_t seq = startSeq;
+    uint64_t tSeen = 0;
+    for (;;) {
+        const int32_t want = seq + 1;
+        if (threadIdx.x == 0) {
+            int32_t got;
+            if (blockIdx.x == 0) {
+                const uint64_t t0 = global_timer_ns();
+                unsigned polls = 0;
+                const unsigned long long tag = (unsigned long long)((unsigned)want & 0xffffu);
+                unsigned long long w0, w1, w2, w3;
+                for (;;) {
+                    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(&hc->word[0]) : "memory");
+                    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(&hc->word[2]) : "memory");
+                    if (w0 == kServeExitWord) { got = kServeExit; break; }
+                    if ((w0 >> 48) == tag && (w1 >> 48) == tag && (w2 >> 48) == tag && (w3 >> 48) == tag) { got = want; break; }
+                    if ((++polls & 31u) == 0 && global_timer_ns() - t0 > idleTimeoutNs) { got = kServeExit; break; }
+                }
+                tSeen = global_timer_ns();
+                asm volatile("fence.acq_rel.sys;" ::: "memory"); /* acquire: the host's action rows precede its doorbell */
+                if (got != kServeExit) {
+                    dc->io.actionSrc = (const int32_t *)(w0 & kServePtrMask); dc->io.rewardOut = (float *)(w1 & kServePtrMask);
+                    dc->io.doneOut = (float *)(w2 & kServePtrMask); dc->io.obsOut = (float *)(w3 & kServePtrMask);
+                    dc->io.actionsVolatile = 0;
+                }
+                st_release_gpu(&dc->seq, got);
+            } else {
+                for (;;) {
+                    got = ld_acquire_gpu(&dc->seq);
+                    if (got == want || got == kServeExit) break;
+                    __nanosleep(20);
+                }
+            }
+            sSeq = got;
+            if (got != kServeExit) {
+                const volatile StepIo *src = &dc->io;
+                sIo.actionSrc = src->actionSrc; sIo.rewardOut = src->rewardOut; sIo.doneOut = src->doneOut;
+                sIo.obsOut = src->obsOut; sIo.actionsVolatile = 0;
+            }
+        }
+        __syncthreads();
+        if (sSeq == kServeExit) break;
+        const StepIo io = sIo;
+        for (int64_t tile = (int64_t)blockIdx.x * warpsPerBlock + warp; tile < numTiles; tile += (int64_t)gridDim.x * warpsPerBlock)
+            step_tile<false>(p, io, warpImg, tile * kWorldsPerWarp, lane);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence(); /* release (gpu scope): this block's writes before the count; the last block's
+                              * system-scope fence below is cumulative over everything it has observed */
+            const unsigned old = atomicAdd(&dc->doneCount, 1u);
+            if (old == gridDim.x - 1) { /* last block of this step */
+                dc->doneCount = 0;      /* nobody touches it again before the host rings the next doorbell */
+                if (blockIdx.x == 0) hc->tSeen = tSeen; /* tuning aid; only block 0 knows it */
+                hc->tDone = global_timer_ns();
+                __threadfence_system();
+                st_release_sys(&hc->complete, want);
+            }
+        }
+        seq = want;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) st_release_sys(&hc->alive, 0);
 }
 
 /* Sim::Sim -> generateWorld (sim.cpp:86-96) for every world + the constant columns. */
@@ -507,8 +674,19 @@ struct bb_engine {
     void *colPtr[26];
     bb::StepParams params;
     cudaStream_t hostStream; /* bb_step_host / setters */
-    int blockThreads, phaseSync;
+    int blockThreads, phaseSync, prefetchBlocks;
     int64_t launches;
+    /* persistent server (bb_serve_*) */
+    bb::ServeHostCtl *serveHost; /* mapped pinned */
+    bb::ServeDevCtl *serveDev;
+    cudaStream_t serveStream;
+    int32_t serveSeq;
+    bool serving;
+    /* device aliases of the pinned buffers seen during this serve session (cudaPointerGetAttributes
+     * costs about a microsecond per pointer; the buffers must stay pinned while the server runs) */
+    const void *aliasHost[64];
+    void *aliasDev[64];
+    int aliasCount;
 };
 
 namespace {
@@ -594,12 +772,15 @@ void pick_launch_shape(int64_t n_worlds, int *threads, int *sync)
 }
 
 int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, float *reward_out = nullptr,
-                float *done_out = nullptr)
+                float *done_out = nullptr, bool host_mapped = false)
 {
     bb::StepParams p = e->params;
-    p.actionSrc = actions_dev;
-    p.rewardOut = reward_out;
-    p.doneOut = done_out;
+    p.io.actionSrc = actions_dev;
+    p.io.rewardOut = reward_out;
+    p.io.doneOut = done_out;
+    p.io.obsOut = nullptr;
+    p.io.actionsVolatile = 0;
+    p.prefetchBlocks = host_mapped ? 0 : e->prefetchBlocks; /* no L2 prefetch of host-mapped rows */
     const int threads = e->blockThreads;
     const int blocks = (int)((e->N * 2 + threads - 1) / threads);
     const int smem = bb::smem_bytes_for(threads);
@@ -649,6 +830,12 @@ bb_engine *bb_create(const bb_config *cfg)
     e->N = cfg->num_worlds;
     e->Npad = (e->N + 31) / 32 * 32;
     e->launches = 0;
+    e->serveHost = nullptr;
+    e->serveDev = nullptr;
+    e->serveStream = nullptr;
+    e->serveSeq = 0;
+    e->serving = false;
+    e->aliasCount = 0;
 
     /* one slab, every column 256-byte aligned */
     size_t offs[26], total = 0;
@@ -686,12 +873,15 @@ bb_engine *bb_create(const bb_config *cfg)
     host_threefry(cfg->rand_seed, 0u, 0u, 0u, key);
     e->params.sc.key0 = key[0];
     e->params.sc.key1 = key[1];
-    e->params.actionSrc = nullptr;
-    e->params.rewardOut = nullptr;
-    e->params.doneOut = nullptr;
+    e->params.io = bb::StepIo{nullptr, nullptr, nullptr, nullptr, 0};
     e->params.numWorlds = e->N;
+    e->params.prefetchBlocks = 0;
 
     pick_launch_shape(e->N, &e->blockThreads, &e->phaseSync);
+    /* L2 prefetch of a later block's rows: measured SLOWER on B200 (2^20 worlds: 340 us -> 380-390 us at
+     * distances of 296..2368 blocks, gpurun exp1), so it is off unless BB_PREFETCH_BLOCKS asks for it. */
+    e->prefetchBlocks = 0;
+    if (const char *s = getenv("BB_PREFETCH_BLOCKS")) e->prefetchBlocks = atoi(s);
     if (bb::smem_bytes_for(512) > 48 * 1024) {
         cudaFuncSetAttribute(bb::bb_step_kernel<512, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::smem_bytes_for(512));
         cudaFuncSetAttribute(bb::bb_step_kernel<512, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::smem_bytes_for(512));
@@ -729,6 +919,10 @@ void bb_destroy(bb_engine *e)
 {
     if (!e) return;
     cudaSetDevice(e->cfg.gpu_id);
+    bb_serve_end(e);
+    if (e->serveStream) cudaStreamDestroy(e->serveStream);
+    if (e->serveHost) cudaFreeHost(e->serveHost);
+    if (e->serveDev) cudaFree(e->serveDev);
     cudaDeviceSynchronize();
     cudaStreamDestroy(e->hostStream);
     cudaFree(e->slab);
@@ -765,11 +959,121 @@ int bb_step_host(bb_engine *e, const int32_t *actions_host, float *reward_host, 
     float *done_dev = (float *)mapped_alias(done_host);
     if (actions_host && !act_dev)
         BB_CUDA_OK(cudaMemcpyAsync(C.action, actions_host, (size_t)e->N * 48, cudaMemcpyHostToDevice, s));
-    if (launch_step(e, act_dev, s, rew_dev, done_dev) != 0) return -1;
+    if (launch_step(e, act_dev, s, rew_dev, done_dev, act_dev != nullptr) != 0) return -1;
     if (reward_host && !rew_dev) BB_CUDA_OK(cudaMemcpyAsync(reward_host, C.reward, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
     if (done_host && !done_dev) BB_CUDA_OK(cudaMemcpyAsync(done_host, C.done, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
     if (obs_host) BB_CUDA_OK(cudaMemcpyAsync(obs_host, C.obs, (size_t)e->N * 1024, cudaMemcpyDeviceToHost, s));
     BB_CUDA_OK(cudaStreamSynchronize(s));
+    return 0;
+}
+
+/* ---- persistent server: host-driven steps without a launch or a stream wait per step ---- */
+
+static int serve_launch(bb_engine *e)
+{
+    const int smem = bb::smem_bytes_for(bb::kServeThreads);
+    int perSm = 0, sms = 0;
+    BB_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, bb::bb_serve_kernel, bb::kServeThreads, smem));
+    BB_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.gpu_id));
+    const int64_t tiles = (e->N + bb::kWorldsPerWarp - 1) / bb::kWorldsPerWarp;
+    int64_t cap = (int64_t)perSm * sms;
+    if (cap > 8 * (int64_t)sms) cap = 8 * (int64_t)sms; /* leave room for other kernels on every SM */
+    const int grid = (int)(tiles < cap ? tiles : cap);
+    if (grid <= 0) { set_error("bb_serve_begin: server kernel cannot be resident"); return -1; }
+    uint64_t idle_ns = 2000000000ull; /* the server leaves after 2 s without a doorbell */
+    if (const char *s = getenv("BB_SERVE_IDLE_MS")) idle_ns = (uint64_t)atoll(s) * 1000000ull;
+    for (int i = 0; i < 4; i++) e->serveHost->word[i] = (unsigned long long)((unsigned)e->serveSeq & 0xffffu) << 48;
+    e->serveHost->complete = e->serveSeq;
+    e->serveHost->alive = 1;
+    BB_CUDA_OK(cudaMemsetAsync(e->serveDev, 0, sizeof(bb::ServeDevCtl), e->serveStream));
+    {
+        const int32_t seq = e->serveSeq; /* dc->seq starts at the last completed sequence */
+        BB_CUDA_OK(cudaMemcpyAsync(&e->serveDev->seq, &seq, sizeof seq, cudaMemcpyHostToDevice, e->serveStream));
+    }
+    bb::StepParams p = e->params;
+    p.prefetchBlocks = 0;
+    bb::ServeHostCtl *hc_dev = nullptr;
+    BB_CUDA_OK(cudaHostGetDevicePointer((void **)&hc_dev, e->serveHost, 0));
+    bb::bb_serve_kernel<<<grid, bb::kServeThreads, smem, e->serveStream>>>(p, hc_dev, e->serveDev, e->serveSeq, idle_ns);
+    e->launches++;
+    BB_CUDA_OK(cudaGetLastError());
+    e->serving = true;
+    return 0;
+}
+
+int bb_serve_begin(bb_engine *e)
+{
+    if (e->serving && e->serveHost->alive) return 0;
+    cudaSetDevice(e->cfg.gpu_id);
+    if (!e->serveStream) BB_CUDA_OK(cudaStreamCreateWithFlags(&e->serveStream, cudaStreamNonBlocking));
+    if (!e->serveHost) {
+        BB_CUDA_OK(cudaHostAlloc((void **)&e->serveHost, sizeof(bb::ServeHostCtl), cudaHostAllocMapped));
+        memset(e->serveHost, 0, sizeof(bb::ServeHostCtl));
+    }
+    if (!e->serveDev) BB_CUDA_OK(cudaMalloc((void **)&e->serveDev, sizeof(bb::ServeDevCtl)));
+    BB_CUDA_OK(cudaDeviceSynchronize()); /* earlier steps / tensor writes on other streams are complete */
+    e->aliasCount = 0;
+    return serve_launch(e);
+}
+
+int bb_serve_step(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host, float *obs_host)
+{
+    if (!e->serving) { set_error("bb_serve_step: call bb_serve_begin first"); return -1; }
+    bb::ServeHostCtl *hc = e->serveHost;
+    if (!__atomic_load_n(&hc->alive, __ATOMIC_ACQUIRE)) { /* idle timeout: the server left; start it again */
+        BB_CUDA_OK(cudaStreamSynchronize(e->serveStream));
+        if (serve_launch(e) != 0) return -1;
+    }
+    auto alias = [e](const void *host) -> void * {
+        if (!host) return nullptr;
+        for (int i = 0; i < e->aliasCount; i++)
+            if (e->aliasHost[i] == host) return e->aliasDev[i];
+        void *dev = mapped_alias(host);
+        if (dev && e->aliasCount < 64) { e->aliasHost[e->aliasCount] = host; e->aliasDev[e->aliasCount++] = dev; }
+        return dev;
+    };
+    const int32_t *act_dev = (const int32_t *)alias(actions_host);
+    float *rew_dev = (float *)alias(reward_host);
+    float *done_dev = (float *)alias(done_host);
+    float *obs_dev = (float *)alias(obs_host);
+    if ((actions_host && !act_dev) || (reward_host && !rew_dev) || (done_host && !done_dev) || (obs_host && !obs_dev)) {
+        set_error("bb_serve_step: buffers must be pinned (page-locked, mapped) host memory");
+        return -1;
+    }
+    const int32_t seq = ++e->serveSeq;
+    e->launches++; /* one pass of the step code over every world, like a launch */
+    const unsigned long long tag = (unsigned long long)((unsigned)seq & 0xffffu) << 48;
+    const void *ptrs[4] = {act_dev, rew_dev, done_dev, obs_dev};
+    for (int i = 0; i < 4; i++) {
+        if ((unsigned long long)(uintptr_t)ptrs[i] & ~bb::kServePtrMask) { set_error("bb_serve_step: buffer alias beyond 48 bits"); return -1; }
+        __atomic_store_n(&hc->word[i], tag | (unsigned long long)(uintptr_t)ptrs[i], __ATOMIC_RELEASE);
+    }
+    /* spin on the completion word the last block writes into this page */
+    uint64_t spins = 0;
+    while (__atomic_load_n(&hc->complete, __ATOMIC_ACQUIRE) != seq) {
+        __builtin_ia32_pause();
+        if ((++spins & 0xfffff) == 0) { /* every ~1M spins: is the server still there? */
+            if (!__atomic_load_n(&hc->alive, __ATOMIC_ACQUIRE) || cudaStreamQuery(e->serveStream) != cudaErrorNotReady) {
+                cudaError_t err = cudaStreamSynchronize(e->serveStream);
+                e->serving = false;
+                set_error(std::string("bb_serve_step: server kernel stopped: ") + cudaGetErrorString(err));
+                return -1;
+            }
+        }
+    }
+    return 0;
+}
+
+/* tuning aid: GPU-side nanoseconds between "doorbell seen" and "last block done" of the last step */
+extern "C" long long bb_serve_last_gpu_ns(bb_engine *e) { return e->serveHost ? (long long)(e->serveHost->tDone - e->serveHost->tSeen) : -1; }
+
+int bb_serve_end(bb_engine *e)
+{
+    if (!e || !e->serving) return 0;
+    __atomic_store_n(&e->serveHost->word[0], bb::kServeExitWord, __ATOMIC_RELEASE);
+    cudaError_t err = cudaStreamSynchronize(e->serveStream);
+    e->serving = false;
+    if (err != cudaSuccess) { set_error(std::string("bb_serve_end: ") + cudaGetErrorString(err)); return -1; }
     return 0;
 }
 

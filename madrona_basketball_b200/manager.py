@@ -92,6 +92,7 @@ class SimpleGridworldSimulator:
         self.num_worlds = int(num_worlds)
         self.gpu_id = max(int(gpu_id), 0)
         self._tensors: Dict[int, Tensor] = {}
+        self._host_ptrs: Dict[int, tuple] = {}
 
     # ------------------------------------------------------------------ lifetime
     def close(self) -> None:
@@ -127,14 +128,38 @@ class SimpleGridworldSimulator:
     def step_host(self, actions: Optional[np.ndarray], reward: Optional[np.ndarray] = None,
                   done: Optional[np.ndarray] = None, obs: Optional[np.ndarray] = None) -> None:
         """Extension: host-buffer step (H2D actions, step, D2H results), synchronous."""
-        def ptr(a, dtype, n):
-            if a is None:
-                return None
-            assert a.dtype == dtype and a.flags["C_CONTIGUOUS"] and a.size == n, (a.dtype, a.shape)
-            return a.ctypes.data
-        n = self.num_worlds
+        n, ptr = self.num_worlds, self._host_ptr
         self._check(self._lib.bb_step_host(self._h, ptr(actions, np.int32, n * 12), ptr(reward, np.float32, n * 2),
                                            ptr(done, np.float32, n * 2), ptr(obs, np.float32, n * 256)), "bb_step_host")
+
+    def serve_begin(self) -> None:
+        """Extension: start the persistent server kernel (bb_serve_begin)."""
+        self._check(self._lib.bb_serve_begin(self._h), "bb_serve_begin")
+
+    def _host_ptr(self, a: Optional[np.ndarray], dtype, n: int):
+        """Address of a host buffer, validated once per array object (the per-step path is latency-bound)."""
+        if a is None:
+            return None
+        hit = self._host_ptrs.get(id(a))
+        if hit is not None and hit[0] is a:
+            return hit[1]
+        assert a.dtype == dtype and a.flags["C_CONTIGUOUS"] and a.size == n, (a.dtype, a.shape)
+        if len(self._host_ptrs) >= 256:
+            self._host_ptrs.clear()
+        self._host_ptrs[id(a)] = (a, a.ctypes.data)   # holds a reference: the id cannot be recycled
+        return self._host_ptrs[id(a)][1]
+
+    def serve_step(self, actions: np.ndarray, reward: Optional[np.ndarray] = None,
+                   done: Optional[np.ndarray] = None, obs: Optional[np.ndarray] = None) -> None:
+        """Extension: one host-buffer step through the persistent server (pinned buffers only)."""
+        n = self.num_worlds
+        rc = self._lib.bb_serve_step(self._h, self._host_ptr(actions, np.int32, n * 12), self._host_ptr(reward, np.float32, n * 2),
+                                     self._host_ptr(done, np.float32, n * 2), self._host_ptr(obs, np.float32, n * 256))
+        if rc != 0:
+            self._check(rc, "bb_serve_step")
+
+    def serve_end(self) -> None:
+        self._check(self._lib.bb_serve_end(self._h), "bb_serve_end")
 
     def set_action(self, world_idx: int, agent_idx: int, move_speed: int, move_angle: int, rotate: int,
                    grab: int, pass_: int = 0, shoot: int = 0, **kw) -> None:

@@ -205,3 +205,67 @@ def test_world_partition_invariance():
         if col in ids:  # entity ids are instance-local (as in the reference): compare the id-free columns
             continue
         assert np.array_equal(sf[col][k:k + m].view(np.int32), sp[col].view(np.int32)), col
+
+
+@pytest.mark.parametrize("n", [1, 50, 300, 8192, 40000])
+def test_persistent_server_steps_match_launch_per_step(n):
+    """bb_serve_*: the resident kernel fed through the host doorbell evolves the worlds exactly like
+    bb_step launches, mirrors reward / done / observations into pinned host memory, survives its own
+    idle exit, and leaves the device columns consistent for ordinary steps afterwards."""
+    import time
+
+    import torch
+
+    a, b = make_engine(n), make_engine(n)
+    act = torch.empty((n, 2, 6), dtype=torch.int32, device="cuda")
+    hact = torch.empty((n, 2, 6), dtype=torch.int32).pin_memory()
+    hrew = torch.empty((n, 2)).pin_memory(); hdone = torch.empty((n, 2)).pin_memory()
+    hobs = torch.empty((n, 2, 128)).pin_memory() if n <= 8192 else None
+    b.serve_begin()
+    steps = 60 if n <= 8192 else 12
+    for s in range(steps):
+        a.fill_actions(SEED, s, out=act); a.step_with_actions(act)
+        torch.cuda.current_stream().synchronize()
+        hact.copy_(act)
+        b.serve_step(hact.numpy(), hrew.numpy(), hdone.numpy(), hobs.numpy() if hobs is not None else None)
+        assert np.array_equal(hrew.numpy().view(np.int32), a.reward_tensor().to_torch().cpu().numpy().view(np.int32)), s
+        assert np.array_equal(hdone.numpy(), a.done_tensor().to_torch().cpu().numpy()), s
+        if hobs is not None and s % 7 == 0:
+            assert np.array_equal(hobs.numpy().view(np.int32), a.observations_tensor().to_torch().cpu().numpy().view(np.int32)), s
+    b.serve_end()
+    torch.cuda.synchronize()
+    assert_states_equal(engine_state(b), engine_state(a), f"server N={n}")
+    # ordinary launches continue from the served state
+    a.fill_actions(SEED, 99, out=act); a.step_with_actions(act); b.step_with_actions(act)
+    torch.cuda.synchronize()
+    assert_states_equal(engine_state(b), engine_state(a), f"after server N={n}")
+
+
+def test_persistent_server_idle_exit_and_restart(monkeypatch):
+    import time
+
+    import torch
+
+    monkeypatch.setenv("BB_SERVE_IDLE_MS", "50")
+    n = 64
+    a, b = make_engine(n), make_engine(n)
+    act = torch.empty((n, 2, 6), dtype=torch.int32, device="cuda")
+    hact = torch.empty((n, 2, 6), dtype=torch.int32).pin_memory()
+    hrew = torch.empty((n, 2)).pin_memory(); hdone = torch.empty((n, 2)).pin_memory()
+    b.serve_begin()
+    for s in range(6):
+        a.fill_actions(SEED, s, out=act); a.step_with_actions(act)
+        torch.cuda.current_stream().synchronize()
+        hact.copy_(act)
+        if s == 3:
+            time.sleep(0.3)                 # the server leaves after 50 ms without a doorbell ...
+            torch.cuda.synchronize()        # ... so a device-wide sync returns
+        b.serve_step(hact.numpy(), hrew.numpy(), hdone.numpy())   # ... and the next step restarts it
+        assert np.array_equal(hrew.numpy().view(np.int32), a.reward_tensor().to_torch().cpu().numpy().view(np.int32)), s
+    b.serve_end()
+    with pytest.raises(RuntimeError, match="pinned"):
+        b.serve_begin()
+        try:
+            b.serve_step(np.zeros((n, 2, 6), np.int32))
+        finally:
+            b.serve_end()

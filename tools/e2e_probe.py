@@ -17,12 +17,12 @@ uact = dact.cpu().numpy().copy(); urew = np.empty((n, 2), np.float32); udone = n
 stream = torch.cuda.current_stream().cuda_stream
 R = 2000
 
-def loop(name, fn):
+def loop(name, fn, sync=True):
     for _ in range(50): fn()
-    torch.cuda.synchronize()
+    if sync: torch.cuda.synchronize()
     t = time.perf_counter()
     for _ in range(R): fn()
-    torch.cuda.synchronize()
+    if sync: torch.cuda.synchronize()
     print(f"{name:55s} {(time.perf_counter() - t) / R * 1e6:7.2f} us/step")
 
 def dev_async(): lib.bb_step_with_actions(h, dact.data_ptr(), stream)
@@ -39,3 +39,18 @@ ua, ur, ud = uact.ctypes.data, urew.ctypes.data, udone.ctypes.data
 loop("bb_step_host pageable (staged copies)", lambda: lib.bb_step_host(h, ua, ur, ud, None))
 na, nr, nd = pact.numpy(), prew.numpy(), pdone.numpy()
 loop("sim.step_host(numpy pinned) python wrapper", lambda: sim.step_host(na, nr, nd))
+
+lib.bb_serve_begin(h)
+loop("bb_serve_step pinned (persistent server)", lambda: lib.bb_serve_step(h, pa, pr, pd, None), sync=False)
+loop("bb_serve_step actions only", lambda: lib.bb_serve_step(h, pa, None, None, None), sync=False)
+loop("bb_serve_step nothing (doorbell + step + completion)", lambda: lib.bb_serve_step(h, None, None, None, None), sync=False)
+lib.bb_serve_last_gpu_ns.restype = ctypes.c_longlong; lib.bb_serve_last_gpu_ns.argtypes = [ctypes.c_void_p]
+acc = []
+for _ in range(200):
+    lib.bb_serve_step(h, pa, pr, pd, None); acc.append(lib.bb_serve_last_gpu_ns(h))
+print("GPU-side doorbell-seen -> last-block-done, pinned io: avg %.2f us min %.2f" % (sum(acc) / len(acc) / 1e3, min(acc) / 1e3))
+acc = []
+for _ in range(200):
+    lib.bb_serve_step(h, None, None, None, None); acc.append(lib.bb_serve_last_gpu_ns(h))
+print("GPU-side doorbell-seen -> last-block-done, no host io: avg %.2f us min %.2f" % (sum(acc) / len(acc) / 1e3, min(acc) / 1e3))
+lib.bb_serve_end(h)
