@@ -269,3 +269,44 @@ def test_persistent_server_idle_exit_and_restart(monkeypatch):
             b.serve_step(np.zeros((n, 2, 6), np.int32))
         finally:
             b.serve_end()
+
+
+def test_full_size_65536_worlds_checksums():
+    """BASELINE.json configs[2] size (65 536 worlds, here on one GPU): engine vs oracle per-world checksums."""
+    import torch
+
+    n = 65536
+    sim, orc = make_engine(n), make_oracle(n)
+    for s in range(150):
+        sim.fill_actions(SEED, s)
+        sim.step()
+    orc.run_synthetic(SEED, 0, 150, 0, 16)
+    ce = sim.checksum().cpu().numpy().view(np.uint64)
+    assert np.array_equal(ce, orc.checksum())
+    assert orc.tensor("rng_count").max() > 3          # resets happened
+
+
+def test_full_size_million_world_stress_checksum_of_checksums():
+    """BASELINE.json configs[4] (2^20 worlds, forced collisions -> a reset every second step), one GPU:
+    per-world checksums against the oracle, plus size-independent properties."""
+    import torch
+
+    n = 1 << 20
+    sim, orc = make_engine(n), make_oracle(n)
+    pe = sim.agent_pos_tensor().to_torch()
+    po = orc.tensor("agent_pos")
+    off_e, off_o = pe.new_tensor([0.05, 0.0, 0.0]), np.array([0.05, 0.0, 0.0], np.float32)
+    for s in range(8):
+        sim.fill_actions(SEED, s); orc.fill_actions(SEED, s)
+        pe[:, 1] = pe[:, 0] + off_e
+        po[:, 1] = po[:, 0] + off_o
+        sim.step(); orc.step(16)
+    ce = sim.checksum().cpu().numpy().view(np.uint64)
+    co = orc.checksum()
+    assert np.array_equal(ce, co)
+    rc = sim.tensor("rng_count").to_torch()
+    assert int(rc.min()) >= 3 + 3 * 4                             # every world reset on every second step (shots add draws)
+    obs = sim.observations_tensor().to_torch()
+    assert torch.isfinite(obs).all() and not obs[:, :, 103:].any()
+    done = sim.done_tensor().to_torch()
+    assert ((done == 0) | (done == 1)).all()
