@@ -118,6 +118,8 @@ int bb_serve_begin(bb_engine *e);
 int bb_serve_step(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host,
                   float *obs_host);
 int bb_serve_end(bb_engine *e);
+/* Tuning aid: GPU-side nanoseconds between "doorbell seen" and "last block done" of the last served step. */
+long long bb_serve_last_gpu_ns(bb_engine *e);
 
 /* Manager::*Tensor() (mgr.cpp:317-445) / Impl::exportTensor (mgr.cpp:121-126):
  * device pointer + declared dtype/shape of a column.  The engine owns the memory

@@ -11,6 +11,8 @@ SOURCES = [os.path.join(_HERE, "csrc", "bb_engine.cu")]
 DEPS = SOURCES + [
     os.path.join(_HERE, "csrc", "bb_world.cuh"),
     os.path.join(_HERE, "csrc", "bb_pair.cuh"),
+    os.path.join(_HERE, "csrc", "bb_rollout.cuh"),
+    os.path.join(_HERE, "..", "include", "bb_rollout.h"),
     os.path.join(_HERE, "..", "include", "bb_math.h"),
     os.path.join(_HERE, "..", "include", "bb_engine.h"),
 ]

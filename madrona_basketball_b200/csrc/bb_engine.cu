@@ -650,6 +650,8 @@ __global__ void bb_checksum_kernel(const __grid_constant__ ChecksumParams cp, in
 
 } // namespace bb
 
+#include "bb_rollout.cuh"
+
 /* ================================ host side ================================ */
 
 static thread_local std::string g_last_error;
@@ -1065,7 +1067,7 @@ int bb_serve_step(bb_engine *e, const int32_t *actions_host, float *reward_host,
 }
 
 /* tuning aid: GPU-side nanoseconds between "doorbell seen" and "last block done" of the last step */
-extern "C" long long bb_serve_last_gpu_ns(bb_engine *e) { return e->serveHost ? (long long)(e->serveHost->tDone - e->serveHost->tSeen) : -1; }
+long long bb_serve_last_gpu_ns(bb_engine *e) { return e->serveHost ? (long long)(e->serveHost->tDone - e->serveHost->tSeen) : -1; }
 
 int bb_serve_end(bb_engine *e)
 {
@@ -1166,5 +1168,107 @@ int bb_math_eval(int fn, const float *x_dev, const float *y_dev, float *out_dev,
 
 int64_t bb_launch_count(const bb_engine *e) { return e->launches; }
 int64_t bb_num_worlds(const bb_engine *e) { return e->N; }
+
+/* ---- fused rollout path (include/bb_rollout.h) ---- */
+
+static int policy_ok(const bb_policy *p, const char *who)
+{
+    if (!p || p->hidden < 1 || p->hidden > BB_POLICY_MAX_HIDDEN) { set_error(std::string(who) + ": policy.hidden must be 1..32"); return -1; }
+    if (((uintptr_t)p->w1 & 15) != 0) { set_error(std::string(who) + ": policy.w1 must be 16-byte aligned"); return -1; }
+    return 0;
+}
+
+static int launch_policy(const bb_policy *pol, const bb::PolicyIo &io, cudaStream_t stream)
+{
+    if (io.n <= 0) return 0;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int64_t blocks = (io.n + bb::kPolWarps - 1) / bb::kPolWarps;
+    if (blocks > 2 * (int64_t)sms) blocks = 2 * (int64_t)sms; /* 2 resident blocks / SM; rows are strided over the warps */
+    bb::bb_policy_kernel<<<(int)blocks, bb::kPolThreads, 0, stream>>>(*pol, io);
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int bb_policy_forward(const bb_policy *pol, const float *obs, int64_t obs_stride, int64_t n, int stochastic, uint32_t seed,
+                      uint32_t draw, int64_t row_offset, int32_t *actions_out, int64_t action_stride, float *logp_out,
+                      float *value_out, float *logits_out, void *cuda_stream)
+{
+    if (policy_ok(pol, "bb_policy_forward") != 0) return -1;
+    bb::PolicyIo io{};
+    io.obs = obs; io.obsStride = obs_stride; io.n = n; io.rowOffset = row_offset;
+    io.stochastic = stochastic; io.seed = seed; io.draw = draw;
+    io.actionsOut = actions_out; io.actionStride = action_stride;
+    io.logpOut = logp_out; io.valueOut = value_out; io.logitsOut = logits_out;
+    return launch_policy(pol, io, (cudaStream_t)cuda_stream);
+}
+
+int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, const bb_rollout_buffers *buf, int32_t agent_idx,
+               uint32_t seed, uint32_t draw_base, int64_t world_offset, void *cuda_stream)
+{
+    if (policy_ok(trainee, "bb_rollout") != 0) return -1;
+    if (frozen && policy_ok(frozen, "bb_rollout(frozen)") != 0) return -1;
+    if (!buf || buf->horizon < 1 || agent_idx < 0 || agent_idx > 1) { set_error("bb_rollout: bad buffers / agent_idx"); return -1; }
+    if (e->serving) { set_error("bb_rollout: the persistent server is running (bb_serve_end first)"); return -1; }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const bb::Columns &C = e->params.col;
+    const int64_t n = e->N;
+    const int T = buf->horizon;
+    /* env.reset(), env.py:178-185 */
+    bb::bb_reset_prologue_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(C.reset, C.action, n, agent_idx);
+    e->launches++;
+    BB_CUDA_OK(cudaGetLastError());
+    if (launch_step(e, nullptr, st) != 0) return -1;
+    for (int t = 0; t <= T; t++) {
+        bb::PolicyIo io{};
+        io.obs = C.obs + agent_idx * BB_OBS_DIM; io.obsStride = 2 * BB_OBS_DIM; io.n = n; io.rowOffset = world_offset;
+        io.stochastic = 1; io.seed = seed; io.draw = draw_base + (uint32_t)t;
+        io.evaluateOnly = (t == T);
+        if (t < T) {
+            io.actionsOut = C.action + agent_idx * 6; io.actionStride = 12;
+            io.logpOut = buf->log_probs + (int64_t)t * n;
+            io.valueOut = buf->values + (int64_t)t * n;
+            io.bufObs = buf->obs + (int64_t)t * n * BB_OBS_DIM;
+            io.bufActions = buf->actions + (int64_t)t * n * BB_NUM_ACTION_DIMS;
+        } else {
+            io.nextValue = buf->next_value;
+        }
+        if (t > 0) { /* reward / done of step t-1 are in the columns now */
+            io.rew = C.reward + agent_idx; io.done = C.done + agent_idx; io.rdStride = 2;
+            io.bufRewPrev = buf->rewards + (int64_t)(t - 1) * n;
+            io.bufNotDonePrev = buf->not_dones + (int64_t)(t - 1) * n;
+            io.curReward = buf->cur_reward; io.epLength = buf->ep_length; io.epSums = buf->ep_sums;
+        } else {
+            io.resetCol = C.reset; /* env.py:182 resets.fill_(0) */
+        }
+        if (launch_policy(trainee, io, st) != 0) return -1;
+        e->launches++;
+        if (t == T) break;
+        if (frozen) { /* env.py:126-143: the frozen policy drives the other agent from its own observation row */
+            bb::PolicyIo fo{};
+            const int other = 1 - agent_idx;
+            fo.obs = C.obs + other * BB_OBS_DIM; fo.obsStride = 2 * BB_OBS_DIM; fo.n = n; fo.rowOffset = world_offset;
+            fo.stochastic = 1; fo.seed = seed; fo.draw = 0x80000000u + draw_base + (uint32_t)t;
+            fo.actionsOut = C.action + other * 6; fo.actionStride = 12;
+            if (launch_policy(frozen, fo, st) != 0) return -1;
+            e->launches++;
+        }
+        if (launch_step(e, nullptr, st) != 0) return -1;
+    }
+    return 0;
+}
+
+int bb_gae(const bb_rollout_buffers *buf, int64_t n, double gamma, double gae_lambda, const double *value_mean,
+           const double *value_var, float value_clamp, float *values_unnorm_out, float *advantages_out, float *returns_out,
+           void *cuda_stream)
+{
+    if (!buf || buf->horizon < 1 || n <= 0 || !advantages_out || !returns_out) { set_error("bb_gae: bad arguments"); return -1; }
+    bb::bb_gae_kernel<<<(int)((n + 127) / 128), 128, 0, (cudaStream_t)cuda_stream>>>(
+        buf->values, buf->next_value, buf->rewards, buf->not_dones, buf->horizon, n, (float)gamma, (float)(gamma * gae_lambda),
+        value_mean, value_var, value_clamp, values_unnorm_out, advantages_out, returns_out);
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
 
 } // extern "C"

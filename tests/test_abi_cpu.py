@@ -11,8 +11,8 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def _declared_symbols():
-    text = open(os.path.join(ROOT, "include", "bb_engine.h")).read()
+def _declared_symbols(header="bb_engine.h"):
+    text = open(os.path.join(ROOT, "include", header)).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     return sorted(set(re.findall(r"\b(bb_[a-z_0-9]+)\s*\(", text)))
 
@@ -33,6 +33,10 @@ def test_library_exports_every_declared_symbol(lib):
     for sym in declared:
         assert hasattr(lib, sym), f"libbball.so lacks {sym}"
     assert sorted(_lib.SYMBOLS) == declared   # the ctypes table covers the whole header
+    rollout = _declared_symbols("bb_rollout.h")
+    assert rollout == ["bb_gae", "bb_policy_forward", "bb_rollout"]
+    for sym in rollout:
+        assert hasattr(lib, sym), f"libbball.so lacks {sym}"
 
 
 def test_library_is_sm100a_native_code():
