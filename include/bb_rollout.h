@@ -47,9 +47,10 @@ typedef struct bb_policy {
 
 /* One Agent.forward over n observation rows (agent.py:134-154).
  *   obs            f32, row r at obs + r * obs_stride (obs_stride = 256 for the view observations[:, agent_idx])
- *   stochastic     1: sample each bucket by inverse CDF with the uniform Threefry2x32((seed, row_offset + r),
- *                     (draw, bucket)) >> 8 * 2^-24  (action.py:30-33 draws with torch.multinomial; the torch RNG
- *                     stream is not reproducible outside torch, the distribution is the same);
+ *   stochastic     1: sample each bucket by inverse CDF; Threefry2x32(key (seed, row_offset + r), counter (draw, c)),
+ *                     c = 0..2, gives the 32-bit words of buckets 2c and 2c+1, u = (word >> 8) * 2^-24
+ *                     (action.py:30-33 draws with torch.multinomial; the torch RNG stream is not reproducible
+ *                     outside torch, the distribution is the same);
  *                  0: argmax per bucket (action.py:21-23)
  *   actions_out    i32, 6 per row at actions_out + r * action_stride (may be NULL); pointing it at
  *                  Action column + agent_idx * 6 with stride 12 is `actions[:, agent_idx] = a` (env.py:147)

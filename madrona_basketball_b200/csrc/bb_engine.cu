@@ -1184,8 +1184,8 @@ static int launch_policy(const bb_policy *pol, const bb::PolicyIo &io, cudaStrea
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    int64_t blocks = (io.n + bb::kPolWarps - 1) / bb::kPolWarps;
-    if (blocks > 2 * (int64_t)sms) blocks = 2 * (int64_t)sms; /* 2 resident blocks / SM; rows are strided over the warps */
+    int64_t blocks = (io.n + bb::kRowsPerBlock - 1) / bb::kRowsPerBlock;
+    if (blocks > 4 * (int64_t)sms) blocks = 4 * (int64_t)sms; /* rows are strided over the resident blocks */
     bb::bb_policy_kernel<<<(int)blocks, bb::kPolThreads, 0, stream>>>(*pol, io);
     BB_CUDA_OK(cudaGetLastError());
     return 0;

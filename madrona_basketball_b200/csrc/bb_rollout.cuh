@@ -5,13 +5,9 @@
  * Reference semantics: scripts/agent.py:108-154 (Agent), scripts/action.py (bucketed categoricals),
  * scripts/ppo.py:60-166 (rollout, compute_advantages), scripts/buffers.py, scripts/ppo_stats.py:21-36.
  *
- * bb_policy_kernel: one WARP per observation row, lane j = hidden channel j (the reference's
- * num_channels is 32 = one warp).  Lane j keeps row j of W1 (128 floats) and of W2 (32) in
- * registers for the whole kernel, so layer 1 is 128 FMAs per row against a broadcast read of the
- * normalised observation from shared memory; LayerNorm statistics are warp-shuffle reductions;
- * the two heads read a transposed [32][20] copy of (actor | critic) from shared memory; lanes 0..5
- * each own one action bucket for the softmax / inverse-CDF sampling.  fp32 FFMA throughout: the
- * contraction is 5.7 kFLOP per row — at 8192 rows a few microseconds on the CUDA cores — and
+ * bb_policy_kernel: four threads per observation row against broadcast 16-byte reads of the weights in
+ * shared memory (see the kernel).  fp32 FFMA throughout: the contraction is 5.7 kFLOP per row - at 8192
+ * rows a few microseconds on the CUDA cores - and
  * agreement with the torch fp32 reference to ~1e-6 matters more here than tensor-core peak.
  */
 #pragma once
@@ -19,8 +15,7 @@
 
 namespace bb {
 
-constexpr int kPolThreads = 128;
-constexpr int kPolWarps = kPolThreads / 32;
+constexpr int kPolThreads = 256;
 constexpr int kHeads = BB_NUM_LOGITS + 1; /* 19 logits + value */
 
 struct PolicyIo {
@@ -42,152 +37,216 @@ struct PolicyIo {
     float *nextValue;
 };
 
-__device__ __constant__ int kBucketOff[BB_NUM_ACTION_DIMS] = {0, 2, 10, 13, 15, 17}; /* env.py:102 */
-__device__ __constant__ int kBucketCnt[BB_NUM_ACTION_DIMS] = {2, 8, 3, 2, 2, 2};
+/* ------------------------------------------------------------------------------------------------
+ * Four threads ("quad") per observation row; thread q of the quad owns hidden channels q, q+4, .., q+28
+ * (and head outputs q, q+4, .., q+16).  The weights stay in torch's [out][in] layout in shared memory
+ * (rows padded by 4 floats): a thread reads its channel's weights for four consecutive inputs as one
+ * 16-byte load - the same address for every row of the block (broadcast), bank-disjoint across the
+ * four q - so each shared load feeds four FMAs and nothing is transposed.  LayerNorm statistics are
+ * two xor-shuffles inside the quad; the hidden vector passes through a private shared row; the six
+ * softmax buckets are spread over the quad.  At 8192 rows that is 1024 warps of ~3 k instructions
+ * (history: warp-per-row 40 us, thread-per-row 29 us at 8192 rows - too few, too long warps).
+ * ------------------------------------------------------------------------------------------------ */
+constexpr int kH = BB_POLICY_MAX_HIDDEN;
+constexpr int kCh = kH / 4;                 /* channels per thread */
+constexpr int kRowsPerBlock = kPolThreads / 4;
+constexpr int kW1Stride = BB_OBS_DIM + 4;   /* 132: rows q, q+1, .. land 4 banks apart */
+constexpr int kW2Stride = kH + 4;           /* 36 */
+constexpr int kHeadPerThread = kHeads / 4;  /* 5 */
 
-BBD float warp_sum(float v)
+struct __align__(16) PolicySmem {
+    float w1[kH][kW1Stride];
+    float w2[kH][kW2Stride];
+    float wh[kHeads][kW2Stride];            /* rows 0..18 actor, row 19 critic */
+    float hid[kRowsPerBlock][kW2Stride];    /* a row's hidden vector (private to its quad) */
+    float out[kRowsPerBlock][kHeads + 4];   /* a row's 19 logits + value */
+    float mean[BB_OBS_DIM], inv[BB_OBS_DIM];
+    float b1[kH], g1[kH], e1[kH], b2[kH], g2[kH], e2[kH], bh[kHeads];
+};
+
+BBD float quad_sum(float v)
 {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
     return v;
 }
 
-/* nn.LayerNorm(H) + ReLU on the value each lane < H holds (biased variance, eps 1e-5) */
-BBD float layer_norm_relu(float v, bool active, int H, float g, float b)
+/* nn.LayerNorm(H) + ReLU over the quad's 32 channels (thread q holds channels 4c + q); biased variance, eps 1e-5 */
+BBD void layer_norm_relu(float (&v)[kCh], int q, int H, const float *g, const float *b)
 {
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < kCh; c++) s += v[c]; /* channels >= H hold 0 */
     const float inv = 1.f / (float)H;
-    const float mean = warp_sum(active ? v : 0.f) * inv;
-    const float d = active ? v - mean : 0.f;
-    const float var = warp_sum(d * d) * inv;
-    const float y = d * rsqrtf(var + 1e-5f) * g + b;
-    return active ? fmaxf(y, 0.f) : 0.f;
+    const float mean = quad_sum(s) * inv;
+    s = 0.f;
+#pragma unroll
+    for (int c = 0; c < kCh; c++) {
+        v[c] = (4 * c + q < H) ? v[c] - mean : 0.f;
+        s = fmaf(v[c], v[c], s);
+    }
+    const float rstd = rsqrtf(quad_sum(s) * inv + 1e-5f);
+#pragma unroll
+    for (int c = 0; c < kCh; c++) v[c] = (4 * c + q < H) ? fmaxf(fmaf(v[c] * rstd, g[4 * c + q], b[4 * c + q]), 0.f) : 0.f;
 }
 
-__global__ void __launch_bounds__(kPolThreads, 2) bb_policy_kernel(const bb_policy P, const PolicyIo io)
+/* the buckets [2,8,3,2,2,2] (env.py:102) spread over the quad: q0 {0,2}, q1 {1}, q2 {3,4}, q3 {5} */
+__device__ __constant__ int kBucketOff[BB_NUM_ACTION_DIMS] = {0, 2, 10, 13, 15, 17};
+__device__ __constant__ int kBucketCnt[BB_NUM_ACTION_DIMS] = {2, 8, 3, 2, 2, 2};
+__device__ __constant__ int kQuadBuckets[4][2] = {{0, 2}, {1, -1}, {3, 4}, {5, -1}};
+
+__global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy P, const PolicyIo io)
 {
-    __shared__ float sMean[BB_OBS_DIM], sInv[BB_OBS_DIM];
-    __shared__ float sHeadT[BB_POLICY_MAX_HIDDEN][kHeads]; /* [k][j]: j < 19 actor rows, j == 19 critic */
-    __shared__ float sHeadB[kHeads];
-    __shared__ __align__(16) float sX[kPolWarps][BB_OBS_DIM];
-    __shared__ float sH[kPolWarps][BB_POLICY_MAX_HIDDEN];
-    __shared__ float sL[kPolWarps][kHeads];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ PolicySmem S;
     const int H = P.hidden;
-    const bool active = lane < H;
-
-    for (int i = threadIdx.x; i < BB_OBS_DIM; i += kPolThreads) { sMean[i] = P.obs_mean[i]; sInv[i] = P.obs_inv_std[i]; }
-    for (int i = threadIdx.x; i < BB_POLICY_MAX_HIDDEN * kHeads; i += kPolThreads) {
-        const int k = i / kHeads, j = i % kHeads;
-        float w = 0.f;
-        if (k < H) w = (j < BB_NUM_LOGITS) ? P.wa[j * H + k] : P.wc[k];
-        sHeadT[k][j] = w;
-    }
-    if (threadIdx.x < kHeads) sHeadB[threadIdx.x] = threadIdx.x < BB_NUM_LOGITS ? P.ba[threadIdx.x] : P.bc[0];
-
-    /* this lane's rows of W1 / W2 and its per-channel vectors, register-resident */
-    float w1[BB_OBS_DIM], w2[BB_POLICY_MAX_HIDDEN];
+    const int tid = threadIdx.x, q = tid & 3, rb = tid >> 2, lane = tid & 31;
+    /* ---- weights -> shared memory in their own layout (coalesced 16-byte reads); padded tails are zero ---- */
 #pragma unroll
-    for (int k = 0; k < BB_OBS_DIM; k += 4) {
-        float4 v = active ? *reinterpret_cast<const float4 *>(P.w1 + (int64_t)lane * BB_OBS_DIM + k) : make_float4(0.f, 0.f, 0.f, 0.f);
-        w1[k] = v.x; w1[k + 1] = v.y; w1[k + 2] = v.z; w1[k + 3] = v.w;
+    for (int i = tid; i < kH * (BB_OBS_DIM / 4); i += kPolThreads) {
+        const int j = i / (BB_OBS_DIM / 4), k4 = i % (BB_OBS_DIM / 4);
+        const float4 v = j < H ? *reinterpret_cast<const float4 *>(P.w1 + j * BB_OBS_DIM + k4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4 *>(&S.w1[j][k4 * 4]) = v;
     }
 #pragma unroll
-    for (int k = 0; k < BB_POLICY_MAX_HIDDEN; k++) w2[k] = (active && k < H) ? P.w2[lane * H + k] : 0.f;
-    const float b1 = active ? P.b1[lane] : 0.f, g1 = active ? P.ln1_g[lane] : 0.f, e1 = active ? P.ln1_b[lane] : 0.f;
-    const float b2 = active ? P.b2[lane] : 0.f, g2 = active ? P.ln2_g[lane] : 0.f, e2 = active ? P.ln2_b[lane] : 0.f;
+    for (int i = tid; i < kH * kH; i += kPolThreads) {
+        const int j = i / kH, k = i % kH;
+        S.w2[j][k] = (j < H && k < H) ? P.w2[j * H + k] : 0.f;
+    }
+    for (int i = tid; i < kHeads * kH; i += kPolThreads) {
+        const int j = i / kH, k = i % kH;
+        S.wh[j][k] = k < H ? (j < BB_NUM_LOGITS ? P.wa[j * H + k] : P.wc[k]) : 0.f;
+    }
+    if (tid < BB_OBS_DIM) { S.mean[tid] = P.obs_mean[tid]; S.inv[tid] = P.obs_inv_std[tid]; }
+    if (tid >= 128 && tid < 128 + kH) {
+        const int j = tid - 128;
+        const bool a = j < H;
+        S.b1[j] = a ? P.b1[j] : 0.f; S.g1[j] = a ? P.ln1_g[j] : 0.f; S.e1[j] = a ? P.ln1_b[j] : 0.f;
+        S.b2[j] = a ? P.b2[j] : 0.f; S.g2[j] = a ? P.ln2_g[j] : 0.f; S.e2[j] = a ? P.ln2_b[j] : 0.f;
+    }
+    if (tid >= 192 && tid < 192 + kHeads) S.bh[tid - 192] = (tid - 192) < BB_NUM_LOGITS ? P.ba[tid - 192] : P.bc[0];
     __syncthreads();
 
-    const int64_t warpsTotal = (int64_t)gridDim.x * kPolWarps;
-    for (int64_t r = (int64_t)blockIdx.x * kPolWarps + warp; r < io.n; r += warpsTotal) {
-        /* ---- observation row: raw copy into the rollout buffer, normalise (agent.py:27-39) ---- */
-        const float *orow = io.obs + r * io.obsStride;
+    const int64_t rowStride = (int64_t)gridDim.x * kRowsPerBlock;
+    for (int64_t rw0 = (int64_t)blockIdx.x * kRowsPerBlock + (rb & ~7); rw0 < io.n; rw0 += rowStride) { /* warp-uniform trip count */
+        const int64_t rr = rw0 + (rb & 7);
+        const bool valid = rr < io.n;
+        const int64_t r = valid ? rr : io.n - 1; /* tail quads shadow the last row and never store */
+        /* ---- backbone.0: observation normaliser (agent.py:27-39) fused into Linear(128,H) ---- */
+        const float4 *orow = reinterpret_cast<const float4 *>(io.obs + r * io.obsStride);
+        float4 *brow = (io.bufObs && valid) ? reinterpret_cast<float4 *>(io.bufObs + r * BB_OBS_DIM) : nullptr;
+        float acc[kCh];
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int k = lane + 32 * i;
-            const float x = orow[k];
-            if (io.bufObs) io.bufObs[r * BB_OBS_DIM + k] = x;
-            float xn = (x - sMean[k]) * sInv[k];
-            if (P.obs_clamp > 0.f) xn = fminf(fmaxf(xn, -P.obs_clamp), P.obs_clamp);
-            sX[warp][k] = xn;
-        }
-        __syncwarp();
-        /* ---- backbone.0-2: Linear(128,H) + LayerNorm + ReLU ---- */
-        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        for (int c = 0; c < kCh; c++) acc[c] = S.b1[4 * c + q];
+        float4 xq = orow[0];
+#pragma unroll 2
+        for (int k4 = 0; k4 < BB_OBS_DIM / 4; k4++) {
+            const float4 x = xq;
+            if (k4 + 1 < BB_OBS_DIM / 4) xq = orow[k4 + 1]; /* next quad of inputs in flight while this one is used */
+            if (brow && (k4 & 3) == q) brow[k4] = x;         /* buffer.obs[step] = obs (ppo.py:128), one store per chunk */
+            const float4 mu = *reinterpret_cast<const float4 *>(&S.mean[k4 * 4]);
+            const float4 is = *reinterpret_cast<const float4 *>(&S.inv[k4 * 4]);
+            float x0 = (x.x - mu.x) * is.x, x1 = (x.y - mu.y) * is.y, x2 = (x.z - mu.z) * is.z, x3 = (x.w - mu.w) * is.w;
+            if (P.obs_clamp > 0.f) {
+                x0 = fminf(fmaxf(x0, -P.obs_clamp), P.obs_clamp); x1 = fminf(fmaxf(x1, -P.obs_clamp), P.obs_clamp);
+                x2 = fminf(fmaxf(x2, -P.obs_clamp), P.obs_clamp); x3 = fminf(fmaxf(x3, -P.obs_clamp), P.obs_clamp);
+            }
 #pragma unroll
-        for (int k = 0; k < BB_OBS_DIM; k += 4) {
-            const float4 x = *reinterpret_cast<const float4 *>(&sX[warp][k]);
-            a0 = fmaf(w1[k], x.x, a0); a1 = fmaf(w1[k + 1], x.y, a1);
-            a2 = fmaf(w1[k + 2], x.z, a2); a3 = fmaf(w1[k + 3], x.w, a3);
+            for (int c = 0; c < kCh; c++) {
+                const float4 w = *reinterpret_cast<const float4 *>(&S.w1[4 * c + q][k4 * 4]);
+                acc[c] = fmaf(w.w, x3, fmaf(w.z, x2, fmaf(w.y, x1, fmaf(w.x, x0, acc[c]))));
+            }
         }
-        float h = layer_norm_relu(((a0 + a1) + (a2 + a3)) + b1, active, H, g1, e1);
-        sH[warp][lane] = h;
+        layer_norm_relu(acc, q, H, S.g1, S.e1);              /* backbone.1-2 */
+#pragma unroll
+        for (int c = 0; c < kCh; c++) S.hid[rb][4 * c + q] = acc[c];
         __syncwarp();
         /* ---- backbone.3-5: Linear(H,H) + LayerNorm + ReLU ---- */
-        a0 = a1 = 0.f;
 #pragma unroll
-        for (int k = 0; k < BB_POLICY_MAX_HIDDEN; k += 2) {
-            a0 = fmaf(w2[k], sH[warp][k], a0);
-            a1 = fmaf(w2[k + 1], sH[warp][k + 1], a1);
-        }
-        __syncwarp();
-        h = layer_norm_relu((a0 + a1) + b2, active, H, g2, e2);
-        sH[warp][lane] = h;
-        __syncwarp();
-        /* ---- heads: lanes 0..18 actor logits, lane 19 critic ---- */
-        float out = 0.f;
-        if (lane < kHeads) {
-            a0 = a1 = 0.f;
+        for (int c = 0; c < kCh; c++) acc[c] = S.b2[4 * c + q];
 #pragma unroll
-            for (int k = 0; k < BB_POLICY_MAX_HIDDEN; k += 2) {
-                a0 = fmaf(sHeadT[k][lane], sH[warp][k], a0);
-                a1 = fmaf(sHeadT[k + 1][lane], sH[warp][k + 1], a1);
+        for (int k4 = 0; k4 < kH / 4; k4++) {
+            const float4 h = *reinterpret_cast<const float4 *>(&S.hid[rb][k4 * 4]);
+#pragma unroll
+            for (int c = 0; c < kCh; c++) {
+                const float4 w = *reinterpret_cast<const float4 *>(&S.w2[4 * c + q][k4 * 4]);
+                acc[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, acc[c]))));
             }
-            out = (a0 + a1) + sHeadB[lane];
-            sL[warp][lane] = out;
-            if (io.logitsOut && lane < BB_NUM_LOGITS) io.logitsOut[r * BB_NUM_LOGITS + lane] = out;
+        }
+        layer_norm_relu(acc, q, H, S.g2, S.e2);
+        __syncwarp(); /* every read of the first hidden vector is done */
+#pragma unroll
+        for (int c = 0; c < kCh; c++) S.hid[rb][4 * c + q] = acc[c];
+        __syncwarp();
+        /* ---- heads: outputs q, q+4, .., q+16 of (19 actor logits | critic) ---- */
+        float o[kHeadPerThread];
+#pragma unroll
+        for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
+#pragma unroll
+        for (int k4 = 0; k4 < kH / 4; k4++) {
+            const float4 h = *reinterpret_cast<const float4 *>(&S.hid[rb][k4 * 4]);
+#pragma unroll
+            for (int c = 0; c < kHeadPerThread; c++) {
+                const float4 w = *reinterpret_cast<const float4 *>(&S.wh[4 * c + q][k4 * 4]);
+                o[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, o[c]))));
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < kHeadPerThread; c++) {
+            const int j = 4 * c + q;
+            S.out[rb][j] = o[c];
+            if (io.logitsOut && valid && j < BB_NUM_LOGITS) io.logitsOut[r * BB_NUM_LOGITS + j] = o[c];
+        }
+        if (q == 3 && valid) { /* output 19 = critic */
+            if (io.evaluateOnly) { if (io.nextValue) io.nextValue[r] = o[kHeadPerThread - 1]; }
+            else if (io.valueOut) io.valueOut[r] = o[kHeadPerThread - 1];
         }
         __syncwarp();
-        if (lane == BB_NUM_LOGITS) {
-            if (io.evaluateOnly) { if (io.nextValue) io.nextValue[r] = out; }
-            else if (io.valueOut) io.valueOut[r] = out;
-        }
-        /* ---- bucketed categoricals (action.py:5-33): lane b owns bucket b ---- */
-        float logp = 0.f;
-        if (!io.evaluateOnly && lane < BB_NUM_ACTION_DIMS) {
-            const int off = kBucketOff[lane], cnt = kBucketCnt[lane];
-            const float *l = &sL[warp][off];
-            float m = l[0];
-            for (int i = 1; i < cnt; i++) m = fmaxf(m, l[i]);
-            float s = 0.f;
-            for (int i = 0; i < cnt; i++) s += expf(l[i] - m);
-            const float lse = m + logf(s);
-            int a = 0;
-            if (io.stochastic) {
-                uint32_t x0, x1;
-                threefry2x32(io.seed, (uint32_t)(io.rowOffset + r), io.draw, (uint32_t)lane, x0, x1);
-                const float u = (float)((x0 ^ x1) >> 8) * 0x1p-24f;
-                float c = 0.f;
-                a = cnt - 1;
-                for (int i = 0; i < cnt; i++) {
-                    c += expf(l[i] - lse);
-                    if (u < c) { a = i; break; }
-                }
-            } else {
-                for (int i = 1; i < cnt; i++) if (l[i] > l[a]) a = i;
-            }
-            logp = l[a] - lse;
-            if (io.actionsOut) io.actionsOut[r * io.actionStride + lane] = a;
-            if (io.bufActions) io.bufActions[r * BB_NUM_ACTION_DIMS + lane] = (float)a;
-        }
         if (!io.evaluateOnly) {
-            /* log_probs.sum(dim=-1), agent.py:152: fixed order bucket 0..5 */
-            float tot = 0.f;
+            /* ---- bucketed categoricals (action.py:5-33): this thread's one or two buckets ---- */
+            float lp[2] = {0.f, 0.f};
 #pragma unroll
-            for (int b = 0; b < BB_NUM_ACTION_DIMS; b++) tot += __shfl_sync(0xffffffffu, logp, b);
-            if (lane == 0 && io.logpOut) io.logpOut[r] = tot;
+            for (int s2 = 0; s2 < 2; s2++) {
+                const int b = kQuadBuckets[q][s2];
+                if (b < 0) continue;
+                const int off = kBucketOff[b], cnt = kBucketCnt[b];
+                const float *l = &S.out[rb][off];
+                float m = l[0];
+                for (int i = 1; i < cnt; i++) m = fmaxf(m, l[i]);
+                float s = 0.f;
+                for (int i = 0; i < cnt; i++) s += expf(l[i] - m);
+                const float lse = m + logf(s);
+                int a = 0;
+                if (io.stochastic) { /* inverse CDF: smallest a with u * s < e_0 + .. + e_a; word (b & 1) of Threefry call b >> 1 */
+                    uint32_t x0, x1;
+                    threefry2x32(io.seed, (uint32_t)(io.rowOffset + r), io.draw, (uint32_t)(b >> 1), x0, x1);
+                    const float us = ((float)(((b & 1) ? x1 : x0) >> 8) * 0x1p-24f) * s;
+                    float c = 0.f;
+                    a = cnt - 1;
+                    for (int i = 0; i < cnt; i++) {
+                        c += expf(l[i] - m);
+                        if (us < c) { a = i; break; }
+                    }
+                } else {
+                    for (int i = 1; i < cnt; i++) if (l[i] > l[a]) a = i;
+                }
+                lp[s2] = l[a] - lse;
+                if (valid) {
+                    if (io.actionsOut) io.actionsOut[r * io.actionStride + b] = a;
+                    if (io.bufActions) io.bufActions[r * BB_NUM_ACTION_DIMS + b] = (float)a;
+                }
+            }
+            /* log_probs.sum(dim=-1), agent.py:152, in bucket order 0..5: owners q0.a, q1.a, q0.b, q2.a, q2.b, q3.a */
+            const int qb = lane & ~3;
+            float tot = __shfl_sync(0xffffffffu, lp[0], qb);
+            tot += __shfl_sync(0xffffffffu, lp[0], qb + 1);
+            tot += __shfl_sync(0xffffffffu, lp[1], qb);
+            tot += __shfl_sync(0xffffffffu, lp[0], qb + 2);
+            tot += __shfl_sync(0xffffffffu, lp[1], qb + 2);
+            tot += __shfl_sync(0xffffffffu, lp[0], qb + 3);
+            if (q == 0 && valid && io.logpOut) io.logpOut[r] = tot;
         }
         /* ---- bookkeeping of the previous step (ppo.py:84-85,128-134; ppo_stats.py:21-36) ---- */
-        if (lane == 0 && io.bufRewPrev) {
+        if (q == 1 && valid && io.bufRewPrev) {
             const float rw = io.rew[r * io.rdStride], dn = io.done[r * io.rdStride];
             io.bufRewPrev[r] = rw;
             io.bufNotDonePrev[r] = 1.0f - dn;
@@ -202,8 +261,8 @@ __global__ void __launch_bounds__(kPolThreads, 2) bb_policy_kernel(const bb_poli
                 io.epLength[r] = el * (1.f - dn);
             }
         }
-        if (lane < 2 && io.resetCol) io.resetCol[r * 2 + lane] = 0;
-        __syncwarp();
+        if (q == 2 && valid && io.resetCol) *reinterpret_cast<int2 *>(io.resetCol + r * 2) = make_int2(0, 0);
+        __syncwarp(); /* S.hid / S.out of this quad are rewritten by the next row */
     }
 }
 

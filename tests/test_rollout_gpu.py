@@ -14,12 +14,14 @@ OFF = np.concatenate([[0], np.cumsum(ACTION_BUCKETS)[:-1]])
 
 
 def _uniforms(seed, rows, draw):
-    """The sampler's uniforms: Threefry2x32(key = (seed, row), counter = (draw, bucket)), (x0 ^ x1) >> 8 * 2^-24."""
+    """The sampler's uniforms: Threefry2x32(key = (seed, row), counter = (draw, c)) for c = 0..2 gives the
+    words of buckets 2c (x0) and 2c+1 (x1); u = (word >> 8) * 2^-24."""
     u = np.empty((len(rows), 6), np.float32)
     for i, r in enumerate(rows):
-        for b in range(6):
-            x0, x1 = oracle.threefry2x32(seed, int(r), draw, b)
-            u[i, b] = np.float32(((x0 ^ x1) >> 8) * 2.0 ** -24)
+        for c in range(3):
+            x0, x1 = oracle.threefry2x32(seed, int(r), draw, c)
+            u[i, 2 * c] = np.float32((x0 >> 8) * 2.0 ** -24)
+            u[i, 2 * c + 1] = np.float32((x1 >> 8) * 2.0 ** -24)
     return u
 
 
