@@ -231,3 +231,44 @@ def test_gae_kernel_matches_ppo_loop():
     assert torch.allclose(buf.values_unnorm, values, rtol=1e-6, atol=1e-6)
     assert torch.allclose(buf.advantages, adv, rtol=1e-5, atol=1e-4)
     assert torch.allclose(buf.returns, ret, rtol=1e-5, atol=1e-4)
+
+
+def test_ppo_iterations_train_end_to_end():
+    """Config 4 in miniature: fused rollout + GAE + torch PPO update (ppo_dist, single process) for a few
+    iterations: finite losses, parameters move, the kernels see the updated weights without copies."""
+    import torch
+
+    from madrona_basketball_b200 import ppo_dist
+    from madrona_basketball_b200.policy_torch import Agent
+    from madrona_basketball_b200.rollout import FusedRollout, PolicyWeights, RolloutBuffers, policy_forward
+
+    torch.manual_seed(0)
+    n, T = 512, 16
+    dev = torch.device("cuda")
+    sim = make_engine(n)
+    agent = Agent().to(dev)
+    cfg = ppo_dist.PPOConfig(num_minibatches=2, update_epochs=2)
+    opt = torch.optim.Adam(agent.parameters(), lr=1e-3, eps=1e-8)
+    w = PolicyWeights.from_module(agent)
+    buf = RolloutBuffers(T, n, dev)
+    roll = FusedRollout(sim, w, 1, seed=9)
+    w0 = agent.backbone[0].weight.detach().clone()
+    for it in range(3):
+        agent.eval()
+        roll.collect(buf)
+        roll.gae(buf, cfg.gamma, cfg.gae_lambda, agent.value_norm.mean, agent.value_norm.var)
+        ppo_dist.finish_advantages(agent, buf)
+        w.refresh()
+        assert abs(float(buf.advantages.mean())) < 1e-4 and abs(float(buf.advantages.std()) - 1.0) < 1e-3
+        agent.train()
+        losses = ppo_dist.update_policy(agent, opt, buf, cfg)
+        assert all(torch.isfinite(v) for v in losses.values())
+    assert not torch.equal(w0, agent.backbone[0].weight)
+    assert float(agent.obs_norm.count) == 1.0 + 3 * n * T
+    # zero-copy: the kernel reads the live (updated) parameters and the refreshed normaliser
+    obs = sim.observations_tensor().to_torch()[:, 1]
+    _, _, v_kernel, logits = policy_forward(w, obs, stochastic=False, want_logits=True)
+    with torch.no_grad():
+        x = agent.backbone(agent.obs_norm(obs))
+        assert torch.allclose(logits, agent.actor(x), rtol=1e-5, atol=2e-5)
+        assert torch.allclose(v_kernel, agent.critic(x).squeeze(-1), rtol=1e-5, atol=2e-5)
