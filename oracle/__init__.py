@@ -80,6 +80,27 @@ def _load(libm: bool) -> ctypes.CDLL:
     return lib
 
 
+def rotate_vec(q, v) -> np.ndarray:
+    """Quat{w,x,y,z}.rotateVec(v) of the oracle's Madrona primitive restatement (float32)."""
+    qa = np.ascontiguousarray(q, dtype=np.float32)
+    va = np.ascontiguousarray(v, dtype=np.float32)
+    out = np.empty(3, np.float32)
+    lib = _load(False)
+    lib.orc_rotate_vec.argtypes = [ctypes.c_void_p] * 3
+    lib.orc_rotate_vec(qa.ctypes.data, va.ctypes.data, out.ctypes.data)
+    return out
+
+
+def court_constants() -> Dict[str, float]:
+    out = np.empty(12, np.float32)
+    lib = _load(False)
+    lib.orc_court_constants.argtypes = [ctypes.c_void_p]
+    lib.orc_court_constants(out.ctypes.data)
+    names = ["COURT_LENGTH_M", "COURT_WIDTH_M", "WORLD_WIDTH_M", "WORLD_HEIGHT_M", "COURT_MIN_X", "COURT_MAX_X", "COURT_MIN_Y",
+             "COURT_MAX_Y", "HOOP_FROM_BASELINE_M", "ARC_RADIUS_M", "CORNER_3_FROM_SIDELINE_M", "CORNER_3_LENGTH_FROM_BASELINE_M"]
+    return {k: float(v) for k, v in zip(names, out)}
+
+
 MATH_FNS = {"sinf": 0, "cosf": 1, "atanf": 2, "atan2f": 3, "acosf": 4, "expf": 5, "erff": 6}
 
 

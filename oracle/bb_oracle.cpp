@@ -1527,6 +1527,21 @@ float orc_rng_uniform(uint32_t seed, uint32_t draw_index)
     return rng.sampleUniform();
 }
 
+/* Quat::rotateVec (madrona_prims.h) and the compile-time court constants (constants.hpp:67-93), for the
+ * fixtures derived from the reference's own Python (scripts/viewer.py:59-65 rotate_vec, src/constants.py). */
+void orc_rotate_vec(const float q[4], const float v[3], float out[3])
+{
+    Vector3 r = Quat{q[0], q[1], q[2], q[3]}.rotateVec(Vector3{v[0], v[1], v[2]});
+    out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+
+void orc_court_constants(float out[12])
+{
+    const float c[12] = {COURT_LENGTH_M, COURT_WIDTH_M, WORLD_WIDTH_M, WORLD_HEIGHT_M, COURT_MIN_X, COURT_MAX_X, COURT_MIN_Y,
+                         COURT_MAX_Y, HOOP_FROM_BASELINE_M, ARC_RADIUS_M, CORNER_3_FROM_SIDELINE_M, CORNER_3_LENGTH_FROM_BASELINE_M};
+    for (int i = 0; i < 12; i++) out[i] = c[i];
+}
+
 /* fn: 0 sinf, 1 cosf, 2 atanf, 3 atan2f(x, y), 4 acosf, 5 expf, 6 erff -- whichever arithmetic this
  * build uses (include/bb_math.h spec, or glibc with -DBB_USE_LIBM). */
 void orc_math_eval(int fn, const float *x, const float *y, float *out, int64_t n)

@@ -84,6 +84,9 @@ void orc_checksum(orc_sim *sim, uint64_t *out_per_world);
 /* Known-answer hooks for tests. */
 void orc_threefry2x32(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t out[2]);
 float orc_rng_uniform(uint32_t seed, uint32_t draw_index);
+void orc_rotate_vec(const float q[4], const float v[3], float out[3]);   /* Quat{w,x,y,z}.rotateVec(v) */
+void orc_court_constants(float out[12]); /* COURT_LENGTH, COURT_WIDTH, WORLD_W, WORLD_H, MIN_X, MAX_X, MIN_Y, MAX_Y,
+                                            HOOP_FROM_BASELINE, ARC_RADIUS, CORNER_3_FROM_SIDELINE, CORNER_3_LENGTH */
 /* Elementwise libm call sites of SURVEY App. E in this build's arithmetic.
  * fn: 0 sinf, 1 cosf, 2 atanf, 3 atan2f(x, y), 4 acosf, 5 expf, 6 erff. */
 void orc_math_eval(int fn, const float *x, const float *y, float *out, int64_t n);

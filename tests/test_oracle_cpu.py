@@ -301,3 +301,22 @@ def test_libm_build_agrees_on_discrete_state_for_a_while():
         assert np.array_equal(a.tensor(k), b.tensor(k)), k
     for k in ["agent_pos", "basketball_pos", "orientation", "agent_velocity"]:
         assert np.allclose(a.tensor(k), b.tensor(k), rtol=1e-5, atol=1e-6), k
+
+
+# ---------------------------------------------------------------- vectors generated by the reference's own Python
+def test_oracle_against_reference_python_fixtures():
+    """tools/make_golden_ref.py ran the reference's scripts/viewer.py `rotate_vec` (its Python mirror of Madrona's
+    Quat::rotateVec) and read src/constants.py; the oracle's primitive / constants must agree.  This is the one
+    piece of the Madrona boundary the reference itself pins."""
+    g = gold("reference_python.npz")
+    q, v, want = g["rotate_q"], g["rotate_v"], g["rotate_out"]
+    for i in range(len(q)):
+        got = oracle.rotate_vec(q[i], v[i])
+        scale = max(1.0, float(np.abs(want[i]).max()), float(np.dot(q[i], q[i])) * float(np.abs(v[i]).max()))
+        assert np.allclose(got, want[i], rtol=0, atol=4e-6 * scale), (i, got, want[i])   # float32 vs the float64 formula
+    assert np.allclose(oracle.rotate_vec([1, 0, 0, 0], [0, 1, 0]), [0, 1, 0])
+    c = oracle.court_constants()
+    for name, val in zip(g["const_names"], g["const_values"]):
+        assert abs(c[str(name)] - float(val)) <= 1e-6 * max(1.0, abs(float(val))), (name, c[str(name)], val)
+    assert int(g["scalar_NUM_AGENTS"]) == 2 and int(g["scalar_NUM_HOOPS"]) == 2 and float(g["scalar_SIMULATION_HZ"]) == 62.0
+    assert abs(float(g["scalar_AGENT_SHOULDER_WIDTH"]) - 0.429) < 1e-12 and float(g["scalar_HOOP_SCORE_ZONE_SIZE"]) == 0.1
