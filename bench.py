@@ -171,7 +171,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -372,13 +372,32 @@ def run_engine(args):
                               "what": "same K steps replayed as one CUDA graph, no L2 flush (informational)"},
             "wall_s_timed_region": wall,
         }
-        print(json.dumps(line))
+        emit(line)
     if world_size > 1:
         dist.destroy_process_group()
     return 0
 
 
+def _claim_stdout():
+    """stdout carries exactly ONE JSON line: libraries that write to fd 1 on their own (NCCL prints its
+    version banner there) are sent to stderr; emit() writes to the saved descriptor."""
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+_JSON_OUT = None
+
+
+def emit(line: dict) -> None:
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
