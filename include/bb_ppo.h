@@ -1,0 +1,84 @@
+/*
+ * bb_ppo.h — C ABI of the fused PPO update (libbball.so): the caller on the far side of the
+ * rollout path, scripts/ppo.py `update_policy` (ppo.py:180-216).
+ *
+ * The reference runs each of its 16 minibatch steps per iteration (4 epochs x 4 minibatches of
+ * 65 536 rows at the ppo.py defaults) as ~200 small torch kernels: Agent.get_stats
+ * (agent.py:171-178) forward, the clipped-PPO loss (ppo.py:192-208), autograd backward,
+ * clip_grad_norm_ and Adam (ppo.py:210-214).  After the rollout fusion (bb_rollout.h) that
+ * update is 96 % of a PPO iteration.  Here a minibatch step is three kernels:
+ *
+ *   bb_ppo_grad   forward + loss + backward of the 5 972-parameter policy over the minibatch rows
+ *                 (gathered through the permutation), per-block partial gradients, then a
+ *                 fixed-order reduction -> one flat gradient.  Deterministic (no atomics).
+ *   (optional)    one flat all-reduce of that gradient across ranks (torch.distributed / NCCL).
+ *   bb_ppo_adam   global-norm clip (nn.utils.clip_grad_norm_) + torch.optim.Adam step on the flat
+ *                 parameter vector.
+ *
+ * Plain pointers and sizes only; all pointers are DEVICE pointers.
+ */
+#ifndef BB_PPO_H
+#define BB_PPO_H
+
+#include <stdint.h>
+#include "bb_rollout.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Flat parameter / gradient layout for Agent(num_channels = 32, num_layers = 2): the order of
+ * `agent.parameters()` (agent.py:111-127), each tensor row-major as torch stores it. */
+#define BB_PPO_HIDDEN 32
+#define BB_PPO_OFF_W1 0        /* backbone.0.weight [32,128] */
+#define BB_PPO_OFF_B1 4096     /* backbone.0.bias   [32]     */
+#define BB_PPO_OFF_G1 4128     /* backbone.1.weight [32]  (LayerNorm gamma) */
+#define BB_PPO_OFF_E1 4160     /* backbone.1.bias   [32]  (LayerNorm beta)  */
+#define BB_PPO_OFF_W2 4192     /* backbone.3.weight [32,32]  */
+#define BB_PPO_OFF_B2 5216     /* backbone.3.bias   [32]     */
+#define BB_PPO_OFF_G2 5248     /* backbone.4.weight [32]     */
+#define BB_PPO_OFF_E2 5280     /* backbone.4.bias   [32]     */
+#define BB_PPO_OFF_WA 5312     /* actor.weight      [19,32]  */
+#define BB_PPO_OFF_BA 5920     /* actor.bias        [19]     */
+#define BB_PPO_OFF_WC 5939     /* critic.weight     [1,32]   */
+#define BB_PPO_OFF_BC 5971     /* critic.bias       [1]      */
+#define BB_PPO_NUM_PARAMS 5972
+#define BB_PPO_NUM_STATS 4     /* sums over the minibatch rows: pg loss, value loss (x0.5 max), entropy, clipped-ratio count */
+
+/* One minibatch of scripts/buffers.py RolloutBuffer.get_minibatch (flattened [T*N, ...] float32). */
+typedef struct bb_ppo_batch {
+    const float *obs;         /* [R,128]  raw observations (normalised inside, agent.py:27-39) */
+    const float *actions;     /* [R,6]    float, as the reference buffer stores them */
+    const float *log_probs;   /* [R]      behaviour log-prob (ppo.py:189 `lp`) */
+    const float *values;      /* [R]      behaviour value   (ppo.py:189 `v`)  */
+    const float *advantages;  /* [R]      normalised advantages (ppo.py:173-174) */
+    const float *returns;     /* [R]      normalised returns    (ppo.py:176) */
+    const int64_t *indices;   /* [m]      rows of this minibatch (torch.randperm slice, ppo.py:186-188); NULL = 0..m-1 */
+    int64_t num_rows;         /* m */
+    float clip_coef;          /* ppo.py:48  0.2  */
+    float ent_coef;           /* ppo.py:49  0.01 */
+    float vf_coef;            /* ppo.py:50  1.0  */
+} bb_ppo_batch;
+
+/* Bytes of scratch `bb_ppo_grad` needs on the current device (per-block partial gradients). */
+int64_t bb_ppo_workspace_bytes(void);
+
+/* loss = pg_loss + vf_coef * c_loss + ent_coef * entropy_loss (ppo.py:192-208) over the minibatch,
+ * means over its m rows; grad_out[BB_PPO_NUM_PARAMS] = d loss / d parameters in the flat layout
+ * above (what loss.backward() leaves in .grad); stats_out[BB_PPO_NUM_STATS] (may be NULL) = sums
+ * over rows of: max(surr1, surr2); 0.5 * max(vf, vf_clipped); entropy; [ratio outside the clip]. */
+int bb_ppo_grad(const bb_policy *pol, const bb_ppo_batch *batch, void *workspace, float *grad_out, float *stats_out,
+                void *cuda_stream);
+
+/* nn.utils.clip_grad_norm_(params, max_grad_norm) followed by torch.optim.Adam.step() (no weight
+ * decay, no amsgrad) on flat vectors of n floats.  grad is first multiplied by grad_scale (1 / world
+ * size after a summing all-reduce).  step_dev: int32 step counter on the device, incremented here.
+ * grad_norm_out (may be NULL): the total norm before clipping. */
+int bb_ppo_adam(float *params, const float *grad, float *exp_avg, float *exp_avg_sq, int32_t *step_dev, int64_t n,
+                float grad_scale, float max_grad_norm, float lr, float beta1, float beta2, float eps,
+                float *grad_norm_out, void *cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BB_PPO_H */

@@ -651,6 +651,7 @@ __global__ void bb_checksum_kernel(const __grid_constant__ ChecksumParams cp, in
 } // namespace bb
 
 #include "bb_rollout.cuh"
+#include "bb_ppo.cuh"
 
 /* ================================ host side ================================ */
 
@@ -1267,6 +1268,64 @@ int bb_gae(const bb_rollout_buffers *buf, int64_t n, double gamma, double gae_la
     bb::bb_gae_kernel<<<(int)((n + 127) / 128), 128, 0, (cudaStream_t)cuda_stream>>>(
         buf->values, buf->next_value, buf->rewards, buf->not_dones, buf->horizon, n, (float)gamma, (float)(gamma * gae_lambda),
         value_mean, value_var, value_clamp, values_unnorm_out, advantages_out, returns_out);
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+/* ---- fused PPO update (include/bb_ppo.h) ---- */
+
+static int ppo_grid(int *blocks_out)
+{
+    int dev = 0, sms = 148;
+    BB_CUDA_OK(cudaGetDevice(&dev));
+    BB_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    *blocks_out = 2 * sms; /* __launch_bounds__(256, 2): every block resident, tiles strided over them */
+    return 0;
+}
+
+int64_t bb_ppo_workspace_bytes(void)
+{
+    int blocks = 0;
+    if (ppo_grid(&blocks) != 0) return -1;
+    return (int64_t)blocks * bb::kPpoPartial * (int64_t)sizeof(float);
+}
+
+int bb_ppo_grad(const bb_policy *pol, const bb_ppo_batch *batch, void *workspace, float *grad_out, float *stats_out,
+                void *cuda_stream)
+{
+    if (!pol || pol->hidden != BB_PPO_HIDDEN) { set_error("bb_ppo_grad: policy.hidden must be 32 (Agent(num_channels=32, num_layers=2))"); return -1; }
+    if (((uintptr_t)pol->w1 & 15) != 0) { set_error("bb_ppo_grad: policy.w1 must be 16-byte aligned"); return -1; }
+    if (!batch || batch->num_rows <= 0 || !batch->obs || !batch->actions || !batch->log_probs || !batch->values ||
+        !batch->advantages || !batch->returns || !workspace || !grad_out) { set_error("bb_ppo_grad: bad arguments"); return -1; }
+    if (((uintptr_t)batch->obs & 15) != 0 || ((uintptr_t)workspace & 15) != 0) { set_error("bb_ppo_grad: obs / workspace must be 16-byte aligned"); return -1; }
+    static bool attrSet = false;
+    if (!attrSet) {
+        BB_CUDA_OK(cudaFuncSetAttribute(bb::bb_ppo_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(bb::PpoSmem)));
+        attrSet = true;
+    }
+    int maxBlocks = 0;
+    if (ppo_grid(&maxBlocks) != 0) return -1;
+    bb::PpoArgs a{};
+    a.b = *batch;
+    a.invM = 1.0f / (float)batch->num_rows;
+    a.numTiles = (batch->num_rows + bb::kPpoRows - 1) / bb::kPpoRows;
+    a.partials = (float *)workspace;
+    const int blocks = (int)(a.numTiles < maxBlocks ? a.numTiles : maxBlocks);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    bb::bb_ppo_grad_kernel<<<blocks, bb::kPpoThreads, sizeof(bb::PpoSmem), st>>>(*pol, a);
+    BB_CUDA_OK(cudaGetLastError());
+    bb::bb_ppo_reduce_kernel<<<(bb::kPpoPartial + 127) / 128, 128, 0, st>>>(a.partials, blocks, grad_out, stats_out);
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int bb_ppo_adam(float *params, const float *grad, float *exp_avg, float *exp_avg_sq, int32_t *step_dev, int64_t n,
+                float grad_scale, float max_grad_norm, float lr, float beta1, float beta2, float eps, float *grad_norm_out,
+                void *cuda_stream)
+{
+    if (!params || !grad || !exp_avg || !exp_avg_sq || !step_dev || n <= 0) { set_error("bb_ppo_adam: bad arguments"); return -1; }
+    bb::bb_ppo_adam_kernel<<<1, bb::kAdamThreads, 0, (cudaStream_t)cuda_stream>>>(params, grad, exp_avg, exp_avg_sq, step_dev, n, grad_scale,
+                                                                                 max_grad_norm, lr, beta1, beta2, eps, grad_norm_out);
     BB_CUDA_OK(cudaGetLastError());
     return 0;
 }

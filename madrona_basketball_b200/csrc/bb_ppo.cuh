@@ -1,0 +1,475 @@
+/*
+ * bb_ppo.cuh — fused PPO minibatch step (include/bb_ppo.h): forward + clipped-PPO loss + backward of
+ * scripts/agent.py Agent(num_channels = 32, num_layers = 2), gradient reduction, grad-norm clip + Adam.
+ *
+ * Reference semantics: scripts/ppo.py:180-216 (update_policy), scripts/agent.py:171-178 (get_stats),
+ * scripts/action.py (bucketed categoricals: log-prob of the taken action and entropy per bucket).
+ * In the reference this is ~200 small torch kernels per minibatch step (3.4 ms at 65 536 rows, launch
+ * bound); here the whole network fits one kernel: 5 972 parameters live in shared memory, a row's
+ * activations in registers / a private shared row, and the weight gradients are accumulated in registers
+ * across the block's row tiles.
+ *
+ * bb_ppo_grad_kernel (256 threads, tiles of 64 rows, persistent grid of 2 blocks per SM):
+ *   row phase   four threads ("quad") per row, thread q owns hidden channels q, q+4, .., q+28, exactly
+ *               the mapping of bb_policy_kernel: broadcast 16-byte reads of the weights in torch's own
+ *               [out][in] layout.  Forward keeps xhat / rstd of both LayerNorms in registers; the loss
+ *               seeds d logits / d value; backward goes through transposed copies of the head and
+ *               second-layer weights, and leaves X, A1, A2, dH1, dH2, dZ of the tile in shared memory.
+ *   tile phase  the weight gradients are three small GEMMs over the tile's 64 rows (dW1 = dH1^T X,
+ *               dW2 = dH2^T A1, dWh = dZ^T A2), each thread owning a register patch of the output.
+ *   epilogue    every block writes its partial gradient (all 5 972 + 4 entries) to the workspace;
+ *               bb_ppo_reduce_kernel adds the partials in block order.  No atomics: bitwise reproducible.
+ * fp32 FFMA: 26 kFLOP per row, 1.7 GFLOP per minibatch of 65 536 rows; agreement with torch autograd
+ * (fp32) is the parity bar, so no reduced-precision tensor-core path.
+ */
+#pragma once
+#include "../../include/bb_ppo.h"
+
+namespace bb {
+
+constexpr int kPpoThreads = 256;
+constexpr int kPpoRows = kPpoThreads / 4;   /* rows per tile */
+constexpr int kPpoPartial = BB_PPO_NUM_PARAMS + BB_PPO_NUM_STATS; /* floats per block partial */
+constexpr int kXS = BB_OBS_DIM + 4;         /* 132 */
+constexpr int kHS = kH + 4;                 /* 36  */
+constexpr int kZS = 24;                     /* 20 head outputs, padded to 6 float4 */
+
+struct __align__(16) PpoSmem {
+    float w1[kH][kXS];
+    float w2[kH][kHS];
+    float w2t[kH][kHS];        /* w2t[k][j] = w2[j][k] */
+    float wh[kHeads][kHS];     /* rows 0..18 actor, row 19 critic */
+    float wht[kH][kZS];        /* wht[k][j] = wh[j][k] */
+    float x[kPpoRows][kXS];    /* normalised observations of the tile */
+    float a1[kPpoRows][kHS];
+    float a2[kPpoRows][kHS];
+    float dh1[kPpoRows][kHS];
+    float dh2[kPpoRows][kHS];
+    float z[kPpoRows][kZS];    /* head outputs, then their gradients */
+    float mean[BB_OBS_DIM], inv[BB_OBS_DIM];
+    float b1[kH], g1[kH], e1[kH], b2[kH], g2[kH], e2[kH], bh[kZS];
+    float red[8][4];           /* loss statistics, one row per warp */
+};
+
+struct PpoArgs {
+    bb_ppo_batch b;
+    float invM;
+    int64_t numTiles;
+    float *partials;
+};
+
+/* LayerNorm(32) forward over the quad: leaves xhat in v, returns rstd */
+BBD float ppo_ln_fwd(float (&v)[kCh])
+{
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < kCh; c++) s += v[c];
+    const float mean = quad_sum(s) * (1.f / kH);
+    s = 0.f;
+#pragma unroll
+    for (int c = 0; c < kCh; c++) { v[c] -= mean; s = fmaf(v[c], v[c], s); }
+    const float rstd = rsqrtf(quad_sum(s) * (1.f / kH) + 1e-5f);
+#pragma unroll
+    for (int c = 0; c < kCh; c++) v[c] *= rstd;
+    return rstd;
+}
+
+/* LayerNorm backward: d (in: dL/dy, out: dL/dh), xhat, gamma of the thread's channels; accumulates dgamma / dbeta */
+BBD void ppo_ln_bwd(float (&d)[kCh], const float (&xhat)[kCh], float rstd, const float *g, int q, float (&dg)[kCh], float (&de)[kCh])
+{
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int c = 0; c < kCh; c++) {
+        dg[c] = fmaf(d[c], xhat[c], dg[c]);
+        de[c] += d[c];
+        d[c] *= g[4 * c + q];
+        s1 += d[c];
+        s2 = fmaf(d[c], xhat[c], s2);
+    }
+    s1 = quad_sum(s1) * (1.f / kH);
+    s2 = quad_sum(s2) * (1.f / kH);
+#pragma unroll
+    for (int c = 0; c < kCh; c++) d[c] = rstd * (d[c] - s1 - xhat[c] * s2);
+}
+
+__global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_policy P, const PpoArgs A)
+{
+    extern __shared__ __align__(16) unsigned char ppoSmemRaw[];
+    PpoSmem &S = *reinterpret_cast<PpoSmem *>(ppoSmemRaw);
+    const int tid = threadIdx.x, q = tid & 3, rb = tid >> 2, lane = tid & 31, warp = tid >> 5;
+
+    /* ---- parameters -> shared memory ---- */
+    for (int i = tid; i < kH * (BB_OBS_DIM / 4); i += kPpoThreads) {
+        const int j = i / (BB_OBS_DIM / 4), k4 = i % (BB_OBS_DIM / 4);
+        *reinterpret_cast<float4 *>(&S.w1[j][k4 * 4]) = *reinterpret_cast<const float4 *>(P.w1 + j * BB_OBS_DIM + k4 * 4);
+    }
+    for (int i = tid; i < kH * kH; i += kPpoThreads) {
+        const int j = i / kH, k = i % kH;
+        const float w = P.w2[i];
+        S.w2[j][k] = w;
+        S.w2t[k][j] = w;
+    }
+    for (int i = tid; i < kHeads * kH; i += kPpoThreads) {
+        const int j = i / kH, k = i % kH;
+        const float w = j < BB_NUM_LOGITS ? P.wa[j * kH + k] : P.wc[k];
+        S.wh[j][k] = w;
+        S.wht[k][j] = w;
+    }
+    if (tid < kH) { S.wht[tid][20] = S.wht[tid][21] = S.wht[tid][22] = S.wht[tid][23] = 0.f; }
+    if (tid < BB_OBS_DIM) { S.mean[tid] = P.obs_mean[tid]; S.inv[tid] = P.obs_inv_std[tid]; }
+    if (tid >= 128 && tid < 128 + kH) {
+        const int j = tid - 128;
+        S.b1[j] = P.b1[j]; S.g1[j] = P.ln1_g[j]; S.e1[j] = P.ln1_b[j];
+        S.b2[j] = P.b2[j]; S.g2[j] = P.ln2_g[j]; S.e2[j] = P.ln2_b[j];
+    }
+    if (tid >= 192 && tid < 192 + kZS) { const int j = tid - 192; S.bh[j] = j < BB_NUM_LOGITS ? P.ba[j] : (j == BB_NUM_LOGITS ? P.bc[0] : 0.f); }
+    __syncthreads();
+
+    /* ---- accumulators that live across the block's tiles ---- */
+    float gW1[4][4], gW2[4], gWh[4], gB = 0.f;                     /* tile-phase patches */
+    float dg1[kCh], de1[kCh], dg2[kCh], de2[kCh];                  /* LayerNorm parameters, per (row slot, channel) */
+    float st0 = 0.f, st1 = 0.f, st2 = 0.f, st3 = 0.f;              /* loss statistics (q == 0 threads) */
+#pragma unroll
+    for (int i = 0; i < 4; i++) { gW2[i] = 0.f; gWh[i] = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; j++) gW1[i][j] = 0.f; }
+#pragma unroll
+    for (int c = 0; c < kCh; c++) { dg1[c] = de1[c] = dg2[c] = de2[c] = 0.f; }
+
+    const bb_ppo_batch &B = A.b;
+    const float clipLo = 1.f - B.clip_coef, clipHi = 1.f + B.clip_coef;
+
+    for (int64_t tile = blockIdx.x; tile < A.numTiles; tile += gridDim.x) {
+        /* =========================== row phase =========================== */
+        const int64_t mrow = tile * kPpoRows + rb;
+        const bool valid = mrow < B.num_rows;
+        const int64_t src = B.indices ? B.indices[valid ? mrow : B.num_rows - 1] : (valid ? mrow : B.num_rows - 1);
+        {   /* observation normaliser (agent.py:27-39): this thread's 8 of the row's 32 float4 chunks */
+            const float4 *orow = reinterpret_cast<const float4 *>(B.obs + src * BB_OBS_DIM);
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const int k4 = 4 * i + q;
+                const float4 x = orow[k4];
+                const float4 mu = *reinterpret_cast<const float4 *>(&S.mean[k4 * 4]);
+                const float4 is = *reinterpret_cast<const float4 *>(&S.inv[k4 * 4]);
+                float4 y = make_float4((x.x - mu.x) * is.x, (x.y - mu.y) * is.y, (x.z - mu.z) * is.z, (x.w - mu.w) * is.w);
+                if (P.obs_clamp > 0.f) {
+                    y.x = fminf(fmaxf(y.x, -P.obs_clamp), P.obs_clamp); y.y = fminf(fmaxf(y.y, -P.obs_clamp), P.obs_clamp);
+                    y.z = fminf(fmaxf(y.z, -P.obs_clamp), P.obs_clamp); y.w = fminf(fmaxf(y.w, -P.obs_clamp), P.obs_clamp);
+                }
+                *reinterpret_cast<float4 *>(&S.x[rb][k4 * 4]) = y;
+            }
+        }
+        __syncwarp();
+        /* ---- backbone.0-2: Linear(128,32) + LayerNorm + ReLU ---- */
+        float xh1[kCh], xh2[kCh];
+        float rstd1, rstd2;
+        unsigned mask1 = 0, mask2 = 0;
+        {
+#pragma unroll
+            for (int c = 0; c < kCh; c++) xh1[c] = S.b1[4 * c + q];
+#pragma unroll 4
+            for (int k4 = 0; k4 < BB_OBS_DIM / 4; k4++) {
+                const float4 x = *reinterpret_cast<const float4 *>(&S.x[rb][k4 * 4]);
+#pragma unroll
+                for (int c = 0; c < kCh; c++) {
+                    const float4 w = *reinterpret_cast<const float4 *>(&S.w1[4 * c + q][k4 * 4]);
+                    xh1[c] = fmaf(w.w, x.w, fmaf(w.z, x.z, fmaf(w.y, x.y, fmaf(w.x, x.x, xh1[c]))));
+                }
+            }
+            rstd1 = ppo_ln_fwd(xh1);
+#pragma unroll
+            for (int c = 0; c < kCh; c++) {
+                const float y = fmaf(xh1[c], S.g1[4 * c + q], S.e1[4 * c + q]);
+                if (y > 0.f) mask1 |= 1u << c;
+                S.a1[rb][4 * c + q] = fmaxf(y, 0.f);
+            }
+        }
+        __syncwarp();
+        /* ---- backbone.3-5: Linear(32,32) + LayerNorm + ReLU ---- */
+        {
+#pragma unroll
+            for (int c = 0; c < kCh; c++) xh2[c] = S.b2[4 * c + q];
+#pragma unroll
+            for (int k4 = 0; k4 < kH / 4; k4++) {
+                const float4 h = *reinterpret_cast<const float4 *>(&S.a1[rb][k4 * 4]);
+#pragma unroll
+                for (int c = 0; c < kCh; c++) {
+                    const float4 w = *reinterpret_cast<const float4 *>(&S.w2[4 * c + q][k4 * 4]);
+                    xh2[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, xh2[c]))));
+                }
+            }
+            rstd2 = ppo_ln_fwd(xh2);
+#pragma unroll
+            for (int c = 0; c < kCh; c++) {
+                const float y = fmaf(xh2[c], S.g2[4 * c + q], S.e2[4 * c + q]);
+                if (y > 0.f) mask2 |= 1u << c;
+                S.a2[rb][4 * c + q] = fmaxf(y, 0.f);
+            }
+        }
+        __syncwarp();
+        /* ---- heads: outputs q, q+4, .., q+16 of (19 actor logits | critic) ---- */
+        {
+            float o[kHeadPerThread];
+#pragma unroll
+            for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
+#pragma unroll
+            for (int k4 = 0; k4 < kH / 4; k4++) {
+                const float4 h = *reinterpret_cast<const float4 *>(&S.a2[rb][k4 * 4]);
+#pragma unroll
+                for (int c = 0; c < kHeadPerThread; c++) {
+                    const float4 w = *reinterpret_cast<const float4 *>(&S.wh[4 * c + q][k4 * 4]);
+                    o[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, o[c]))));
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < kHeadPerThread; c++) S.z[rb][4 * c + q] = o[c];
+        }
+        __syncwarp();
+        /* ---- loss (ppo.py:192-208) and its gradient w.r.t. the head outputs; buckets spread over the quad ---- */
+        {
+            float lpPart = 0.f, entPart = 0.f;
+            float p[2][8], lg[2][8], Hb[2] = {0.f, 0.f};
+            int act[2] = {0, 0};
+#pragma unroll
+            for (int s2 = 0; s2 < 2; s2++) {
+                const int b = kQuadBuckets[q][s2];
+                if (b < 0) continue;
+                const int off = kBucketOff[b], cnt = kBucketCnt[b];
+                const float *l = &S.z[rb][off];
+                float m = l[0];
+                for (int i = 1; i < cnt; i++) m = fmaxf(m, l[i]);
+                float s = 0.f;
+                for (int i = 0; i < cnt; i++) s += expf(l[i] - m);
+                const float lse = m + logf(s);
+                float h = 0.f;
+                for (int i = 0; i < cnt; i++) {
+                    const float lgp = l[i] - lse, pr = expf(lgp);
+                    lg[s2][i] = lgp; p[s2][i] = pr;
+                    h = fmaf(-pr, lgp, h);
+                }
+                int a = (int)B.actions[src * BB_NUM_ACTION_DIMS + b];
+                a = a < 0 ? 0 : (a >= cnt ? cnt - 1 : a);
+                act[s2] = a;
+                float la = lg[s2][0];
+                for (int i = 1; i < cnt; i++) if (i == a) la = lg[s2][i];
+                lpPart += la;
+                Hb[s2] = h;
+                entPart += h;
+            }
+            const float lp = quad_sum(lpPart), ent = quad_sum(entPart);
+            /* actor: ratio = exp(lp - lp_old); max(-adv * ratio, -adv * clamp(ratio)) */
+            const float adv = B.advantages[src];
+            const float ratio = expf(lp - B.log_probs[src]);
+            const float surr1 = -adv * ratio;
+            const float surr2 = -adv * fminf(fmaxf(ratio, clipLo), clipHi);
+            const bool inside = ratio >= clipLo && ratio <= clipHi;
+            /* d max / d ratio: inside the clip both branches carry -adv (torch splits a tie 0.5 + 0.5); outside only surr1 can */
+            float dRatio = 0.f;
+            if (inside) dRatio = -adv;
+            else if (surr1 > surr2) dRatio = -adv;
+            else if (surr1 == surr2) dRatio = -0.5f * adv;
+            const float gLp = valid ? A.invM * dRatio * ratio : 0.f;
+            const float gEnt = valid ? A.invM * B.ent_coef : 0.f;   /* d(-ent_coef * mean H)/dz_j = ent_coef/m * p_j (log p_j + H) */
+#pragma unroll
+            for (int s2 = 0; s2 < 2; s2++) {
+                const int b = kQuadBuckets[q][s2];
+                if (b < 0) continue;
+                const int off = kBucketOff[b], cnt = kBucketCnt[b];
+                for (int i = 0; i < cnt; i++) {
+                    const float oneHot = (i == act[s2]) ? 1.f : 0.f;
+                    S.z[rb][off + i] = fmaf(gLp, oneHot - p[s2][i], gEnt * p[s2][i] * (lg[s2][i] + Hb[s2]));
+                }
+            }
+            if (q == 3) { /* critic (ppo.py:197-201): 0.5 * max((v - ret)^2, (v_old + clamp(v - v_old) - ret)^2) * vf_coef */
+                const float v = S.z[rb][BB_NUM_LOGITS];
+                const float vo = B.values[src], ret = B.returns[src];
+                const float dvo = v - vo;
+                const float vclip = vo + fminf(fmaxf(dvo, -B.clip_coef), B.clip_coef);
+                const float e1 = v - ret, e2 = vclip - ret;
+                const float l1 = e1 * e1, l2 = e2 * e2;
+                const float passes = (dvo >= -B.clip_coef && dvo <= B.clip_coef) ? 1.f : 0.f;
+                float dv;
+                if (l1 > l2) dv = 2.f * e1;
+                else if (l2 > l1) dv = 2.f * e2 * passes;
+                else dv = e1 + e2 * passes;
+                S.z[rb][BB_NUM_LOGITS] = valid ? A.invM * 0.5f * B.vf_coef * dv : 0.f;
+                if (valid) st1 += 0.5f * fmaxf(l1, l2);
+            }
+            if (q == 0 && valid) { st0 += fmaxf(surr1, surr2); st2 += ent; st3 += inside ? 0.f : 1.f; }
+        }
+        __syncwarp();
+        /* ---- backward through the heads, LayerNorm 2, Linear 2, LayerNorm 1 ---- */
+        {
+            float d[kCh];
+#pragma unroll
+            for (int c = 0; c < kCh; c++) d[c] = 0.f;
+#pragma unroll
+            for (int j4 = 0; j4 < kHeads / 4; j4++) {
+                const float4 g = *reinterpret_cast<const float4 *>(&S.z[rb][j4 * 4]);
+#pragma unroll
+                for (int c = 0; c < kCh; c++) {
+                    const float4 w = *reinterpret_cast<const float4 *>(&S.wht[4 * c + q][j4 * 4]);
+                    d[c] = fmaf(w.w, g.w, fmaf(w.z, g.z, fmaf(w.y, g.y, fmaf(w.x, g.x, d[c]))));
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < kCh; c++) if (!((mask2 >> c) & 1u)) d[c] = 0.f;
+            ppo_ln_bwd(d, xh2, rstd2, S.g2, q, dg2, de2);
+#pragma unroll
+            for (int c = 0; c < kCh; c++) S.dh2[rb][4 * c + q] = d[c];
+            __syncwarp();
+#pragma unroll
+            for (int c = 0; c < kCh; c++) d[c] = 0.f;
+#pragma unroll
+            for (int k4 = 0; k4 < kH / 4; k4++) {
+                const float4 g = *reinterpret_cast<const float4 *>(&S.dh2[rb][k4 * 4]);
+#pragma unroll
+                for (int c = 0; c < kCh; c++) {
+                    const float4 w = *reinterpret_cast<const float4 *>(&S.w2t[4 * c + q][k4 * 4]);
+                    d[c] = fmaf(w.w, g.w, fmaf(w.z, g.z, fmaf(w.y, g.y, fmaf(w.x, g.x, d[c]))));
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < kCh; c++) if (!((mask1 >> c) & 1u)) d[c] = 0.f;
+            ppo_ln_bwd(d, xh1, rstd1, S.g1, q, dg1, de1);
+#pragma unroll
+            for (int c = 0; c < kCh; c++) S.dh1[rb][4 * c + q] = d[c];
+        }
+        __syncthreads();
+        /* =========================== tile phase: weight gradients =========================== */
+        {
+            const int cg = warp, kg = lane;            /* dW1 patch: channels 4cg.., inputs 4kg.. */
+            const int j2 = tid >> 3, k42 = tid & 7;    /* dW2 / dWh patch: output j2, inputs 4k42.. */
+#pragma unroll 4
+            for (int r = 0; r < kPpoRows; r++) {
+                const float4 dd = *reinterpret_cast<const float4 *>(&S.dh1[r][cg * 4]);
+                const float4 xx = *reinterpret_cast<const float4 *>(&S.x[r][kg * 4]);
+                gW1[0][0] = fmaf(dd.x, xx.x, gW1[0][0]); gW1[0][1] = fmaf(dd.x, xx.y, gW1[0][1]);
+                gW1[0][2] = fmaf(dd.x, xx.z, gW1[0][2]); gW1[0][3] = fmaf(dd.x, xx.w, gW1[0][3]);
+                gW1[1][0] = fmaf(dd.y, xx.x, gW1[1][0]); gW1[1][1] = fmaf(dd.y, xx.y, gW1[1][1]);
+                gW1[1][2] = fmaf(dd.y, xx.z, gW1[1][2]); gW1[1][3] = fmaf(dd.y, xx.w, gW1[1][3]);
+                gW1[2][0] = fmaf(dd.z, xx.x, gW1[2][0]); gW1[2][1] = fmaf(dd.z, xx.y, gW1[2][1]);
+                gW1[2][2] = fmaf(dd.z, xx.z, gW1[2][2]); gW1[2][3] = fmaf(dd.z, xx.w, gW1[2][3]);
+                gW1[3][0] = fmaf(dd.w, xx.x, gW1[3][0]); gW1[3][1] = fmaf(dd.w, xx.y, gW1[3][1]);
+                gW1[3][2] = fmaf(dd.w, xx.z, gW1[3][2]); gW1[3][3] = fmaf(dd.w, xx.w, gW1[3][3]);
+                const float d2 = S.dh2[r][j2];
+                const float4 aa = *reinterpret_cast<const float4 *>(&S.a1[r][k42 * 4]);
+                gW2[0] = fmaf(d2, aa.x, gW2[0]); gW2[1] = fmaf(d2, aa.y, gW2[1]);
+                gW2[2] = fmaf(d2, aa.z, gW2[2]); gW2[3] = fmaf(d2, aa.w, gW2[3]);
+                if (j2 < kHeads) { /* warps 0..4 */
+                    const float dz = S.z[r][j2];
+                    const float4 bb2 = *reinterpret_cast<const float4 *>(&S.a2[r][k42 * 4]);
+                    gWh[0] = fmaf(dz, bb2.x, gWh[0]); gWh[1] = fmaf(dz, bb2.y, gWh[1]);
+                    gWh[2] = fmaf(dz, bb2.z, gWh[2]); gWh[3] = fmaf(dz, bb2.w, gWh[3]);
+                } else if (tid >= 160 && tid < 160 + 2 * kH + kHeads) { /* biases: b1 | b2 | head biases */
+                    const int t = tid - 160;
+                    gB += t < kH ? S.dh1[r][t] : (t < 2 * kH ? S.dh2[r][t - kH] : S.z[r][t - 2 * kH]);
+                }
+            }
+        }
+        __syncthreads(); /* the next tile rewrites the shared activations */
+    }
+
+    /* =========================== epilogue: this block's partial =========================== */
+    float *out = A.partials + (int64_t)blockIdx.x * kPpoPartial;
+    {
+        const int cg = warp, kg = lane, j2 = tid >> 3, k42 = tid & 7;
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+            *reinterpret_cast<float4 *>(out + BB_PPO_OFF_W1 + (4 * cg + i) * BB_OBS_DIM + 4 * kg) = make_float4(gW1[i][0], gW1[i][1], gW1[i][2], gW1[i][3]);
+        *reinterpret_cast<float4 *>(out + BB_PPO_OFF_W2 + j2 * kH + 4 * k42) = make_float4(gW2[0], gW2[1], gW2[2], gW2[3]);
+        if (j2 < kHeads) {
+            float *dst = out + (j2 < BB_NUM_LOGITS ? BB_PPO_OFF_WA + j2 * kH : BB_PPO_OFF_WC) + 4 * k42; /* WC is not 16-byte aligned */
+            dst[0] = gWh[0]; dst[1] = gWh[1]; dst[2] = gWh[2]; dst[3] = gWh[3];
+        } else if (tid >= 160 && tid < 160 + 2 * kH + kHeads) {
+            const int t = tid - 160;
+            const int off = t < kH ? BB_PPO_OFF_B1 + t : (t < 2 * kH ? BB_PPO_OFF_B2 + (t - kH)
+                          : (t - 2 * kH < BB_NUM_LOGITS ? BB_PPO_OFF_BA + (t - 2 * kH) : BB_PPO_OFF_BC));
+            out[off] = gB;
+        }
+    }
+    /* LayerNorm parameter gradients: sum the 64 row slots per channel through shared memory (fixed order) */
+#pragma unroll
+    for (int c = 0; c < kCh; c++) {
+        S.a1[rb][4 * c + q] = dg1[c]; S.a2[rb][4 * c + q] = de1[c];
+        S.dh1[rb][4 * c + q] = dg2[c]; S.dh2[rb][4 * c + q] = de2[c];
+    }
+    if (q == 0) { S.z[rb][0] = st0; S.z[rb][2] = st2; S.z[rb][3] = st3; }
+    if (q == 3) S.z[rb][1] = st1;
+    __syncthreads();
+    if (tid < 4 * kH) {
+        const int arr = tid >> 5, ch = tid & 31;
+        const float(*src)[kHS] = arr == 0 ? S.a1 : (arr == 1 ? S.a2 : (arr == 2 ? S.dh1 : S.dh2));
+        float s = 0.f;
+        for (int r = 0; r < kPpoRows; r++) s += src[r][ch];
+        const int off = arr == 0 ? BB_PPO_OFF_G1 : (arr == 1 ? BB_PPO_OFF_E1 : (arr == 2 ? BB_PPO_OFF_G2 : BB_PPO_OFF_E2));
+        out[off + ch] = s;
+    } else if (tid < 4 * kH + BB_PPO_NUM_STATS) {
+        const int k = tid - 4 * kH;
+        float s = 0.f;
+        for (int r = 0; r < kPpoRows; r++) s += S.z[r][k];
+        out[BB_PPO_NUM_PARAMS + k] = s;
+    }
+}
+
+/* grad[j] = sum over blocks (in block order) of partial[b][j]; the last BB_PPO_NUM_STATS entries go to stats */
+__global__ void bb_ppo_reduce_kernel(const float *partials, int numBlocks, float *grad, float *stats)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= kPpoPartial) return;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int b = 0;
+    for (; b + 4 <= numBlocks; b += 4) {
+        s0 += partials[(int64_t)b * kPpoPartial + j];
+        s1 += partials[(int64_t)(b + 1) * kPpoPartial + j];
+        s2 += partials[(int64_t)(b + 2) * kPpoPartial + j];
+        s3 += partials[(int64_t)(b + 3) * kPpoPartial + j];
+    }
+    for (; b < numBlocks; b++) s0 += partials[(int64_t)b * kPpoPartial + j];
+    const float s = (s0 + s1) + (s2 + s3);
+    if (j < BB_PPO_NUM_PARAMS) grad[j] = s;
+    else if (stats) stats[j - BB_PPO_NUM_PARAMS] = s;
+}
+
+/* clip_grad_norm_ + Adam on a flat vector; one block (the policy has 5 972 parameters) */
+constexpr int kAdamThreads = 1024;
+__global__ void __launch_bounds__(kAdamThreads) bb_ppo_adam_kernel(float *params, const float *grad, float *m, float *v, int32_t *stepDev,
+                                                                    int64_t n, float gradScale, float maxNorm, float lr, float beta1,
+                                                                    float beta2, float eps, float *normOut)
+{
+    __shared__ float red[kAdamThreads / 32];
+    __shared__ float sNorm;
+    float s = 0.f;
+    for (int64_t i = threadIdx.x; i < n; i += kAdamThreads) { const float g = grad[i] * gradScale; s = fmaf(g, g, s); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float t = red[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (threadIdx.x == 0) sNorm = sqrtf(t);
+    }
+    __syncthreads();
+    const float norm = sNorm;
+    /* torch: clip_coef = max_norm / (total_norm + 1e-6), clamped to 1 */
+    const float clip = maxNorm > 0.f ? fminf(maxNorm / (norm + 1e-6f), 1.f) : 1.f;
+    const int32_t step = stepDev[0] + 1;
+    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+    const float stepSize = (float)((double)lr / bc1);
+    const float bc2Sqrt = (float)sqrt(bc2);
+    for (int64_t i = threadIdx.x; i < n; i += kAdamThreads) {
+        const float g = grad[i] * gradScale * clip;
+        const float mi = m[i] + (g - m[i]) * (1.f - beta1);       /* exp_avg.lerp_(grad, 1 - beta1) */
+        const float vi = fmaf(beta2, v[i], (1.f - beta2) * g * g); /* exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2) */
+        m[i] = mi; v[i] = vi;
+        const float denom = sqrtf(vi) / bc2Sqrt + eps;
+        params[i] -= stepSize * (mi / denom);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { stepDev[0] = step; if (normOut) normOut[0] = norm; }
+}
+
+} // namespace bb

@@ -1,0 +1,154 @@
+"""Fused PPO update (include/bb_ppo.h): host-side mirror of scripts/ppo.py `update_policy` (ppo.py:180-216).
+
+A minibatch step is `bb_ppo_grad` (forward + clipped-PPO loss + backward of the 5 972-parameter policy in one
+kernel, deterministic block-order reduction) -> optional flat all-reduce across ranks -> `bb_ppo_adam`
+(clip_grad_norm_ + Adam).  The parameters of the torch module are re-bound as views of ONE flat float32
+vector, so the kernels, `state_dict()` (reference checkpoint keys) and `PolicyWeights` all see the same memory.
+torch is used for storage, the permutation (`torch.randperm`, ppo.py:186) and the collective only.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, Optional
+
+from . import _lib
+from .rollout import BBPolicy, PolicyWeights, _bind as _bind_rollout
+
+NUM_PARAMS, NUM_STATS = 5972, 4
+# flat layout = order of agent.parameters() (agent.py:111-127); offsets are include/bb_ppo.h BB_PPO_OFF_*
+PARAM_ORDER = ["backbone.0.weight", "backbone.0.bias", "backbone.1.weight", "backbone.1.bias", "backbone.3.weight",
+               "backbone.3.bias", "backbone.4.weight", "backbone.4.bias", "actor.weight", "actor.bias", "critic.weight",
+               "critic.bias"]
+
+_fp = ctypes.c_void_p
+
+
+class BBPpoBatch(ctypes.Structure):
+    _fields_ = [("obs", _fp), ("actions", _fp), ("log_probs", _fp), ("values", _fp), ("advantages", _fp), ("returns", _fp),
+                ("indices", _fp), ("num_rows", ctypes.c_int64), ("clip_coef", ctypes.c_float), ("ent_coef", ctypes.c_float),
+                ("vf_coef", ctypes.c_float)]
+
+
+def _bind(lib):
+    if getattr(lib, "_ppo_bound", False):
+        return lib
+    _bind_rollout(lib)
+    vp, f32 = ctypes.c_void_p, ctypes.c_float
+    lib.bb_ppo_workspace_bytes.restype = ctypes.c_int64
+    lib.bb_ppo_workspace_bytes.argtypes = []
+    lib.bb_ppo_grad.restype = ctypes.c_int
+    lib.bb_ppo_grad.argtypes = [ctypes.POINTER(BBPolicy), ctypes.POINTER(BBPpoBatch), vp, vp, vp, vp]
+    lib.bb_ppo_adam.restype = ctypes.c_int
+    lib.bb_ppo_adam.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int64, f32, f32, f32, f32, f32, f32, vp, vp]
+    lib._ppo_bound = True
+    return lib
+
+
+def flatten_parameters_(agent):
+    """Re-binds the module's parameters as views of one flat float32 vector (in PARAM_ORDER) and returns it."""
+    import torch
+
+    named = dict(agent.named_parameters())
+    assert list(named) == PARAM_ORDER, f"unexpected parameter list {list(named)}"
+    dev = named[PARAM_ORDER[0]].device
+    flat = torch.empty(NUM_PARAMS, dtype=torch.float32, device=dev)
+    off = 0
+    with torch.no_grad():
+        for k in PARAM_ORDER:
+            p = named[k]
+            n = p.numel()
+            flat[off:off + n].copy_(p.detach().reshape(-1))
+            p.data = flat[off:off + n].view(p.shape)
+            off += n
+    assert off == NUM_PARAMS, "Agent must be Agent(input_dim=128, num_channels=32, num_layers=2)"
+    return flat
+
+
+class FusedPPO:
+    """clip-PPO minibatch steps on the flat parameter vector of an `Agent` (policy_torch.Agent / reference Agent)."""
+
+    def __init__(self, agent, lr: float = 3e-4, betas=(0.9, 0.999), eps: float = 1e-8, clip_coef: float = 0.2,
+                 ent_coef: float = 0.01, vf_coef: float = 1.0, max_grad_norm: float = 1.0):
+        import torch
+
+        self._lib = _bind(_lib.load())
+        self.agent = agent
+        self.flat = flatten_parameters_(agent)
+        dev = self.device = self.flat.device
+        assert dev.type == "cuda", "the fused PPO update has no CPU path"
+        self.weights = PolicyWeights.from_module(agent)      # pointers into self.flat + the normaliser vectors
+        self.exp_avg = torch.zeros_like(self.flat)
+        self.exp_avg_sq = torch.zeros_like(self.flat)
+        self.step = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.grad = torch.zeros_like(self.flat)
+        self.stats = torch.zeros(NUM_STATS, dtype=torch.float32, device=dev)
+        self.grad_norm = torch.zeros(1, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            nbytes = int(self._lib.bb_ppo_workspace_bytes())
+        if nbytes <= 0:
+            raise RuntimeError("bb_ppo_workspace_bytes failed: " + _lib.last_error())
+        self.workspace = torch.empty(nbytes // 4, dtype=torch.float32, device=dev)
+        self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
+        self.clip_coef, self.ent_coef, self.vf_coef = float(clip_coef), float(ent_coef), float(vf_coef)
+        self.max_grad_norm = float(max_grad_norm)
+
+    def _stream(self):
+        import torch
+
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def gradient(self, obs, actions, log_probs, values, advantages, returns, indices=None):
+        """d loss / d parameters of one minibatch (ppo.py:189-211) into self.grad (flat); loss sums into self.stats.
+        All tensors are the flattened rollout buffers ([R,128], [R,6], [R]...); `indices` (int64 [m]) selects the rows."""
+        import torch
+
+        for t in (obs, actions, log_probs, values, advantages, returns):
+            assert t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+        b = BBPpoBatch()
+        b.obs, b.actions, b.log_probs = obs.data_ptr(), actions.data_ptr(), log_probs.data_ptr()
+        b.values, b.advantages, b.returns = values.data_ptr(), advantages.data_ptr(), returns.data_ptr()
+        if indices is not None:
+            assert indices.dtype == torch.int64 and indices.is_contiguous() and indices.is_cuda
+            b.indices, b.num_rows = indices.data_ptr(), indices.numel()
+        else:
+            b.indices, b.num_rows = None, obs.shape[0]
+        b.clip_coef, b.ent_coef, b.vf_coef = self.clip_coef, self.ent_coef, self.vf_coef
+        rc = self._lib.bb_ppo_grad(ctypes.byref(self.weights.c), ctypes.byref(b), self.workspace.data_ptr(), self.grad.data_ptr(),
+                                   self.stats.data_ptr(), self._stream())
+        if rc != 0:
+            raise RuntimeError("bb_ppo_grad failed: " + _lib.last_error())
+        self._last_rows = int(b.num_rows)
+        return self.grad
+
+    def apply(self, grad_scale: float = 1.0) -> None:
+        """clip_grad_norm_ + Adam step (ppo.py:212-214) with self.grad * grad_scale."""
+        rc = self._lib.bb_ppo_adam(self.flat.data_ptr(), self.grad.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(),
+                                   self.step.data_ptr(), NUM_PARAMS, float(grad_scale), self.max_grad_norm, self.lr,
+                                   self.betas[0], self.betas[1], self.eps, self.grad_norm.data_ptr(), self._stream())
+        if rc != 0:
+            raise RuntimeError("bb_ppo_adam failed: " + _lib.last_error())
+
+    def update(self, buf, num_minibatches: int = 4, update_epochs: int = 4, generator=None) -> Dict[str, "object"]:
+        """ppo.py:180-216 on this rank's rollout buffers (rollout.RolloutBuffers after finish_advantages).  With
+        torch.distributed initialised the flat gradient is summed across ranks (one all-reduce per step) and averaged."""
+        import torch
+        import torch.distributed as dist
+
+        ws = dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+        total = buf.horizon * buf.n_envs
+        mb = total // num_minibatches
+        obs = buf.obs.view(-1, buf.obs.shape[-1])
+        act = buf.actions.view(-1, buf.actions.shape[-1])
+        lp, v = buf.log_probs.view(-1), buf.values.view(-1)
+        adv, ret = buf.advantages.view(-1), buf.returns.view(-1)
+        self.weights.refresh()   # the observation normaliser moved since the rollout (ppo.py:168)
+        for _ in range(update_epochs):
+            perm = torch.randperm(total, device=self.device, generator=generator)
+            for start in range(0, mb * num_minibatches, mb):
+                self.gradient(obs, act, lp, v, adv, ret, perm[start:start + mb])
+                if ws > 1:
+                    dist.all_reduce(self.grad, op=dist.ReduceOp.SUM)
+                self.apply(1.0 / ws)
+        m = float(mb)
+        return {"pg_loss": self.stats[0] / m, "v_loss": self.stats[1] / m * self.vf_coef,
+                "ent_loss": -self.stats[2] / m * self.ent_coef, "clip_frac": self.stats[3] / m, "grad_norm": self.grad_norm[0]}

@@ -37,6 +37,10 @@ def test_library_exports_every_declared_symbol(lib):
     assert rollout == ["bb_gae", "bb_policy_forward", "bb_rollout"]
     for sym in rollout:
         assert hasattr(lib, sym), f"libbball.so lacks {sym}"
+    ppo = _declared_symbols("bb_ppo.h")
+    assert ppo == ["bb_ppo_adam", "bb_ppo_grad", "bb_ppo_workspace_bytes"]
+    for sym in ppo:
+        assert hasattr(lib, sym), f"libbball.so lacks {sym}"
 
 
 def test_library_is_sm100a_native_code():

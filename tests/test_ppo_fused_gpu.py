@@ -1,0 +1,185 @@
+"""GPU parity of the fused PPO update (include/bb_ppo.h) against plain torch fp32 autograd of the reference's
+update_policy (scripts/ppo.py:180-216) on the same minibatch.  Floating-point kernels: the gradient is a sum over
+65 536 rows in a different order than torch's, so the tolerance is 1e-4 relative to the largest gradient entry of
+each parameter tensor (stated per assert); Adam steps agree to 1e-6 relative."""
+import numpy as np
+import pytest
+
+from helpers import make_engine
+from ref_agent import ACTION_BUCKETS
+
+pytestmark = pytest.mark.gpu
+
+
+def _agent(seed=0, scale=1.0):
+    import torch
+
+    from madrona_basketball_b200.policy_torch import Agent
+
+    torch.manual_seed(seed)
+    a = Agent().cuda()
+    g = torch.Generator().manual_seed(seed + 1)
+    with torch.no_grad():   # non-trivial heads and normaliser (the reference's init makes the heads ~0.01)
+        for p in a.parameters():
+            p.copy_((torch.randn(p.shape, generator=g) * (0.3 if p.dim() > 1 else 0.1) * scale).cuda())
+        a.backbone[1].weight.add_(1.0); a.backbone[4].weight.add_(1.0)
+        a.obs_norm.mean.copy_((torch.randn(128, generator=g, dtype=torch.float64) * 0.5).cuda())
+        a.obs_norm.var.copy_((torch.rand(128, generator=g, dtype=torch.float64) * 4.0 + 0.05).cuda())
+    return a
+
+
+def _batch(rows, seed=3):
+    """Real observation rows from the engine + synthetic behaviour statistics."""
+    import torch
+
+    n = (rows + 1) // 2
+    sim = make_engine(n)
+    for s in range(30):
+        sim.fill_actions(11, s)
+        sim.step()
+    torch.cuda.synchronize()
+    obs = sim.observations_tensor().to_torch().reshape(-1, 128)[:rows].clone()
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    act = torch.stack([torch.randint(0, nb, (rows,), generator=g, device="cuda") for nb in ACTION_BUCKETS], dim=1).float()
+    adv = torch.randn(rows, generator=g, device="cuda")
+    ret = torch.randn(rows, generator=g, device="cuda")
+    return obs, act, adv, ret, g
+
+
+def _torch_loss(agent, obs, act, lp_old, v_old, adv, ret, clip=0.2, ent_coef=0.01, vf_coef=1.0):
+    import torch
+
+    lp, ent, v = agent.get_stats(obs, act)
+    ratio = torch.exp(lp - lp_old)
+    pg = torch.max(-adv * ratio, -adv * torch.clamp(ratio, 1 - clip, 1 + clip))
+    v_clip = v_old + (v - v_old).clamp(-clip, clip)
+    vl = 0.5 * torch.max((v - ret) ** 2, (v_clip - ret) ** 2)
+    loss = pg.mean() + vf_coef * vl.mean() - ent_coef * ent.mean()
+    return loss, pg.sum(), vl.sum(), ent.sum(), ((ratio < 1 - clip) | (ratio > 1 + clip)).float().sum()
+
+
+def _behaviour(agent, obs, act, g, spread):
+    """lp_old / v_old around the current policy so that a good share of rows is clipped on either side."""
+    import torch
+
+    with torch.no_grad():
+        lp, _, v = agent.get_stats(obs, act)
+    rows = obs.shape[0]
+    return (lp + spread * torch.randn(rows, generator=g, device="cuda")).contiguous(), \
+           (v + spread * torch.randn(rows, generator=g, device="cuda")).contiguous()
+
+
+@pytest.mark.parametrize("rows,use_idx", [(4096, False), (1000, True), (65536, True), (37, False)])
+def test_gradient_matches_torch_autograd(rows, use_idx):
+    import torch
+
+    from madrona_basketball_b200.ppo_fused import PARAM_ORDER, FusedPPO
+
+    agent = _agent(seed=rows)
+    obs, act, adv, ret, g = _batch(rows + 50)
+    fused = FusedPPO(agent)
+    lp_old, v_old = _behaviour(agent, obs, act, g, 0.25)
+    idx = torch.randperm(rows + 50, generator=g, device="cuda")[:rows].contiguous() if use_idx else None
+    sel = idx if use_idx else torch.arange(rows, device="cuda")
+    o = obs if use_idx else obs[:rows].contiguous()
+    a = act if use_idx else act[:rows].contiguous()
+    args = (lp_old, v_old, adv, ret) if use_idx else tuple(t[:rows].contiguous() for t in (lp_old, v_old, adv, ret))
+    grad = fused.gradient(o, a, *args, indices=idx).clone()
+    stats = fused.stats.clone()
+
+    agent.zero_grad()
+    loss, pg_sum, vl_sum, ent_sum, nclip = _torch_loss(agent, obs[sel], act[sel], lp_old[sel], v_old[sel], adv[sel], ret[sel])
+    loss.backward()
+    torch.cuda.synchronize()
+    named = dict(agent.named_parameters())
+    off = 0
+    for k in PARAM_ORDER:
+        ref = named[k].grad.reshape(-1)
+        got = grad[off:off + ref.numel()]
+        off += ref.numel()
+        scale = ref.abs().max().item()
+        assert scale > 0
+        err = (got - ref).abs().max().item()
+        assert err <= 1e-4 * scale + 1e-9, f"{k}: max err {err:.3e} vs scale {scale:.3e}"   # 1e-4 of the tensor's largest entry
+    ref_stats = torch.stack([pg_sum, vl_sum, ent_sum, nclip]).detach()
+    assert torch.allclose(stats[:3], ref_stats[:3], rtol=2e-5, atol=1e-3), (stats, ref_stats)
+    assert abs(stats[3].item() - ref_stats[3].item()) <= max(2.0, 1e-3 * rows)   # rows within an ulp of the clip edge
+    assert 0.05 * rows < ref_stats[3].item() < 0.95 * rows                          # both regimes are exercised
+
+
+def test_gradient_is_bitwise_reproducible():
+    import torch
+
+    from madrona_basketball_b200.ppo_fused import FusedPPO
+
+    agent = _agent(seed=5)
+    obs, act, adv, ret, g = _batch(20000)
+    fused = FusedPPO(agent)
+    lp_old, v_old = _behaviour(agent, obs, act, g, 0.2)
+    g1 = fused.gradient(obs, act, lp_old, v_old, adv, ret).clone()
+    g2 = fused.gradient(obs, act, lp_old, v_old, adv, ret).clone()
+    torch.cuda.synchronize()
+    assert torch.equal(g1, g2)
+
+
+def test_clip_and_adam_match_torch():
+    import torch
+
+    from madrona_basketball_b200.ppo_fused import PARAM_ORDER, FusedPPO
+
+    agent = _agent(seed=9)
+    ref = _agent(seed=9)
+    fused = FusedPPO(agent, lr=3e-4, max_grad_norm=1.0)
+    opt = torch.optim.Adam(ref.parameters(), lr=3e-4, eps=1e-8)
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    rnamed = dict(ref.named_parameters())
+    for step in range(5):
+        gflat = torch.randn(5972, generator=gen, device="cuda") * (3.0 if step % 2 == 0 else 0.005)   # clipped / not clipped
+        fused.grad.copy_(gflat)
+        fused.apply(0.5)
+        off = 0
+        for k in PARAM_ORDER:
+            p = rnamed[k]
+            p.grad = (gflat[off:off + p.numel()] * 0.5).view_as(p).clone()
+            off += p.numel()
+        norm = torch.nn.utils.clip_grad_norm_(list(ref.parameters()), 1.0)
+        opt.step()
+        torch.cuda.synchronize()
+        assert abs(fused.grad_norm.item() - norm.item()) <= 1e-5 * norm.item()
+        named = dict(agent.named_parameters())
+        for k in PARAM_ORDER:
+            assert torch.allclose(named[k], rnamed[k], rtol=1e-6, atol=1e-7), k   # Adam arithmetic: 1e-6 relative
+    assert int(fused.step.item()) == 5
+
+
+def test_fused_update_tracks_torch_update_policy():
+    """One epoch (4 minibatches) of ppo.py:180-216 with the same permutation: parameters agree to 1e-4 absolute
+    (16 384-row gradients summed in a different order, then Adam's normalisation)."""
+    import torch
+
+    from madrona_basketball_b200.ppo_fused import PARAM_ORDER, FusedPPO
+
+    rows, nmb = 16384, 4
+    agent, ref = _agent(seed=21), _agent(seed=21)
+    obs, act, adv, ret, g = _batch(rows)
+    lp_old, v_old = _behaviour(agent, obs, act, g, 0.1)
+    fused = FusedPPO(agent)
+    opt = torch.optim.Adam(ref.parameters(), lr=3e-4, eps=1e-8)
+    perm = torch.randperm(rows, generator=g, device="cuda")
+    mb = rows // nmb
+    for s in range(0, rows, mb):
+        idx = perm[s:s + mb]
+        fused.gradient(obs, act, lp_old, v_old, adv, ret, idx)
+        fused.apply()
+        loss = _torch_loss(ref, obs[idx], act[idx], lp_old[idx], v_old[idx], adv[idx], ret[idx])[0]
+        opt.zero_grad()
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(list(ref.parameters()), 1.0)
+        opt.step()
+    torch.cuda.synchronize()
+    named, rnamed = dict(agent.named_parameters()), dict(ref.named_parameters())
+    for k in PARAM_ORDER:
+        assert torch.allclose(named[k], rnamed[k], rtol=0, atol=1e-4), (k, (named[k] - rnamed[k]).abs().max())
+    # the module's state_dict still carries the reference's checkpoint keys, now as views of the flat vector
+    assert set(PARAM_ORDER) <= set(agent.state_dict().keys())
+    assert named["actor.weight"].data_ptr() == fused.flat.data_ptr() + 4 * 5312
