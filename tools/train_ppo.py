@@ -5,9 +5,10 @@ rollouts, 4 epochs x 4 minibatches), one process per GPU:
     python tools/train_ppo.py --iters 20
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 tools/train_ppo.py --iters 20
 
-Rollout and GAE run in libbball.so (bb_rollout, bb_gae: no host sync per step); normaliser updates, advantage
-normalisation and the clipped-PPO update stay in torch as in the reference, with one flat NCCL all-reduce per
-optimiser step (ppo_dist.py).  Prints one JSON line on rank 0: env-steps/s (SPS) over the timed iterations.
+Rollout and GAE run in libbball.so (bb_rollout, bb_gae: no host sync per step); the clipped-PPO update is
+bb_ppo_grad + bb_ppo_adam (--update fused, default) or torch autograd as in the reference (--update torch), with
+one flat NCCL all-reduce of the gradient per optimiser step; normaliser updates and advantage normalisation stay
+in torch (ppo_dist.py).  Prints one JSON line on rank 0: env-steps/s (SPS) over the timed iterations.
 """
 import argparse
 import json
@@ -28,6 +29,8 @@ def main():
     ap.add_argument("--trainee-idx", type=int, default=1)   # ppo.py:34
     ap.add_argument("--seed", type=int, default=321)        # ppo.py:26
     ap.add_argument("--save", default=None, help="write the trained state_dict here (reference checkpoint format)")
+    ap.add_argument("--update", default="fused", choices=["fused", "torch"],
+                    help="fused: bb_ppo_grad + bb_ppo_adam (3 kernels per minibatch step); torch: autograd + torch.optim.Adam as in the reference")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -49,7 +52,12 @@ def main():
     agent = Agent().to(dev)
     ppo_dist.broadcast_module_(agent)
     cfg = ppo_dist.PPOConfig()
-    opt = torch.optim.Adam(agent.parameters(), lr=cfg.learning_rate, eps=1e-8)
+    if args.update == "fused":   # re-binds the parameters as views of one flat vector: before anything takes their pointers
+        from madrona_basketball_b200.ppo_fused import FusedPPO
+        fused = FusedPPO(agent, lr=cfg.learning_rate, eps=1e-8, clip_coef=cfg.clip_coef, ent_coef=cfg.ent_coef,
+                         vf_coef=cfg.vf_coef, max_grad_norm=cfg.max_grad_norm)
+    else:
+        opt = torch.optim.Adam(agent.parameters(), lr=cfg.learning_rate, eps=1e-8)
     weights = PolicyWeights.from_module(agent)
     buf = RolloutBuffers(T, n, dev)
     roll = FusedRollout(shard.sim, weights, args.trainee_idx, seed=args.seed, world_offset=shard.world_offset)
@@ -75,7 +83,10 @@ def main():
         weights.refresh()                                               # the observation normaliser moved
         e[2].record()
         agent.train()
-        losses = ppo_dist.update_policy(agent, opt, buf, cfg, generator=gen)   # ppo.py:180-216
+        if args.update == "fused":                                      # ppo.py:180-216
+            losses = fused.update(buf, cfg.num_minibatches, cfg.update_epochs, generator=gen)
+        else:
+            losses = ppo_dist.update_policy(agent, opt, buf, cfg, generator=gen)
         e[3].record()
         torch.cuda.synchronize()
         t_roll += e[0].elapsed_time(e[1]); t_adv += e[1].elapsed_time(e[2]); t_upd += e[2].elapsed_time(e[3])
@@ -90,7 +101,7 @@ def main():
     if rank == 0:
         steps = n * ws * T * args.iters
         print(json.dumps({
-            "what": "PPO iterations (rollout + GAE + 4x4 minibatch update), ppo.py defaults, fused rollout path",
+            "what": "PPO iterations (rollout + GAE + 4x4 minibatch update), ppo.py defaults, fused rollout path, update=" + args.update,
             "n_gpus": ws, "envs_per_gpu": n, "rollout_steps": T, "iters": args.iters,
             "env_steps_per_s": steps / float(t.item()), "s_per_iter": float(t.item()) / args.iters,
             "ms_per_iter_rank0": {"rollout": t_roll / args.iters, "advantages_normalisers": t_adv / args.iters, "update": t_upd / args.iters},
