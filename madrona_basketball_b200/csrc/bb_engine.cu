@@ -1308,7 +1308,14 @@ int bb_ppo_grad(const bb_policy *pol, const bb_ppo_batch *batch, void *workspace
     bb::PpoArgs a{};
     a.b = *batch;
     a.invM = 1.0f / (float)batch->num_rows;
-    a.numTiles = (batch->num_rows + bb::kPpoRows - 1) / bb::kPpoRows;
+    /* equal shares: with t tiles per resident block, rows per tile = ceil(m / (blocks * t)) rounded up to a warp's 8 rows
+     * (65 536 rows on 296 blocks: 4 tiles of 56 rows instead of 3-or-4 tiles of 64) */
+    const int64_t tilesPerBlock = (batch->num_rows + (int64_t)maxBlocks * bb::kPpoRows - 1) / ((int64_t)maxBlocks * bb::kPpoRows);
+    int64_t rpt = (batch->num_rows + maxBlocks * tilesPerBlock - 1) / (maxBlocks * tilesPerBlock);
+    rpt = (rpt + 7) / 8 * 8;
+    if (rpt > bb::kPpoRows) rpt = bb::kPpoRows;
+    a.rowsPerTile = (int)rpt;
+    a.numTiles = (batch->num_rows + rpt - 1) / rpt;
     a.partials = (float *)workspace;
     const int blocks = (int)(a.numTiles < maxBlocks ? a.numTiles : maxBlocks);
     cudaStream_t st = (cudaStream_t)cuda_stream;

@@ -48,13 +48,13 @@ struct __align__(16) PpoSmem {
     float z[kPpoRows][kZS];    /* head outputs, then their gradients */
     float mean[BB_OBS_DIM], inv[BB_OBS_DIM];
     float b1[kH], g1[kH], e1[kH], b2[kH], g2[kH], e2[kH], bh[kZS];
-    float red[8][4];           /* loss statistics, one row per warp */
 };
 
 struct PpoArgs {
     bb_ppo_batch b;
     float invM;
     int64_t numTiles;
+    int rowsPerTile;          /* multiple of 8, <= kPpoRows: chosen so that the resident blocks get equal shares */
     float *partials;
 };
 
@@ -141,8 +141,9 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
 
     for (int64_t tile = blockIdx.x; tile < A.numTiles; tile += gridDim.x) {
         /* =========================== row phase =========================== */
-        const int64_t mrow = tile * kPpoRows + rb;
+        const int64_t mrow = tile * A.rowsPerTile + rb;
         const bool valid = mrow < B.num_rows;
+        if ((rb & ~7) < A.rowsPerTile) { /* warp-uniform: warps beyond the tile's rows only join the barriers */
         const int64_t src = B.indices ? B.indices[valid ? mrow : B.num_rows - 1] : (valid ? mrow : B.num_rows - 1);
         {   /* observation normaliser (agent.py:27-39): this thread's 8 of the row's 32 float4 chunks */
             const float4 *orow = reinterpret_cast<const float4 *>(B.obs + src * BB_OBS_DIM);
@@ -229,30 +230,29 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
         /* ---- loss (ppo.py:192-208) and its gradient w.r.t. the head outputs; buckets spread over the quad ---- */
         {
             float lpPart = 0.f, entPart = 0.f;
-            float p[2][8], lg[2][8], Hb[2] = {0.f, 0.f};
+            float Hb[2] = {0.f, 0.f};
             int act[2] = {0, 0};
 #pragma unroll
-            for (int s2 = 0; s2 < 2; s2++) {
+            for (int s2 = 0; s2 < 2; s2++) { /* pass 1: the row's logits become log-probabilities in place */
                 const int b = kQuadBuckets[q][s2];
                 if (b < 0) continue;
                 const int off = kBucketOff[b], cnt = kBucketCnt[b];
-                const float *l = &S.z[rb][off];
+                float *l = &S.z[rb][off];
                 float m = l[0];
                 for (int i = 1; i < cnt; i++) m = fmaxf(m, l[i]);
                 float s = 0.f;
                 for (int i = 0; i < cnt; i++) s += expf(l[i] - m);
                 const float lse = m + logf(s);
-                float h = 0.f;
-                for (int i = 0; i < cnt; i++) {
-                    const float lgp = l[i] - lse, pr = expf(lgp);
-                    lg[s2][i] = lgp; p[s2][i] = pr;
-                    h = fmaf(-pr, lgp, h);
-                }
                 int a = (int)B.actions[src * BB_NUM_ACTION_DIMS + b];
                 a = a < 0 ? 0 : (a >= cnt ? cnt - 1 : a);
                 act[s2] = a;
-                float la = lg[s2][0];
-                for (int i = 1; i < cnt; i++) if (i == a) la = lg[s2][i];
+                float h = 0.f, la = 0.f;
+                for (int i = 0; i < cnt; i++) {
+                    const float lgp = l[i] - lse;
+                    l[i] = lgp;
+                    h = fmaf(-expf(lgp), lgp, h);
+                    if (i == a) la = lgp;
+                }
                 lpPart += la;
                 Hb[s2] = h;
                 entPart += h;
@@ -276,9 +276,11 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
                 const int b = kQuadBuckets[q][s2];
                 if (b < 0) continue;
                 const int off = kBucketOff[b], cnt = kBucketCnt[b];
-                for (int i = 0; i < cnt; i++) {
+                float *l = &S.z[rb][off];
+                for (int i = 0; i < cnt; i++) { /* pass 2: log-probabilities become gradients */
+                    const float lgp = l[i], pr = expf(lgp);
                     const float oneHot = (i == act[s2]) ? 1.f : 0.f;
-                    S.z[rb][off + i] = fmaf(gLp, oneHot - p[s2][i], gEnt * p[s2][i] * (lg[s2][i] + Hb[s2]));
+                    l[i] = fmaf(gLp, oneHot - pr, gEnt * pr * (lgp + Hb[s2]));
                 }
             }
             if (q == 3) { /* critic (ppo.py:197-201): 0.5 * max((v - ret)^2, (v_old + clamp(v - v_old) - ret)^2) * vf_coef */
@@ -336,13 +338,14 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
 #pragma unroll
             for (int c = 0; c < kCh; c++) S.dh1[rb][4 * c + q] = d[c];
         }
+        } /* row phase */
         __syncthreads();
         /* =========================== tile phase: weight gradients =========================== */
         {
             const int cg = warp, kg = lane;            /* dW1 patch: channels 4cg.., inputs 4kg.. */
             const int j2 = tid >> 3, k42 = tid & 7;    /* dW2 / dWh patch: output j2, inputs 4k42.. */
 #pragma unroll 4
-            for (int r = 0; r < kPpoRows; r++) {
+            for (int r = 0; r < A.rowsPerTile; r++) {
                 const float4 dd = *reinterpret_cast<const float4 *>(&S.dh1[r][cg * 4]);
                 const float4 xx = *reinterpret_cast<const float4 *>(&S.x[r][kg * 4]);
                 gW1[0][0] = fmaf(dd.x, xx.x, gW1[0][0]); gW1[0][1] = fmaf(dd.x, xx.y, gW1[0][1]);
