@@ -475,4 +475,121 @@ __global__ void __launch_bounds__(kAdamThreads) bb_ppo_adam_kernel(float *params
     if (threadIdx.x == 0) { stepDev[0] = step; if (normOut) normOut[0] = norm; }
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * compute_advantages after the GAE scan (ppo.py:167-176): normaliser updates and advantage / value
+ * normalisation.  The reference (and ppo_dist.finish_advantages) does this with ~40 torch kernels, a
+ * float64 copy of the 262 144 x 128 observation batch and two host synchronisations (1.3 ms); here one
+ * pass computes every column's sum and sum of squares in float64 (bb_ppo_moments_kernel + a block-order
+ * reduction), the sums of all ranks are added with ONE all-reduce, a single block applies the
+ * RunningMeanStd updates (agent.py:41-51), and one elementwise kernel normalises the three buffers.
+ * ------------------------------------------------------------------------------------------------ */
+constexpr int kMomCols = BB_OBS_DIM + 3;      /* 128 observation columns, values, returns, advantages */
+constexpr int kMomThreads = 256;
+
+__global__ void __launch_bounds__(kMomThreads) bb_ppo_moments_kernel(const float *obs, const float *vals, const float *rets, const float *advs,
+                                                                     int64_t rows, double *partials)
+{
+    __shared__ double sh[kMomThreads / 32][BB_OBS_DIM][2];
+    __shared__ double sc[kMomThreads / 32][6];
+    const int tid = threadIdx.x, c4 = tid & 31, rsub = tid >> 5;
+    double s[4] = {0, 0, 0, 0}, q[4] = {0, 0, 0, 0};
+    for (int64_t r = (int64_t)blockIdx.x * 8 + rsub; r < rows; r += (int64_t)gridDim.x * 8) {
+        const float4 x = *reinterpret_cast<const float4 *>(obs + r * BB_OBS_DIM + c4 * 4);
+        s[0] += x.x; s[1] += x.y; s[2] += x.z; s[3] += x.w;
+        q[0] = fma((double)x.x, (double)x.x, q[0]); q[1] = fma((double)x.y, (double)x.y, q[1]);
+        q[2] = fma((double)x.z, (double)x.z, q[2]); q[3] = fma((double)x.w, (double)x.w, q[3]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) { sh[rsub][c4 * 4 + i][0] = s[i]; sh[rsub][c4 * 4 + i][1] = q[i]; }
+    double t[6] = {0, 0, 0, 0, 0, 0};
+    for (int64_t i = (int64_t)blockIdx.x * kMomThreads + tid; i < rows; i += (int64_t)gridDim.x * kMomThreads) {
+        const double v = vals[i], r = rets[i], a = advs[i];
+        t[0] += v; t[1] += r; t[2] += a;
+        t[3] = fma(v, v, t[3]); t[4] = fma(r, r, t[4]); t[5] = fma(a, a, t[5]);
+    }
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t[k] += __shfl_xor_sync(0xffffffffu, t[k], o);
+    }
+    if ((tid & 31) == 0) for (int k = 0; k < 6; k++) sc[tid >> 5][k] = t[k];
+    __syncthreads();
+    double *out = partials + (int64_t)blockIdx.x * 2 * kMomCols;
+    if (tid < BB_OBS_DIM) {
+        double a = 0, b = 0;
+        for (int w = 0; w < kMomThreads / 32; w++) { a += sh[w][tid][0]; b += sh[w][tid][1]; }
+        out[tid] = a; out[kMomCols + tid] = b;
+    } else if (tid < BB_OBS_DIM + 3) {
+        const int k = tid - BB_OBS_DIM;
+        double a = 0, b = 0;
+        for (int w = 0; w < kMomThreads / 32; w++) { a += sc[w][k]; b += sc[w][3 + k]; }
+        out[tid] = a; out[kMomCols + tid] = b;
+    }
+}
+
+__global__ void bb_ppo_moments_reduce_kernel(const double *partials, int numBlocks, double *sums)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= 2 * kMomCols) return;
+    double s = 0;
+    for (int b = 0; b < numBlocks; b++) s += partials[(int64_t)b * 2 * kMomCols + j];
+    sums[j] = s;
+}
+
+struct NormState { double *mean, *var, *count; };
+
+/* RunningMeanStd.update (agent.py:41-51) for one column given the batch's sum / sum of squares / count */
+BBD void rms_update(double sum, double sumsq, double n, double &mean, double &var, double &count)
+{
+    const double bmean = sum / n;
+    const double bvar = fmax(sumsq - n * bmean * bmean, 0.0) / fmax(n - 1.0, 1.0); /* unbiased, torch.var_mean */
+    const double tot = n + count;
+    const double delta = bmean - mean;
+    const double m = var * count + bvar * n + delta * delta * count * n / tot;
+    mean = mean + delta * n / tot;
+    var = m / tot;
+    count = tot;
+}
+
+/* one block: sums are GLOBAL (all ranks), n the global row count.  scal[4] = {adv mean, adv std + 1e-8, value mean f32, value rstd f32} */
+__global__ void __launch_bounds__(BB_OBS_DIM) bb_ppo_finish_stats_kernel(const double *sums, double n, NormState obsN, NormState valN,
+                                                                         float *obsMeanF, float *obsInvStdF, float *scal)
+{
+    const int c = threadIdx.x;
+    {
+        double mean = obsN.mean[c], var = obsN.var[c], count = obsN.count[0];
+        rms_update(sums[c], sums[kMomCols + c], n, mean, var, count);
+        obsN.mean[c] = mean; obsN.var[c] = var;
+        /* agent.py:28-30,36: float32 casts, then + epsilon, rsqrt */
+        obsMeanF[c] = (float)mean;
+        obsInvStdF[c] = rsqrtf((float)var + 1e-5f);
+        __syncthreads(); /* every thread has read the old count */
+        if (c == 0) obsN.count[0] = count;
+    }
+    if (c == 0) {
+        double mean = valN.mean[0], var = valN.var[0], count = valN.count[0];
+        rms_update(sums[BB_OBS_DIM + 0], sums[kMomCols + BB_OBS_DIM + 0], n, mean, var, count);   /* value_norm.update(values) */
+        rms_update(sums[BB_OBS_DIM + 1], sums[kMomCols + BB_OBS_DIM + 1], n, mean, var, count);   /* value_norm.update(returns) */
+        valN.mean[0] = mean; valN.var[0] = var; valN.count[0] = count;
+        const double am = sums[BB_OBS_DIM + 2] / n;
+        const double av = fmax(sums[kMomCols + BB_OBS_DIM + 2] - n * am * am, 0.0) / fmax(n - 1.0, 1.0);
+        scal[0] = (float)am;
+        scal[1] = (float)sqrt(av) + 1e-8f;
+        scal[2] = (float)mean;
+        scal[3] = rsqrtf((float)var + 1e-5f);
+    }
+}
+
+/* ppo.py:173-176 elementwise: advantages normalised; values / returns through the UPDATED value normaliser (clamped) */
+__global__ void bb_ppo_finish_apply_kernel(const float *scal, float clampV, float *vals, float *rets, float *advs, int64_t rows)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows) return;
+    const float am = scal[0], as = scal[1], vm = scal[2], vr = scal[3];
+    advs[i] = (advs[i] - am) / as;
+    float v = (vals[i] - vm) * vr, r = (rets[i] - vm) * vr;
+    if (clampV > 0.f) { v = fminf(fmaxf(v, -clampV), clampV); r = fminf(fmaxf(r, -clampV), clampV); }
+    vals[i] = v; rets[i] = r;
+}
+
 } // namespace bb
