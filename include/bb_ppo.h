@@ -78,6 +78,31 @@ int bb_ppo_adam(float *params, const float *grad, float *exp_avg, float *exp_avg
                 float grad_scale, float max_grad_norm, float lr, float beta1, float beta2, float eps,
                 float *grad_norm_out, void *cuda_stream);
 
+/* ---- compute_advantages after the GAE scan (ppo.py:167-176) ----
+ * BB_PPO_MOMENT_COLS columns: the 128 observation columns, then values (un-normalised), returns, advantages. */
+#define BB_PPO_MOMENT_COLS 131
+
+/* Bytes of scratch bb_ppo_moments needs on the current device. */
+int64_t bb_ppo_moments_workspace_bytes(void);
+
+/* One pass over this rank's rollout rows: sums_out[c] = sum over rows of column c, sums_out[131 + c] = sum of
+ * squares, float64, block-order reduction (bitwise reproducible).  Sums of several ranks add (one all-reduce). */
+int bb_ppo_moments(const float *obs, const float *values_unnorm, const float *returns, const float *advantages, int64_t rows,
+                   void *workspace, double *sums_out, void *cuda_stream);
+
+/* RunningMeanStd state (agent.py:24-26): float64 mean[dim], var[dim], count[1] on the device, updated in place. */
+typedef struct bb_running_norm { double *mean, *var, *count; } bb_running_norm;
+
+/* ppo.py:167-176 given GLOBAL sums over `global_rows` rows (all ranks): obs_norm.update(obs); value_norm.update(values);
+ * value_norm.update(returns) (agent.py:41-51, unbiased batch variance); advantages = (adv - mean) / (std + 1e-8);
+ * values, returns = value_norm(.) with the UPDATED statistics, clamped to +-value_clamp (agent.py:36-39), on this rank's
+ * `rows` elements in place.  obs_mean_f32 / obs_inv_std_f32 [128]: the float32 vectors bb_policy reads (agent.py:28-30,36).
+ * scratch: 4 floats on the device. */
+int bb_ppo_finish_advantages(const double *sums, double global_rows, const bb_running_norm *obs_norm,
+                             const bb_running_norm *value_norm, float *obs_mean_f32, float *obs_inv_std_f32, float value_clamp,
+                             float *values_unnorm, float *returns, float *advantages, int64_t rows, float *scratch,
+                             void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

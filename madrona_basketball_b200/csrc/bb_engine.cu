@@ -1337,4 +1337,43 @@ int bb_ppo_adam(float *params, const float *grad, float *exp_avg, float *exp_avg
     return 0;
 }
 
+int64_t bb_ppo_moments_workspace_bytes(void)
+{
+    int blocks = 0;
+    if (ppo_grid(&blocks) != 0) return -1;
+    return (int64_t)blocks * 2 * bb::kMomCols * (int64_t)sizeof(double);
+}
+
+int bb_ppo_moments(const float *obs, const float *values_unnorm, const float *returns, const float *advantages, int64_t rows,
+                   void *workspace, double *sums_out, void *cuda_stream)
+{
+    if (!obs || !values_unnorm || !returns || !advantages || rows <= 0 || !workspace || !sums_out) { set_error("bb_ppo_moments: bad arguments"); return -1; }
+    if (((uintptr_t)obs & 15) != 0) { set_error("bb_ppo_moments: obs must be 16-byte aligned"); return -1; }
+    int maxBlocks = 0;
+    if (ppo_grid(&maxBlocks) != 0) return -1;
+    const int64_t want = (rows + 7) / 8;
+    const int blocks = (int)(want < maxBlocks ? want : maxBlocks);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    bb::bb_ppo_moments_kernel<<<blocks, bb::kMomThreads, 0, st>>>(obs, values_unnorm, returns, advantages, rows, (double *)workspace);
+    BB_CUDA_OK(cudaGetLastError());
+    bb::bb_ppo_moments_reduce_kernel<<<(2 * bb::kMomCols + 63) / 64, 64, 0, st>>>((const double *)workspace, blocks, sums_out);
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int bb_ppo_finish_advantages(const double *sums, double global_rows, const bb_running_norm *obs_norm, const bb_running_norm *value_norm,
+                             float *obs_mean_f32, float *obs_inv_std_f32, float value_clamp, float *values_unnorm, float *returns,
+                             float *advantages, int64_t rows, float *scratch, void *cuda_stream)
+{
+    if (!sums || global_rows < 2.0 || !obs_norm || !value_norm || !obs_mean_f32 || !obs_inv_std_f32 || !values_unnorm || !returns ||
+        !advantages || rows <= 0 || !scratch) { set_error("bb_ppo_finish_advantages: bad arguments"); return -1; }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    bb::NormState on{obs_norm->mean, obs_norm->var, obs_norm->count}, vn{value_norm->mean, value_norm->var, value_norm->count};
+    bb::bb_ppo_finish_stats_kernel<<<1, BB_OBS_DIM, 0, st>>>(sums, global_rows, on, vn, obs_mean_f32, obs_inv_std_f32, scratch);
+    BB_CUDA_OK(cudaGetLastError());
+    bb::bb_ppo_finish_apply_kernel<<<(int)((rows + 255) / 256), 256, 0, st>>>(scratch, value_clamp, values_unnorm, returns, advantages, rows);
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
 } // extern "C"

@@ -23,6 +23,13 @@ PARAM_ORDER = ["backbone.0.weight", "backbone.0.bias", "backbone.1.weight", "bac
 _fp = ctypes.c_void_p
 
 
+class BBRunningNorm(ctypes.Structure):
+    _fields_ = [("mean", _fp), ("var", _fp), ("count", _fp)]
+
+
+MOMENT_COLS = 131   # include/bb_ppo.h BB_PPO_MOMENT_COLS
+
+
 class BBPpoBatch(ctypes.Structure):
     _fields_ = [("obs", _fp), ("actions", _fp), ("log_probs", _fp), ("values", _fp), ("advantages", _fp), ("returns", _fp),
                 ("indices", _fp), ("num_rows", ctypes.c_int64), ("clip_coef", ctypes.c_float), ("ent_coef", ctypes.c_float),
@@ -40,6 +47,13 @@ def _bind(lib):
     lib.bb_ppo_grad.argtypes = [ctypes.POINTER(BBPolicy), ctypes.POINTER(BBPpoBatch), vp, vp, vp, vp]
     lib.bb_ppo_adam.restype = ctypes.c_int
     lib.bb_ppo_adam.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int64, f32, f32, f32, f32, f32, f32, vp, vp]
+    lib.bb_ppo_moments_workspace_bytes.restype = ctypes.c_int64
+    lib.bb_ppo_moments_workspace_bytes.argtypes = []
+    lib.bb_ppo_moments.restype = ctypes.c_int
+    lib.bb_ppo_moments.argtypes = [vp, vp, vp, vp, ctypes.c_int64, vp, vp, vp]
+    lib.bb_ppo_finish_advantages.restype = ctypes.c_int
+    lib.bb_ppo_finish_advantages.argtypes = [vp, ctypes.c_double, ctypes.POINTER(BBRunningNorm), ctypes.POINTER(BBRunningNorm), vp, vp,
+                                             f32, vp, vp, vp, ctypes.c_int64, vp, vp]
     lib._ppo_bound = True
     return lib
 
@@ -88,6 +102,11 @@ class FusedPPO:
         if nbytes <= 0:
             raise RuntimeError("bb_ppo_workspace_bytes failed: " + _lib.last_error())
         self.workspace = torch.empty(nbytes // 4, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            mbytes = int(self._lib.bb_ppo_moments_workspace_bytes())
+        self.mom_workspace = torch.empty(mbytes // 8, dtype=torch.float64, device=dev)
+        self.mom_sums = torch.zeros(2 * MOMENT_COLS, dtype=torch.float64, device=dev)
+        self.mom_scratch = torch.zeros(4, dtype=torch.float32, device=dev)
         self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
         self.clip_coef, self.ent_coef, self.vf_coef = float(clip_coef), float(ent_coef), float(vf_coef)
         self.max_grad_norm = float(max_grad_norm)
@@ -128,7 +147,40 @@ class FusedPPO:
         if rc != 0:
             raise RuntimeError("bb_ppo_adam failed: " + _lib.last_error())
 
-    def update(self, buf, num_minibatches: int = 4, update_epochs: int = 4, generator=None) -> Dict[str, "object"]:
+    def finish_advantages(self, buf) -> None:
+        """The part of compute_advantages after the GAE scan (ppo.py:167-176; same contract as
+        ppo_dist.finish_advantages): expects buf.values_unnorm / advantages / returns from FusedRollout.gae; updates
+        agent.obs_norm and agent.value_norm (statistics over the rows of ALL ranks, one all-reduce of 262 doubles),
+        leaves advantages normalised and values_unnorm / returns in the value normaliser's scale, and refreshes the
+        float32 normaliser vectors self.weights points the kernels at.  Four kernels, no host synchronisation."""
+        import torch
+        import torch.distributed as dist
+
+        a = self.agent
+        for nrm in (a.obs_norm, a.value_norm):
+            assert nrm.mean.dtype == torch.float64 and nrm.mean.is_cuda and nrm.count.dtype == torch.float64
+        rows = buf.horizon * buf.n_envs
+        st = self._stream()
+        rc = self._lib.bb_ppo_moments(buf.obs.data_ptr(), buf.values_unnorm.data_ptr(), buf.returns.data_ptr(),
+                                      buf.advantages.data_ptr(), rows, self.mom_workspace.data_ptr(), self.mom_sums.data_ptr(), st)
+        if rc != 0:
+            raise RuntimeError("bb_ppo_moments failed: " + _lib.last_error())
+        ws = dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+        if ws > 1:
+            dist.all_reduce(self.mom_sums, op=dist.ReduceOp.SUM)   # every rank holds the same number of rows
+        on, vn = BBRunningNorm(), BBRunningNorm()
+        on.mean, on.var, on.count = a.obs_norm.mean.data_ptr(), a.obs_norm.var.data_ptr(), a.obs_norm.count.data_ptr()
+        vn.mean, vn.var, vn.count = a.value_norm.mean.data_ptr(), a.value_norm.var.data_ptr(), a.value_norm.count.data_ptr()
+        w = self.weights
+        rc = self._lib.bb_ppo_finish_advantages(self.mom_sums.data_ptr(), float(rows * ws), ctypes.byref(on), ctypes.byref(vn),
+                                                w._t["obs_mean"].data_ptr(), w._t["obs_inv_std"].data_ptr(),
+                                                float(getattr(a.value_norm, "clamp", 5.0)), buf.values_unnorm.data_ptr(),
+                                                buf.returns.data_ptr(), buf.advantages.data_ptr(), rows, self.mom_scratch.data_ptr(), st)
+        if rc != 0:
+            raise RuntimeError("bb_ppo_finish_advantages failed: " + _lib.last_error())
+
+    def update(self, buf, num_minibatches: int = 4, update_epochs: int = 4, generator=None,
+               refresh_normalizer: bool = True) -> Dict[str, "object"]:
         """ppo.py:180-216 on this rank's rollout buffers (rollout.RolloutBuffers after finish_advantages).  With
         torch.distributed initialised the flat gradient is summed across ranks (one all-reduce per step) and averaged."""
         import torch
@@ -141,7 +193,8 @@ class FusedPPO:
         act = buf.actions.view(-1, buf.actions.shape[-1])
         lp, v = buf.log_probs.view(-1), buf.values.view(-1)
         adv, ret = buf.advantages.view(-1), buf.returns.view(-1)
-        self.weights.refresh()   # the observation normaliser moved since the rollout (ppo.py:168)
+        if refresh_normalizer:   # the observation normaliser moved since the rollout (ppo.py:168); finish_advantages() already did it
+            self.weights.refresh()
         for _ in range(update_epochs):
             perm = torch.randperm(total, device=self.device, generator=generator)
             for start in range(0, mb * num_minibatches, mb):

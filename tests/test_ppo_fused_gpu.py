@@ -183,3 +183,45 @@ def test_fused_update_tracks_torch_update_policy():
     # the module's state_dict still carries the reference's checkpoint keys, now as views of the flat vector
     assert set(PARAM_ORDER) <= set(agent.state_dict().keys())
     assert named["actor.weight"].data_ptr() == fused.flat.data_ptr() + 4 * 5312
+
+
+def test_finish_advantages_matches_torch():
+    """ppo.py:167-176 (normaliser updates, advantage / value normalisation): fused kernels vs the torch float64
+    restatement in ppo_dist.finish_advantages.  Normaliser buffers (float64) rtol 1e-9; float32 outputs rtol 1e-5."""
+    import copy
+    import types
+
+    import torch
+
+    from madrona_basketball_b200 import ppo_dist
+    from madrona_basketball_b200.ppo_fused import FusedPPO
+
+    T, n = 8, 1111
+    agent = _agent(seed=33)
+    with torch.no_grad():
+        agent.value_norm.mean.fill_(1.7); agent.value_norm.var.fill_(9.0); agent.value_norm.count.fill_(5000.0)
+        agent.obs_norm.count.fill_(12345.0)
+    ref = copy.deepcopy(agent)
+    obs, _, _, _, g = _batch(T * n)
+    mk = lambda scale, shift: (torch.randn(T, n, generator=g, device="cuda") * scale + shift).contiguous()
+    buf = types.SimpleNamespace(horizon=T, n_envs=n, obs=obs.view(T, n, 128).contiguous(), values_unnorm=mk(3.0, 2.0),
+                                returns=mk(4.0, 1.0), advantages=mk(2.5, -0.7))
+    rbuf = types.SimpleNamespace(horizon=T, n_envs=n, obs=buf.obs.clone(), values_unnorm=buf.values_unnorm.clone(),
+                                 returns=buf.returns.clone(), advantages=buf.advantages.clone())
+    fused = FusedPPO(agent)
+    for it in range(2):   # twice: the second pass starts from the updated statistics
+        fused.finish_advantages(buf)
+        ppo_dist.finish_advantages(ref, rbuf)
+        torch.cuda.synchronize()
+        for name in ("obs_norm", "value_norm"):
+            a, r = getattr(agent, name), getattr(ref, name)
+            assert torch.allclose(a.mean, r.mean, rtol=1e-9, atol=1e-12), (name, "mean", it)
+            assert torch.allclose(a.var, r.var, rtol=1e-9, atol=1e-12), (name, "var", it)
+            assert torch.allclose(a.count, r.count, rtol=0, atol=0), (name, "count", it)
+        for f in ("advantages", "values_unnorm", "returns"):
+            assert torch.allclose(getattr(buf, f), getattr(rbuf, f), rtol=1e-5, atol=1e-6), (f, it)
+        w = fused.weights._t
+        assert torch.allclose(w["obs_mean"], ref.obs_norm.mean.float(), rtol=1e-6, atol=1e-7)
+        assert torch.allclose(w["obs_inv_std"], torch.rsqrt(ref.obs_norm.var.float() + 1e-5), rtol=1e-6)
+        # feed new (already normalised-scale) numbers back in for the second pass
+    assert abs(buf.advantages.mean().item()) < 1e-3 and abs(buf.advantages.std().item() - 1.0) < 1e-3

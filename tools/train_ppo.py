@@ -58,7 +58,7 @@ def main():
                          vf_coef=cfg.vf_coef, max_grad_norm=cfg.max_grad_norm)
     else:
         opt = torch.optim.Adam(agent.parameters(), lr=cfg.learning_rate, eps=1e-8)
-    weights = PolicyWeights.from_module(agent)
+    weights = fused.weights if args.update == "fused" else PolicyWeights.from_module(agent)
     buf = RolloutBuffers(T, n, dev)
     roll = FusedRollout(shard.sim, weights, args.trainee_idx, seed=args.seed, world_offset=shard.world_offset)
     gen = torch.Generator(device=dev).manual_seed(args.seed + rank)
@@ -79,12 +79,15 @@ def main():
         roll.collect(buf)                                               # ppo.py:60-141
         e[1].record()
         roll.gae(buf, cfg.gamma, cfg.gae_lambda, agent.value_norm.mean, agent.value_norm.var)   # ppo.py:144-166
-        ppo_dist.finish_advantages(agent, buf)                          # ppo.py:167-176
-        weights.refresh()                                               # the observation normaliser moved
+        if args.update == "fused":
+            fused.finish_advantages(buf)                                # ppo.py:167-176, incl. the float32 normaliser vectors
+        else:
+            ppo_dist.finish_advantages(agent, buf)
+            weights.refresh()                                           # the observation normaliser moved
         e[2].record()
         agent.train()
         if args.update == "fused":                                      # ppo.py:180-216
-            losses = fused.update(buf, cfg.num_minibatches, cfg.update_epochs, generator=gen)
+            losses = fused.update(buf, cfg.num_minibatches, cfg.update_epochs, generator=gen, refresh_normalizer=False)
         else:
             losses = ppo_dist.update_policy(agent, opt, buf, cfg, generator=gen)
         e[3].record()
