@@ -310,3 +310,31 @@ def test_full_size_million_world_stress_checksum_of_checksums():
     assert torch.isfinite(obs).all() and not obs[:, :, 103:].any()
     done = sim.done_tensor().to_torch()
     assert ((done == 0) | (done == 1)).all()
+
+
+def test_north_star_tolerance_against_glibc_arithmetic():
+    """north_star's own bar, against the arithmetic the reference's CPU executor would run (glibc libm instead of the
+    correctly rounded spec): 1000 steps of random actions, discrete state identical, agent position / velocity /
+    orientation within 1e-5 relative.  The ball integrates a velocity that differs by glibc's 1-ulp sinf / cosf errors
+    over flights of up to ~300 steps, so its position gets 1e-4 (measured worst: 1.5e-5)."""
+    import torch
+
+    n, steps = 64, 1000
+    sim, orc = make_engine(n), make_oracle(n, libm=True)
+    discrete = ["done", "agent_possession", "ball_physics", "ball_grabbed", "world_clock", "rng_count", "action_mask",
+                "action", "reset", "cur_step", "inbounding"]
+    for s in range(steps):
+        sim.fill_actions(SEED, s)
+        orc.fill_actions(SEED, s)
+        sim.step()
+        orc.step(num_threads=8)
+        if s % 50 == 49:
+            torch.cuda.synchronize()
+            e, o = engine_state(sim), orc.state()
+            for k in discrete:
+                assert np.array_equal(e[k], o[k]), (k, s)
+            for k, rtol in (("agent_pos", 1e-5), ("agent_velocity", 1e-5), ("orientation", 1e-5), ("basketball_pos", 1e-4),
+                            ("ball_velocity", 1e-5)):
+                err = np.abs(e[k] - o[k]) / np.maximum(np.abs(o[k]), 1.0)
+                assert err.max() <= rtol, (k, s, float(err.max()))
+    assert int(orc.tensor("rng_count").max()) > 3   # shots / resets happened
