@@ -1376,4 +1376,37 @@ int bb_ppo_finish_advantages(const double *sums, double global_rows, const bb_ru
     return 0;
 }
 
+static int64_t randperm_sort_bytes(int64_t n)
+{
+    size_t temp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, temp, (const uint32_t *)nullptr, (uint32_t *)nullptr, (const int32_t *)nullptr,
+                                    (int32_t *)nullptr, (int)n, 0, 32, (cudaStream_t)0);
+    return (int64_t)((temp + 255) / 256 * 256);
+}
+
+int64_t bb_randperm_workspace_bytes(int64_t n)
+{
+    if (n <= 0 || n > 0x7fffffff) return -1;
+    const int64_t arr = (n * 4 + 255) / 256 * 256; /* keys in, keys out, identity values */
+    return 3 * arr + randperm_sort_bytes(n);
+}
+
+int bb_randperm(int64_t n, uint32_t seed, uint32_t stream_id, void *workspace, int64_t workspace_bytes, int32_t *perm_out, void *cuda_stream)
+{
+    if (n <= 0 || n > 0x7fffffff || !workspace || !perm_out) { set_error("bb_randperm: bad arguments"); return -1; }
+    const int64_t arr = (n * 4 + 255) / 256 * 256;
+    const int64_t sortBytes = randperm_sort_bytes(n);
+    if (workspace_bytes < 3 * arr + sortBytes || ((uintptr_t)workspace & 255) != 0) { set_error("bb_randperm: workspace too small or misaligned"); return -1; }
+    char *w = (char *)workspace;
+    uint32_t *keysIn = (uint32_t *)w, *keysOut = (uint32_t *)(w + arr);
+    int32_t *valsIn = (int32_t *)(w + 2 * arr);
+    void *temp = w + 3 * arr;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    bb::bb_randperm_keys_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(keysIn, valsIn, n, seed, stream_id);
+    BB_CUDA_OK(cudaGetLastError());
+    size_t tb = (size_t)sortBytes;
+    BB_CUDA_OK(cub::DeviceRadixSort::SortPairs(temp, tb, keysIn, keysOut, valsIn, perm_out, (int)n, 0, 32, st));
+    return 0;
+}
+
 } // extern "C"

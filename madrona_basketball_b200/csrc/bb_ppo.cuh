@@ -23,6 +23,7 @@
  * (fp32) is the parity bar, so no reduced-precision tensor-core path.
  */
 #pragma once
+#include <cub/device/device_radix_sort.cuh>
 #include "../../include/bb_ppo.h"
 
 namespace bb {
@@ -144,7 +145,8 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
         const int64_t mrow = tile * A.rowsPerTile + rb;
         const bool valid = mrow < B.num_rows;
         if ((rb & ~7) < A.rowsPerTile) { /* warp-uniform: warps beyond the tile's rows only join the barriers */
-        const int64_t src = B.indices ? B.indices[valid ? mrow : B.num_rows - 1] : (valid ? mrow : B.num_rows - 1);
+        const int64_t mr = valid ? mrow : B.num_rows - 1;
+        const int64_t src = B.indices ? B.indices[mr] : (B.indices32 ? (int64_t)B.indices32[mr] : mr);
         {   /* observation normaliser (agent.py:27-39): this thread's 8 of the row's 32 float4 chunks */
             const float4 *orow = reinterpret_cast<const float4 *>(B.obs + src * BB_OBS_DIM);
 #pragma unroll
@@ -590,6 +592,17 @@ __global__ void bb_ppo_finish_apply_kernel(const float *scal, float clampV, floa
     float v = (vals[i] - vm) * vr, r = (rets[i] - vm) * vr;
     if (clampV > 0.f) { v = fminf(fmaxf(v, -clampV), clampV); r = fminf(fmaxf(r, -clampV), clampV); }
     vals[i] = v; rets[i] = r;
+}
+
+/* keys / identity values for bb_randperm */
+__global__ void bb_randperm_keys_kernel(uint32_t *keys, int32_t *vals, int64_t n, uint32_t seed, uint32_t stream)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t a, b;
+    threefry2x32(seed, stream, (uint32_t)i, 0u, a, b);
+    keys[i] = a;
+    vals[i] = (int32_t)i;
 }
 
 } // namespace bb

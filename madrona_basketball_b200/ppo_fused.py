@@ -33,7 +33,7 @@ MOMENT_COLS = 131   # include/bb_ppo.h BB_PPO_MOMENT_COLS
 class BBPpoBatch(ctypes.Structure):
     _fields_ = [("obs", _fp), ("actions", _fp), ("log_probs", _fp), ("values", _fp), ("advantages", _fp), ("returns", _fp),
                 ("indices", _fp), ("num_rows", ctypes.c_int64), ("clip_coef", ctypes.c_float), ("ent_coef", ctypes.c_float),
-                ("vf_coef", ctypes.c_float)]
+                ("vf_coef", ctypes.c_float), ("indices32", _fp)]
 
 
 def _bind(lib):
@@ -54,6 +54,10 @@ def _bind(lib):
     lib.bb_ppo_finish_advantages.restype = ctypes.c_int
     lib.bb_ppo_finish_advantages.argtypes = [vp, ctypes.c_double, ctypes.POINTER(BBRunningNorm), ctypes.POINTER(BBRunningNorm), vp, vp,
                                              f32, vp, vp, vp, ctypes.c_int64, vp, vp]
+    lib.bb_randperm_workspace_bytes.restype = ctypes.c_int64
+    lib.bb_randperm_workspace_bytes.argtypes = [ctypes.c_int64]
+    lib.bb_randperm.restype = ctypes.c_int
+    lib.bb_randperm.argtypes = [ctypes.c_int64, ctypes.c_uint32, ctypes.c_uint32, vp, ctypes.c_int64, vp, vp]
     lib._ppo_bound = True
     return lib
 
@@ -82,7 +86,7 @@ class FusedPPO:
     """clip-PPO minibatch steps on the flat parameter vector of an `Agent` (policy_torch.Agent / reference Agent)."""
 
     def __init__(self, agent, lr: float = 3e-4, betas=(0.9, 0.999), eps: float = 1e-8, clip_coef: float = 0.2,
-                 ent_coef: float = 0.01, vf_coef: float = 1.0, max_grad_norm: float = 1.0):
+                 ent_coef: float = 0.01, vf_coef: float = 1.0, max_grad_norm: float = 1.0, seed: int = 0):
         import torch
 
         self._lib = _bind(_lib.load())
@@ -110,6 +114,25 @@ class FusedPPO:
         self.lr, self.betas, self.eps = float(lr), (float(betas[0]), float(betas[1])), float(eps)
         self.clip_coef, self.ent_coef, self.vf_coef = float(clip_coef), float(ent_coef), float(vf_coef)
         self.max_grad_norm = float(max_grad_norm)
+        self.seed, self._perms = int(seed) & 0xFFFFFFFF, 0   # bb_randperm stream: one draw per epoch
+        self._perm_ws, self._perm_out = None, None
+
+    def randperm(self, n: int):
+        """torch.randperm(n) of ppo.py:186 as bb_randperm (Threefry keys + radix sort): int32 [n], a new draw per call."""
+        import torch
+
+        if self._perm_out is None or self._perm_out.numel() != n:
+            nbytes = int(self._lib.bb_randperm_workspace_bytes(n))
+            if nbytes <= 0:
+                raise RuntimeError("bb_randperm_workspace_bytes failed")
+            self._perm_ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            self._perm_out = torch.empty(n, dtype=torch.int32, device=self.device)
+        rc = self._lib.bb_randperm(n, self.seed, self._perms & 0xFFFFFFFF, self._perm_ws.data_ptr(), self._perm_ws.numel(),
+                                   self._perm_out.data_ptr(), self._stream())
+        if rc != 0:
+            raise RuntimeError("bb_randperm failed: " + _lib.last_error())
+        self._perms += 1
+        return self._perm_out
 
     def _stream(self):
         import torch
@@ -126,11 +149,16 @@ class FusedPPO:
         b = BBPpoBatch()
         b.obs, b.actions, b.log_probs = obs.data_ptr(), actions.data_ptr(), log_probs.data_ptr()
         b.values, b.advantages, b.returns = values.data_ptr(), advantages.data_ptr(), returns.data_ptr()
+        b.indices, b.indices32 = None, None
         if indices is not None:
-            assert indices.dtype == torch.int64 and indices.is_contiguous() and indices.is_cuda
-            b.indices, b.num_rows = indices.data_ptr(), indices.numel()
+            assert indices.dtype in (torch.int64, torch.int32) and indices.is_contiguous() and indices.is_cuda
+            if indices.dtype == torch.int64:
+                b.indices = indices.data_ptr()
+            else:
+                b.indices32 = indices.data_ptr()
+            b.num_rows = indices.numel()
         else:
-            b.indices, b.num_rows = None, obs.shape[0]
+            b.num_rows = obs.shape[0]
         b.clip_coef, b.ent_coef, b.vf_coef = self.clip_coef, self.ent_coef, self.vf_coef
         rc = self._lib.bb_ppo_grad(ctypes.byref(self.weights.c), ctypes.byref(b), self.workspace.data_ptr(), self.grad.data_ptr(),
                                    self.stats.data_ptr(), self._stream())
@@ -180,7 +208,7 @@ class FusedPPO:
             raise RuntimeError("bb_ppo_finish_advantages failed: " + _lib.last_error())
 
     def update(self, buf, num_minibatches: int = 4, update_epochs: int = 4, generator=None,
-               refresh_normalizer: bool = True) -> Dict[str, "object"]:
+               refresh_normalizer: bool = True, permutation: str = "fused") -> Dict[str, "object"]:
         """ppo.py:180-216 on this rank's rollout buffers (rollout.RolloutBuffers after finish_advantages).  With
         torch.distributed initialised the flat gradient is summed across ranks (one all-reduce per step) and averaged."""
         import torch
@@ -196,7 +224,8 @@ class FusedPPO:
         if refresh_normalizer:   # the observation normaliser moved since the rollout (ppo.py:168); finish_advantages() already did it
             self.weights.refresh()
         for _ in range(update_epochs):
-            perm = torch.randperm(total, device=self.device, generator=generator)
+            # one permutation of the rollout rows per epoch (ppo.py:186): bb_randperm, or torch's own stream
+            perm = self.randperm(total) if permutation == "fused" else torch.randperm(total, device=self.device, generator=generator)
             for start in range(0, mb * num_minibatches, mb):
                 self.gradient(obs, act, lp, v, adv, ret, perm[start:start + mb])
                 if ws > 1:

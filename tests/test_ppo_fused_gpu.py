@@ -225,3 +225,36 @@ def test_finish_advantages_matches_torch():
         assert torch.allclose(w["obs_inv_std"], torch.rsqrt(ref.obs_norm.var.float() + 1e-5), rtol=1e-6)
         # feed new (already normalised-scale) numbers back in for the second pass
     assert abs(buf.advantages.mean().item()) < 1e-3 and abs(buf.advantages.std().item() - 1.0) < 1e-3
+
+
+def test_randperm_is_a_permutation_and_looks_uniform():
+    """bb_randperm (ppo.py:186 torch.randperm): a permutation of 0..n-1, different per draw, reproducible per (seed,
+    draw), position-vs-value uncorrelated, and the minibatch gradient through int32 indices equals the int64 path."""
+    import torch
+
+    from madrona_basketball_b200.ppo_fused import FusedPPO
+
+    agent = _agent(seed=2)
+    fused, again = FusedPPO(agent, seed=11), FusedPPO(_agent(seed=2), seed=11)
+    for n in (262144, 1000, 37):
+        p1 = fused.randperm(n).clone()
+        p2 = fused.randperm(n).clone()
+        q1 = again.randperm(n).clone()
+        torch.cuda.synchronize()
+        assert p1.dtype == torch.int32 and torch.equal(torch.sort(p1.long())[0], torch.arange(n, device="cuda"))
+        assert torch.equal(torch.sort(p2.long())[0], torch.arange(n, device="cuda"))
+        assert not torch.equal(p1, p2) and torch.equal(p1, q1)
+        again.randperm(n)
+        if n >= 1000:
+            x = torch.arange(n, device="cuda", dtype=torch.float64)
+            r = torch.corrcoef(torch.stack([x, p1.double()]))[0, 1].item()
+            assert abs(r) < 5.0 / n ** 0.5                      # 5 sigma of the null distribution
+            fixed = (p1.long() == torch.arange(n, device="cuda")).sum().item()
+            assert fixed <= 8                                    # expected 1 fixed point
+    obs, act, adv, ret, g = _batch(5000)
+    lp_old, v_old = _behaviour(agent, obs, act, g, 0.2)
+    idx32 = fused.randperm(5000)[:2048].contiguous()
+    g32 = fused.gradient(obs, act, lp_old, v_old, adv, ret, idx32).clone()
+    g64 = fused.gradient(obs, act, lp_old, v_old, adv, ret, idx32.long().contiguous()).clone()
+    torch.cuda.synchronize()
+    assert torch.equal(g32, g64)

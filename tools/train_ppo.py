@@ -55,7 +55,7 @@ def main():
     if args.update == "fused":   # re-binds the parameters as views of one flat vector: before anything takes their pointers
         from madrona_basketball_b200.ppo_fused import FusedPPO
         fused = FusedPPO(agent, lr=cfg.learning_rate, eps=1e-8, clip_coef=cfg.clip_coef, ent_coef=cfg.ent_coef,
-                         vf_coef=cfg.vf_coef, max_grad_norm=cfg.max_grad_norm)
+                         vf_coef=cfg.vf_coef, max_grad_norm=cfg.max_grad_norm, seed=args.seed + 7919 * rank)
     else:
         opt = torch.optim.Adam(agent.parameters(), lr=cfg.learning_rate, eps=1e-8)
     weights = fused.weights if args.update == "fused" else PolicyWeights.from_module(agent)
