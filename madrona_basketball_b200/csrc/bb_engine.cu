@@ -1321,7 +1321,7 @@ int bb_ppo_grad(const bb_policy *pol, const bb_ppo_batch *batch, void *workspace
     cudaStream_t st = (cudaStream_t)cuda_stream;
     bb::bb_ppo_grad_kernel<<<blocks, bb::kPpoThreads, sizeof(bb::PpoSmem), st>>>(*pol, a);
     BB_CUDA_OK(cudaGetLastError());
-    bb::bb_ppo_reduce_kernel<<<(bb::kPpoPartial + 127) / 128, 128, 0, st>>>(a.partials, blocks, grad_out, stats_out);
+    bb::bb_ppo_reduce_kernel<<<(bb::kPpoPartial + bb::kRedCols - 1) / bb::kRedCols, bb::kRedCols * bb::kRedSlices, 0, st>>>(a.partials, blocks, grad_out, stats_out);
     BB_CUDA_OK(cudaGetLastError());
     return 0;
 }

@@ -418,23 +418,33 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
     }
 }
 
-/* grad[j] = sum over blocks (in block order) of partial[b][j]; the last BB_PPO_NUM_STATS entries go to stats */
-__global__ void bb_ppo_reduce_kernel(const float *partials, int numBlocks, float *grad, float *stats)
+/* grad[j] = sum over blocks of partial[b][j]; the last BB_PPO_NUM_STATS entries go to stats.  32 columns x 8 slices per
+ * block: slice s adds the partials b = s, s + 8, .. in order, the eight slice sums are added in slice order (a fixed
+ * summation tree: bitwise reproducible), and eight loads per column are in flight instead of one dependent chain. */
+constexpr int kRedCols = 32, kRedSlices = 8;
+__global__ void __launch_bounds__(kRedCols * kRedSlices) bb_ppo_reduce_kernel(const float *partials, int numBlocks, float *grad, float *stats)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= kPpoPartial) return;
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    int b = 0;
-    for (; b + 4 <= numBlocks; b += 4) {
-        s0 += partials[(int64_t)b * kPpoPartial + j];
-        s1 += partials[(int64_t)(b + 1) * kPpoPartial + j];
-        s2 += partials[(int64_t)(b + 2) * kPpoPartial + j];
-        s3 += partials[(int64_t)(b + 3) * kPpoPartial + j];
+    __shared__ float sh[kRedSlices][kRedCols];
+    const int c = threadIdx.x & (kRedCols - 1), sl = threadIdx.x / kRedCols;
+    const int j = blockIdx.x * kRedCols + c;
+    float s0 = 0.f, s1 = 0.f;
+    if (j < kPpoPartial) {
+        int b = sl;
+        for (; b + kRedSlices < numBlocks; b += 2 * kRedSlices) {
+            s0 += partials[(int64_t)b * kPpoPartial + j];
+            s1 += partials[(int64_t)(b + kRedSlices) * kPpoPartial + j];
+        }
+        if (b < numBlocks) s0 += partials[(int64_t)b * kPpoPartial + j];
     }
-    for (; b < numBlocks; b++) s0 += partials[(int64_t)b * kPpoPartial + j];
-    const float s = (s0 + s1) + (s2 + s3);
-    if (j < BB_PPO_NUM_PARAMS) grad[j] = s;
-    else if (stats) stats[j - BB_PPO_NUM_PARAMS] = s;
+    sh[sl][c] = s0 + s1;
+    __syncthreads();
+    if (sl == 0 && j < kPpoPartial) {
+        float s = 0.f;
+#pragma unroll
+        for (int k = 0; k < kRedSlices; k++) s += sh[k][c];
+        if (j < BB_PPO_NUM_PARAMS) grad[j] = s;
+        else if (stats) stats[j - BB_PPO_NUM_PARAMS] = s;
+    }
 }
 
 /* clip_grad_norm_ + Adam on a flat vector; one block (the policy has 5 972 parameters) */
