@@ -455,6 +455,9 @@ template <int kMaxT, bool kSync>
 __global__ void __launch_bounds__(kMaxT, BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_kernel(const __grid_constant__ StepParams p)
 {
     extern __shared__ float smem[];
+    /* programmatic dependent launch (bb_rollout): let the next kernel of the chain be scheduled early, and wait here for
+     * the previous one to complete; both are no-ops for an ordinary launch */
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float *warpImg = smem + warp * kWorldsPerWarp * kFeatStride;
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -774,8 +777,23 @@ void pick_launch_shape(int64_t n_worlds, int *threads, int *sync)
     if (*threads == 32) *sync = 0;
 }
 
+/* launch with programmaticStreamSerialization: the kernel may start while its predecessor in the stream is still
+ * running; it must griddepcontrol.wait before touching anything the predecessor writes (our step / policy kernels do) */
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), int blocks, int threads, size_t smem, cudaStream_t stream, bool pdl, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)blocks); cfg.blockDim = dim3((unsigned)threads);
+    cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, float *reward_out = nullptr,
-                float *done_out = nullptr, bool host_mapped = false)
+                float *done_out = nullptr, bool host_mapped = false, bool pdl = false)
 {
     bb::StepParams p = e->params;
     p.io.actionSrc = actions_dev;
@@ -787,7 +805,9 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
     const int threads = e->blockThreads;
     const int blocks = (int)((e->N * 2 + threads - 1) / threads);
     const int smem = bb::smem_bytes_for(threads);
-    if (threads <= 128) {
+    if (pdl && threads <= 128 && !e->phaseSync) {
+        BB_CUDA_OK(launch_pdl(bb::bb_step_kernel<128, false>, blocks, threads, (size_t)smem, stream, true, p));
+    } else if (threads <= 128) {
         if (e->phaseSync) bb::bb_step_kernel<128, true><<<blocks, threads, smem, stream>>>(p);
         else bb::bb_step_kernel<128, false><<<blocks, threads, smem, stream>>>(p);
     } else {
@@ -1179,7 +1199,7 @@ static int policy_ok(const bb_policy *p, const char *who)
     return 0;
 }
 
-static int launch_policy(const bb_policy *pol, const bb::PolicyIo &io, cudaStream_t stream)
+static int launch_policy(const bb_policy *pol, const bb::PolicyIo &io, cudaStream_t stream, bool pdl = false)
 {
     if (io.n <= 0) return 0;
     int dev = 0, sms = 148;
@@ -1187,7 +1207,8 @@ static int launch_policy(const bb_policy *pol, const bb::PolicyIo &io, cudaStrea
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int64_t blocks = (io.n + bb::kRowsPerBlock - 1) / bb::kRowsPerBlock;
     if (blocks > 4 * (int64_t)sms) blocks = 4 * (int64_t)sms; /* rows are strided over the resident blocks */
-    bb::bb_policy_kernel<<<(int)blocks, bb::kPolThreads, 0, stream>>>(*pol, io);
+    if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_policy_kernel, (int)blocks, bb::kPolThreads, (size_t)0, stream, true, *pol, io));
+    else bb::bb_policy_kernel<<<(int)blocks, bb::kPolThreads, 0, stream>>>(*pol, io);
     BB_CUDA_OK(cudaGetLastError());
     return 0;
 }
@@ -1220,6 +1241,7 @@ int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, 
     bb::bb_reset_prologue_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(C.reset, C.action, n, agent_idx);
     e->launches++;
     BB_CUDA_OK(cudaGetLastError());
+    static const bool pdl = [] { const char *s = getenv("BB_ROLLOUT_PDL"); return !(s && atoi(s) == 0); }();
     if (launch_step(e, nullptr, st) != 0) return -1;
     for (int t = 0; t <= T; t++) {
         bb::PolicyIo io{};
@@ -1243,7 +1265,7 @@ int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, 
         } else {
             io.resetCol = C.reset; /* env.py:182 resets.fill_(0) */
         }
-        if (launch_policy(trainee, io, st) != 0) return -1;
+        if (launch_policy(trainee, io, st, pdl) != 0) return -1;
         e->launches++;
         if (t == T) break;
         if (frozen) { /* env.py:126-143: the frozen policy drives the other agent from its own observation row */
@@ -1252,10 +1274,10 @@ int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, 
             fo.obs = C.obs + other * BB_OBS_DIM; fo.obsStride = 2 * BB_OBS_DIM; fo.n = n; fo.rowOffset = world_offset;
             fo.stochastic = 1; fo.seed = seed; fo.draw = 0x80000000u + draw_base + (uint32_t)t;
             fo.actionsOut = C.action + other * 6; fo.actionStride = 12;
-            if (launch_policy(frozen, fo, st) != 0) return -1;
+            if (launch_policy(frozen, fo, st, pdl) != 0) return -1;
             e->launches++;
         }
-        if (launch_step(e, nullptr, st) != 0) return -1;
+        if (launch_step(e, nullptr, st, nullptr, nullptr, false, pdl) != 0) return -1;
     }
     return 0;
 }

@@ -124,6 +124,9 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
         S.b2[j] = a ? P.b2[j] : 0.f; S.g2[j] = a ? P.ln2_g[j] : 0.f; S.e2[j] = a ? P.ln2_b[j] : 0.f;
     }
     if (tid >= 192 && tid < 192 + kHeads) S.bh[tid - 192] = (tid - 192) < BB_NUM_LOGITS ? P.ba[tid - 192] : P.bc[0];
+    /* programmatic dependent launch (bb_rollout): the weights above do not depend on the step kernel that precedes this
+     * launch in the stream; everything below does.  No-ops for an ordinary launch. */
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     __syncthreads();
 
     const int64_t rowStride = (int64_t)gridDim.x * kRowsPerBlock;
