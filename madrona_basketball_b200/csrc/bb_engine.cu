@@ -1341,10 +1341,10 @@ int bb_ppo_grad(const bb_policy *pol, const bb_ppo_batch *batch, void *workspace
     a.partials = (float *)workspace;
     const int blocks = (int)(a.numTiles < maxBlocks ? a.numTiles : maxBlocks);
     cudaStream_t st = (cudaStream_t)cuda_stream;
-    bb::bb_ppo_grad_kernel<<<blocks, bb::kPpoThreads, sizeof(bb::PpoSmem), st>>>(*pol, a);
-    BB_CUDA_OK(cudaGetLastError());
-    bb::bb_ppo_reduce_kernel<<<(bb::kPpoPartial + bb::kRedCols - 1) / bb::kRedCols, bb::kRedCols * bb::kRedSlices, 0, st>>>(a.partials, blocks, grad_out, stats_out);
-    BB_CUDA_OK(cudaGetLastError());
+    static const bool pdl = [] { const char *s = getenv("BB_PPO_PDL"); return !(s && atoi(s) == 0); }();
+    BB_CUDA_OK(launch_pdl(bb::bb_ppo_grad_kernel, blocks, bb::kPpoThreads, sizeof(bb::PpoSmem), st, pdl, *pol, a));
+    BB_CUDA_OK(launch_pdl(bb::bb_ppo_reduce_kernel, (bb::kPpoPartial + bb::kRedCols - 1) / bb::kRedCols, bb::kRedCols * bb::kRedSlices, (size_t)0, st, pdl,
+                          (const float *)a.partials, blocks, grad_out, stats_out));
     return 0;
 }
 
@@ -1353,9 +1353,9 @@ int bb_ppo_adam(float *params, const float *grad, float *exp_avg, float *exp_avg
                 void *cuda_stream)
 {
     if (!params || !grad || !exp_avg || !exp_avg_sq || !step_dev || n <= 0) { set_error("bb_ppo_adam: bad arguments"); return -1; }
-    bb::bb_ppo_adam_kernel<<<1, bb::kAdamThreads, 0, (cudaStream_t)cuda_stream>>>(params, grad, exp_avg, exp_avg_sq, step_dev, n, grad_scale,
-                                                                                 max_grad_norm, lr, beta1, beta2, eps, grad_norm_out);
-    BB_CUDA_OK(cudaGetLastError());
+    static const bool pdl = [] { const char *s = getenv("BB_PPO_PDL"); return !(s && atoi(s) == 0); }();
+    BB_CUDA_OK(launch_pdl(bb::bb_ppo_adam_kernel, 1, bb::kAdamThreads, (size_t)0, (cudaStream_t)cuda_stream, pdl, params, grad, exp_avg,
+                          exp_avg_sq, step_dev, n, grad_scale, max_grad_norm, lr, beta1, beta2, eps, grad_norm_out));
     return 0;
 }
 

@@ -98,6 +98,7 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
     extern __shared__ __align__(16) unsigned char ppoSmemRaw[];
     PpoSmem &S = *reinterpret_cast<PpoSmem *>(ppoSmemRaw);
     const int tid = threadIdx.x, q = tid & 3, rb = tid >> 2, lane = tid & 31, warp = tid >> 5;
+    asm volatile("griddepcontrol.wait;" ::: "memory"); /* programmatic dependent launch: the previous Adam step wrote the weights */
 
     /* ---- parameters -> shared memory ---- */
     for (int i = tid; i < kH * (BB_OBS_DIM / 4); i += kPpoThreads) {
@@ -425,6 +426,7 @@ constexpr int kRedCols = 32, kRedSlices = 8;
 __global__ void __launch_bounds__(kRedCols * kRedSlices) bb_ppo_reduce_kernel(const float *partials, int numBlocks, float *grad, float *stats)
 {
     __shared__ float sh[kRedSlices][kRedCols];
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int c = threadIdx.x & (kRedCols - 1), sl = threadIdx.x / kRedCols;
     const int j = blockIdx.x * kRedCols + c;
     float s0 = 0.f, s1 = 0.f;
@@ -455,6 +457,7 @@ __global__ void __launch_bounds__(kAdamThreads) bb_ppo_adam_kernel(float *params
 {
     __shared__ float red[kAdamThreads / 32];
     __shared__ float sNorm;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     float s = 0.f;
     for (int64_t i = threadIdx.x; i < n; i += kAdamThreads) { const float g = grad[i] * gradScale; s = fmaf(g, g, s); }
 #pragma unroll
