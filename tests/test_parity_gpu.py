@@ -338,3 +338,21 @@ def test_north_star_tolerance_against_glibc_arithmetic():
                 err = np.abs(e[k] - o[k]) / np.maximum(np.abs(o[k]), 1.0)
                 assert err.max() <= rtol, (k, s, float(err.max()))
     assert int(orc.tensor("rng_count").max()) > 3   # shots / resets happened
+
+
+def test_config2_8192_worlds_10000_steps_checksums():
+    """8192 worlds x 10 000 steps of random actions on one GPU (16 full 620-step episodes per
+    world, thousands of shots / resets): per-world checksums of the complete state against the oracle every 1000 steps."""
+    import torch
+
+    n, steps, every = 8192, 10000, 1000
+    sim, orc = make_engine(n), make_oracle(n)
+    for s0 in range(0, steps, every):
+        for s in range(s0, s0 + every):
+            sim.fill_actions(SEED, s)
+            sim.step()
+        orc.run_synthetic(SEED, s0, every, 0, 16)
+        ce = sim.checksum().cpu().numpy().view(np.uint64)
+        co = orc.checksum()
+        assert np.array_equal(ce, co), (s0 + every, int((ce != co).sum()))
+    assert int(orc.tensor("rng_count").min()) >= 3 + 3 * 15      # every world went through >= 15 resets
