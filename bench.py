@@ -260,6 +260,21 @@ def run_engine(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     warm_value = total_worlds * K / (float(t.item()) * 1e-3)
 
+    # ---------------------------------------------------------------- bb_step_n: the engine's own graph replay (informational)
+    # K steps as ONE CUDA-graph launch with programmatic-dependent-launch edges between the step kernels; the Action column is
+    # whatever hardCodeDefenseSystem leaves in it (the scripts/run.py loop: no host work between steps), L2 warm.
+    sim.step_n(K)
+    barrier()
+    with sampler:
+        e0.record()
+        sim.step_n(K)
+        e1.record()
+        barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    step_n_value = total_worlds * K / (float(t.item()) * 1e-3)
+
     # ---------------------------------------------------------------- e2e: host buffers through the C ABI
     # Every step takes its own action batch from pinned host memory (a ring of pre-filled pinned
     # buffers: the producer is not what is measured) and returns reward + done into pinned host memory.
@@ -370,6 +385,9 @@ def run_engine(args):
             "cpu_baseline": cpu_baseline,
             "l2_warm_graph": {"value": warm_value, "unit": UNIT,
                               "what": "same K steps replayed as one CUDA graph, no L2 flush (informational)"},
+            "graph_step_n": {"value": step_n_value, "unit": UNIT,
+                             "what": "K steps through bb_step_n: one CUDA-graph launch, programmatic dependent launch between the step "
+                                     "kernels, device-resident actions (scripts/run.py loop), no L2 flush (informational)"},
             "wall_s_timed_region": wall,
         }
         emit(line)

@@ -91,6 +91,13 @@ void bb_destroy(bb_engine *e);
  * `cuda_stream` (a cudaStream_t; 0 = legacy default stream).  Asynchronous. */
 int bb_step(bb_engine *e, void *cuda_stream);
 
+/* n consecutive Manager::step() calls with no host work in between (the loop of scripts/run.py:16-20, or the
+ * reference's own `for _ in range(n): sim.step()`), as ONE CUDA-graph launch: the n step kernels are captured once per
+ * n (programmatic-dependent-launch edges between consecutive steps: blocks of step k+1 start as blocks of step k
+ * retire and wait for its completion before touching state) and the instantiated graph is replayed on `cuda_stream`.
+ * The Action column is whatever the caller and hardCodeDefenseSystem left in it, exactly as with n bb_step calls. */
+int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream);
+
 /* bb_step, but Action is first taken from `actions_dev` (device, i32 [N,2,6]) —
  * the fused equivalent of `action_tensor.copy_(actions); step()`
  * (scripts/env.py:143,155).  actions_dev == NULL behaves like bb_step. */

@@ -10,7 +10,7 @@ LIB_PATH = os.environ.get("BB_LIB_PATH") or os.path.join(_HERE, "libbball.so")  
 
 # every symbol include/bb_engine.h declares
 SYMBOLS = [
-    "bb_create", "bb_destroy", "bb_step", "bb_step_with_actions", "bb_step_host", "bb_export",
+    "bb_create", "bb_destroy", "bb_step", "bb_step_n", "bb_step_with_actions", "bb_step_host", "bb_export",
     "bb_set_action", "bb_trigger_reset", "bb_fill_actions", "bb_checksum", "bb_launch_count",
     "bb_num_worlds", "bb_last_error", "bb_math_eval", "bb_serve_begin", "bb_serve_step", "bb_serve_end",
     "bb_serve_last_gpu_ns",
@@ -50,6 +50,8 @@ def load() -> ctypes.CDLL:
     lib.bb_destroy.argtypes = [vp]
     lib.bb_step.restype = ctypes.c_int
     lib.bb_step.argtypes = [vp, vp]
+    lib.bb_step_n.restype = ctypes.c_int
+    lib.bb_step_n.argtypes = [vp, i32, vp]
     lib.bb_step_with_actions.restype = ctypes.c_int
     lib.bb_step_with_actions.argtypes = [vp, vp, vp]
     lib.bb_step_host.restype = ctypes.c_int

@@ -682,6 +682,10 @@ struct bb_engine {
     cudaStream_t hostStream; /* bb_step_host / setters */
     int blockThreads, phaseSync, prefetchBlocks;
     int64_t launches;
+    /* bb_step_n: graph of stepGraphN step kernels */
+    cudaGraphExec_t stepGraphExec;
+    int32_t stepGraphN;
+    cudaStream_t captureStream;
     /* persistent server (bb_serve_*) */
     bb::ServeHostCtl *serveHost; /* mapped pinned */
     bb::ServeDevCtl *serveDev;
@@ -853,6 +857,9 @@ bb_engine *bb_create(const bb_config *cfg)
     e->N = cfg->num_worlds;
     e->Npad = (e->N + 31) / 32 * 32;
     e->launches = 0;
+    e->stepGraphExec = nullptr;
+    e->stepGraphN = 0;
+    e->captureStream = nullptr;
     e->serveHost = nullptr;
     e->serveDev = nullptr;
     e->serveStream = nullptr;
@@ -944,6 +951,8 @@ void bb_destroy(bb_engine *e)
     cudaSetDevice(e->cfg.gpu_id);
     bb_serve_end(e);
     if (e->serveStream) cudaStreamDestroy(e->serveStream);
+    if (e->stepGraphExec) cudaGraphExecDestroy(e->stepGraphExec);
+    if (e->captureStream) cudaStreamDestroy(e->captureStream);
     if (e->serveHost) cudaFreeHost(e->serveHost);
     if (e->serveDev) cudaFree(e->serveDev);
     cudaDeviceSynchronize();
@@ -953,6 +962,34 @@ void bb_destroy(bb_engine *e)
 }
 
 int bb_step(bb_engine *e, void *cuda_stream) { return launch_step(e, nullptr, (cudaStream_t)cuda_stream); }
+
+int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream)
+{
+    if (n <= 0) return 0;
+    if (e->serving) { set_error("bb_step_n: the persistent server is running (bb_serve_end first)"); return -1; }
+    if (!e->stepGraphExec || e->stepGraphN != n) {
+        if (e->stepGraphExec) { cudaGraphExecDestroy(e->stepGraphExec); e->stepGraphExec = nullptr; }
+        if (!e->captureStream) BB_CUDA_OK(cudaStreamCreateWithFlags(&e->captureStream, cudaStreamNonBlocking));
+        const int64_t launches0 = e->launches;
+        cudaGraph_t graph = nullptr;
+        for (int attempt = 0; attempt < 2 && !e->stepGraphExec; attempt++) {
+            const bool pdl = attempt == 0; /* second attempt: plain edges, should a driver refuse programmatic ones in capture */
+            BB_CUDA_OK(cudaStreamBeginCapture(e->captureStream, cudaStreamCaptureModeThreadLocal));
+            int rc = 0;
+            for (int32_t i = 0; i < n && rc == 0; i++) rc = launch_step(e, nullptr, e->captureStream, nullptr, nullptr, false, pdl && i > 0);
+            cudaError_t err = cudaStreamEndCapture(e->captureStream, &graph);
+            if (rc == 0 && err == cudaSuccess && cudaGraphInstantiate(&e->stepGraphExec, graph, 0) != cudaSuccess) e->stepGraphExec = nullptr;
+            if (graph) { cudaGraphDestroy(graph); graph = nullptr; }
+            cudaGetLastError();
+        }
+        e->launches = launches0;
+        if (!e->stepGraphExec) { set_error("bb_step_n: graph capture failed"); return -1; }
+        e->stepGraphN = n;
+    }
+    BB_CUDA_OK(cudaGraphLaunch(e->stepGraphExec, (cudaStream_t)cuda_stream));
+    e->launches += n;
+    return 0;
+}
 
 int bb_step_with_actions(bb_engine *e, const int32_t *actions_dev, void *cuda_stream)
 {

@@ -120,6 +120,10 @@ class SimpleGridworldSimulator:
         """Manager::step (mgr.cpp:243-246), enqueued on torch's current stream."""
         self._check(self._lib.bb_step(self._h, self._stream()), "bb_step")
 
+    def step_n(self, n: int) -> None:
+        """Extension: n consecutive step() calls as one CUDA-graph launch (bb_step_n)."""
+        self._check(self._lib.bb_step_n(self._h, int(n), self._stream()), "bb_step_n")
+
     def step_with_actions(self, actions) -> None:
         """Extension: `action_tensor.copy_(actions); step()` fused into the kernel's loads."""
         assert actions.is_cuda and actions.is_contiguous() and actions.numel() == self.num_worlds * 12

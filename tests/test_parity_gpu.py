@@ -356,3 +356,24 @@ def test_config2_8192_worlds_10000_steps_checksums():
         co = orc.checksum()
         assert np.array_equal(ce, co), (s0 + every, int((ce != co).sum()))
     assert int(orc.tensor("rng_count").min()) >= 3 + 3 * 15      # every world went through >= 15 resets
+
+
+@pytest.mark.parametrize("n", [300, 8192, 200000])
+def test_step_n_graph_replay_equals_separate_steps(n):
+    """bb_step_n: k steps as one CUDA-graph launch (programmatic dependent launch edges between the step kernels at
+    rollout sizes, plain edges with the large-batch kernel) == k separate step() calls, bit for bit; replay and
+    re-capture with another k included."""
+    import torch
+
+    a, b = make_engine(n), make_engine(n)
+    for s in range(5):                       # some non-trivial state and actions first
+        for sim in (a, b):
+            sim.fill_actions(SEED, s)
+            sim.step()
+    for k in (40, 40, 7, 1):
+        for _ in range(k):
+            a.step()
+        b.step_n(k)
+        torch.cuda.synchronize()
+        assert_states_equal(engine_state(b), engine_state(a), f"step_n N={n} k={k}")
+    assert a.launch_count() == b.launch_count()
