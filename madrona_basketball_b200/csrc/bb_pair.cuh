@@ -214,51 +214,61 @@ BBD void pair_reset_world(Lane &L, const SimConst &c)
     L.didReset = true;
 }
 
-/* agentCollisionSystem (game.cpp:537-648), pair (agent0, agent1); p0/q0, p1/q1 in agent order */
-BBD void pair_collision(Lane &L, Vec3 ca, Quat qa, Vec3 cb, Quat qb)
+/* agentCollisionSystem (game.cpp:537-648) for the pair (agent 0, agent 1), split over the two lanes: each lane builds
+ * its OWN agent's rectangle and tests the two separating axes that rectangle contributes (the reference's axis order is
+ * a.right, a.forward, b.right, b.forward: lane 0 holds axes 0-1, lane 1 axes 2-3), the partner's four vertices and the
+ * partial verdicts cross by shuffle.  The reference stops at the first separating axis and keeps the FIRST axis of
+ * least overlap (strict <): lane 0's candidate wins unless lane 1's overlap is strictly smaller. */
+BBD void pair_collision(Lane &L, Vec3 opos)
 {
     const float hw = kShoulderWidth / 2.0f, hd = kAgentDepth / 2.0f;
-    Vec3 fa = rotate_vec(qa, v3(0.f, 1.f, 0.f));
-    Vec3 ra = v3(fa.y, -fa.x, 0.f);
-    Vec3 hwa = ra * hw, hda = fa * hd;
-    Vec3 va[4] = {ca - hda + hwa, ca - hda - hwa, ca + hda - hwa, ca + hda + hwa};
-    Vec3 fb = rotate_vec(qb, v3(0.f, 1.f, 0.f));
-    Vec3 rb = v3(fb.y, -fb.x, 0.f);
-    Vec3 hwb = rb * hw, hdb = fb * hd;
-    Vec3 vb[4] = {cb - hdb + hwb, cb - hdb - hwb, cb + hdb - hwb, cb + hdb + hwb};
-    Vec3 axes[4] = {normalize(ra), normalize(fa), normalize(rb), normalize(fb)};
-    bool colliding = true;
-    float min_overlap = FLT_MAX;
+    const int me = L.me;
+    const Vec3 c = L.A.pos;
+    const Vec3 f = rotate_vec(L.A.q, v3(0.f, 1.f, 0.f));
+    const Vec3 r = v3(f.y, -f.x, 0.f);
+    const Vec3 hwv = r * hw, hdv = f * hd;
+    const Vec3 mv[4] = {c - hdv + hwv, c - hdv - hwv, c + hdv - hwv, c + hdv + hwv};
+    const Vec3 ov[4] = {xorv(mv[0]), xorv(mv[1]), xorv(mv[2]), xorv(mv[3])};
+    const Vec3 axes[2] = {normalize(r), normalize(f)};
+    bool coll = true;
+    float minOv = FLT_MAX;
     Vec3 mtv = v3(0.f, 0.f, 0.f);
 #pragma unroll
-    for (int j = 0; j < 4; j++) {
-        if (!colliding) continue;
-        Vec3 ax = axes[j];
-        float amin = dot(va[0], ax), amax = amin, bmin = dot(vb[0], ax), bmax = bmin;
+    for (int j = 0; j < 2; j++) {
+        const Vec3 ax = axes[j];
+        float amin = dot(mv[0], ax), amax = amin, bmin = dot(ov[0], ax), bmax = bmin;
 #pragma unroll
         for (int k = 1; k < 4; k++) {
-            float pa = dot(va[k], ax), pb = dot(vb[k], ax);
+            const float pa = dot(mv[k], ax), pb = dot(ov[k], ax);
             if (pa < amin) amin = pa;
             if (pa > amax) amax = pa;
             if (pb < bmin) bmin = pb;
             if (pb > bmax) bmax = pb;
         }
         if (!(amax > bmin && bmax > amin)) {
-            colliding = false;
+            coll = false;
         } else {
-            float overlap = fminf(amax, bmax) - fmaxf(amin, bmin);
-            if (overlap < min_overlap) { min_overlap = overlap; mtv = ax; }
+            const float overlap = fminf(amax, bmax) - fmaxf(amin, bmin);
+            if (coll && overlap < minOv) { minOv = overlap; mtv = ax; }
         }
     }
-    if (colliding) {
+    const bool ocoll = xori(coll ? 1 : 0) != 0;
+    const float oMin = xorf(minOv);
+    const Vec3 oMtv = xorv(mtv);
+    if (coll && ocoll) {
+        const float m0 = me ? oMin : minOv, m1 = me ? minOv : oMin;
+        const Vec3 t0 = sel(me != 0, oMtv, mtv), t1 = sel(me != 0, mtv, oMtv);
+        const bool second = m1 < m0;
+        const float min_overlap = second ? m1 : m0;
+        Vec3 corr = second ? t1 : t0;
         if (L.G.teamInPoss == (float)0) {
-            if (L.me == 0) L.A.reward -= 10.f; else L.A.reward += 10.f;
+            if (me == 0) L.A.reward -= 10.f; else L.A.reward += 10.f;
             L.resetNow = 1;
         }
-        Vec3 corr = mtv;
+        const Vec3 ca = sel(me == 0, c, opos), cb = sel(me == 0, opos, c);
         if (dot(cb - ca, corr) < 0.f) corr = -corr;
-        Vec3 shift = (corr * min_overlap) * 0.5f;
-        if (L.me == 0) L.A.pos = L.A.pos - shift; else L.A.pos = L.A.pos + shift;
+        const Vec3 shift = (corr * min_overlap) * 0.5f;
+        if (me == 0) L.A.pos = L.A.pos - shift; else L.A.pos = L.A.pos + shift;
     }
 }
 
@@ -418,10 +428,7 @@ BBD void pair_step_fast(Lane &L, const SimConst &c)
     A.pointsWorth = shot_point_value(A.pos, v3(me ? c.hoopX[0] : c.hoopX[1], c.hoopY, 0.f)); /* 15 */
     phase_sync<kSync>();
     opos = xorv(A.pos);
-    {                                  /* 16 collision */
-        Quat oq = xorq(A.q);
-        pair_collision(L, sel(me == 0, A.pos, opos), selq(me == 0, A.q, oq), sel(me == 0, opos, A.pos), selq(me == 0, oq, A.q));
-    }
+    pair_collision(L, opos);           /* 16 collision */
     phase_sync<kSync>();
     opos = xorv(A.pos);
     pair_defense(L, opos, xori(A.hasBall), c); /* 17 */
