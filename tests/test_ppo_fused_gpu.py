@@ -258,3 +258,64 @@ def test_randperm_is_a_permutation_and_looks_uniform():
     g64 = fused.gradient(obs, act, lp_old, v_old, adv, ret, idx32.long().contiguous()).clone()
     torch.cuda.synchronize()
     assert torch.equal(g32, g64)
+
+
+def test_fused_ppo_iterations_track_the_torch_path():
+    """Config 4 in miniature, twice on identical engines / policies / sampling streams: (a) fused rollout + GAE +
+    ppo_dist.finish_advantages + torch update_policy, (b) the same with FusedPPO.finish_advantages + FusedPPO.update fed
+    the SAME permutations (torch.randperm with equal generators).  After 3 iterations the parameters agree to 2e-3
+    absolute (different summation orders through Adam's normalisation, then through three rollouts of sampled actions
+    that may flip near a CDF edge) and the normalisers to 1e-6 relative; the kernels read the updated weights in place."""
+    import copy
+
+    import torch
+
+    from madrona_basketball_b200 import ppo_dist
+    from madrona_basketball_b200.policy_torch import Agent
+    from madrona_basketball_b200.ppo_fused import FusedPPO
+    from madrona_basketball_b200.rollout import FusedRollout, PolicyWeights, RolloutBuffers, policy_forward
+
+    torch.manual_seed(0)
+    n, T = 512, 16
+    dev = torch.device("cuda")
+    cfg = ppo_dist.PPOConfig(num_minibatches=2, update_epochs=2)
+    agent_t = Agent().to(dev)
+    agent_f = copy.deepcopy(agent_t)
+    sim_t, sim_f = make_engine(n), make_engine(n)
+    opt = torch.optim.Adam(agent_t.parameters(), lr=cfg.learning_rate, eps=1e-8)
+    fused = FusedPPO(agent_f, lr=cfg.learning_rate, eps=1e-8)
+    w_t = PolicyWeights.from_module(agent_t)
+    buf_t, buf_f = RolloutBuffers(T, n, dev), RolloutBuffers(T, n, dev)
+    roll_t, roll_f = FusedRollout(sim_t, w_t, 1, seed=9), FusedRollout(sim_f, fused.weights, 1, seed=9)
+    g_t, g_f = torch.Generator(device=dev).manual_seed(5), torch.Generator(device=dev).manual_seed(5)
+    for it in range(3):
+        roll_t.collect(buf_t)
+        roll_t.gae(buf_t, cfg.gamma, cfg.gae_lambda, agent_t.value_norm.mean, agent_t.value_norm.var)
+        ppo_dist.finish_advantages(agent_t, buf_t)
+        w_t.refresh()
+        ppo_dist.update_policy(agent_t, opt, buf_t, cfg, generator=g_t)
+
+        roll_f.collect(buf_f)
+        roll_f.gae(buf_f, cfg.gamma, cfg.gae_lambda, agent_f.value_norm.mean, agent_f.value_norm.var)
+        fused.finish_advantages(buf_f)
+        losses = fused.update(buf_f, cfg.num_minibatches, cfg.update_epochs, generator=g_f, refresh_normalizer=False,
+                              permutation="torch")
+        assert all(bool(torch.isfinite(v)) for v in losses.values())
+        if it == 0:   # the first rollout is identical, so the first iteration's inputs are too
+            assert torch.equal(buf_t.obs, buf_f.obs) and torch.equal(buf_t.actions, buf_f.actions)
+            assert torch.allclose(buf_t.advantages, buf_f.advantages, rtol=1e-5, atol=1e-6)
+    torch.cuda.synchronize()
+    for (k, a), (_, b) in zip(agent_t.named_parameters(), agent_f.named_parameters()):
+        assert torch.allclose(a, b, rtol=0, atol=2e-3), (k, float((a - b).abs().max()))
+    assert torch.allclose(agent_t.obs_norm.mean, agent_f.obs_norm.mean, rtol=1e-6, atol=1e-6)
+    assert float(agent_f.obs_norm.count) == 1.0 + 3 * n * T
+    # the fused path's own permutation stream also trains (finite, parameters move)
+    before = fused.flat.clone()
+    fused.update(buf_f, cfg.num_minibatches, cfg.update_epochs, refresh_normalizer=False)
+    torch.cuda.synchronize()
+    assert torch.isfinite(fused.flat).all() and not torch.equal(before, fused.flat)
+    obs = sim_f.observations_tensor().to_torch()[:, 1]
+    _, _, v_kernel, logits = policy_forward(fused.weights, obs, stochastic=False, want_logits=True)
+    with torch.no_grad():
+        x = agent_f.backbone(agent_f.obs_norm(obs))
+        assert torch.allclose(logits, agent_f.actor(x), rtol=1e-5, atol=2e-5)
