@@ -15,7 +15,10 @@
 
 namespace bb {
 
-constexpr int kPolThreads = 256;
+#ifndef BB_POL_THREADS
+#define BB_POL_THREADS 256
+#endif
+constexpr int kPolThreads = BB_POL_THREADS; /* multiple of 32, >= 224 (the staging code addresses threads 0..211) */
 constexpr int kHeads = BB_NUM_LOGITS + 1; /* 19 logits + value */
 
 struct PolicyIo {
