@@ -29,6 +29,8 @@ def main():
     ap.add_argument("--trainee-idx", type=int, default=1)   # ppo.py:34
     ap.add_argument("--seed", type=int, default=321)        # ppo.py:26
     ap.add_argument("--save", default=None, help="write the trained state_dict here (reference checkpoint format)")
+    ap.add_argument("--log-every", type=int, default=0,
+                    help="every K iterations read the episode statistics (one host sync) and record the window's mean return")
     ap.add_argument("--update", default="fused", choices=["fused", "torch"],
                     help="fused: bb_ppo_grad + bb_ppo_adam (3 kernels per minibatch step); torch: autograd + torch.optim.Adam as in the reference")
     args = ap.parse_args()
@@ -66,6 +68,7 @@ def main():
     ev = lambda: torch.cuda.Event(enable_timing=True)
     t_roll = t_adv = t_upd = 0.0
     losses = {}
+    curve, curve_prev = [], [0.0, 0.0, 0.0]
     for it in range(args.warmup + args.iters):
         if it == args.warmup:
             if ws > 1:
@@ -93,6 +96,12 @@ def main():
         e[3].record()
         torch.cuda.synchronize()
         t_roll += e[0].elapsed_time(e[1]); t_adv += e[1].elapsed_time(e[2]); t_upd += e[2].elapsed_time(e[3])
+        if args.log_every and (it + 1) % args.log_every == 0:   # learning curve: episodes finished in this window (this rank)
+            cur = buf.ep_sums.tolist()
+            d = [c - p for c, p in zip(cur, curve_prev)]
+            curve_prev = cur
+            if d[2] > 0:
+                curve.append({"iter": it + 1, "episodes": d[2], "mean_return": d[0] / d[2], "mean_length": d[1] / d[2]})
     wall = time.perf_counter() - wall0
     t = torch.tensor([wall], dtype=torch.float64, device=dev)
     if ws > 1:
@@ -111,6 +120,7 @@ def main():
             "episodes_finished": stats["episodes"], "mean_return": stats["return_sum"] / max(stats["episodes"], 1.0),
             "mean_episode_length": stats["length_sum"] / max(stats["episodes"], 1.0),
             "last_losses": {k: float(v) for k, v in losses.items()},
+            "learning_curve_rank0": curve,
         }))
     if ws > 1:
         dist.destroy_process_group()
