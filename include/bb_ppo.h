@@ -112,6 +112,28 @@ int64_t bb_randperm_workspace_bytes(int64_t n);
 int bb_randperm(int64_t n, uint32_t seed, uint32_t stream, void *workspace, int64_t workspace_bytes, int32_t *perm_out,
                 void *cuda_stream);
 
+/* ---- gradient all-reduce fused into the optimiser step, over NVLink peer memory (multi-GPU PPO) ----
+ * The reference is single-GPU; with one process per GPU the 24 KB flat gradient has to be summed across ranks before
+ * every Adam step (16 times per PPO iteration).  NCCL does that in ~30 us of latency per call; here the collective is
+ * part of the optimiser kernel: every rank publishes its gradient in a device buffer that its peers map through CUDA
+ * IPC, raises a sequence flag (release, system scope), waits for the peers' flags, and then reads all ranks' gradients
+ * straight from peer memory, adding them in rank order (every rank computes the same bits) before the clip + Adam
+ * arithmetic of bb_ppo_adam.  One kernel, one NVLink round trip, no NCCL call.
+ *
+ *   bb_p2p_create        allocates this rank's exchange buffer, returns an opaque context and writes the 64-byte CUDA IPC
+ *                        handle of the buffer to handle_out (exchange the handles with any host-side all-gather)
+ *   bb_p2p_connect       opens the peers' buffers (handles: world_size x 64 bytes in rank order)
+ *   bb_ppo_adam_p2p      bb_ppo_adam with grad := (1 / world_size) * sum over ranks of grad.  Every rank must call it the
+ *                        same number of times.  A peer that does not show up within timeout_ms makes the kernel give up
+ *                        WITHOUT applying the step and sets *error_flag_dev (int32, device) to 1. */
+typedef struct bb_p2p bb_p2p;
+bb_p2p *bb_p2p_create(int32_t rank, int32_t world_size, int64_t num_floats, unsigned char handle_out[64]);
+int bb_p2p_connect(bb_p2p *ctx, const unsigned char *handles);
+void bb_p2p_destroy(bb_p2p *ctx);
+int bb_ppo_adam_p2p(bb_p2p *ctx, float *params, const float *grad, float *exp_avg, float *exp_avg_sq, int32_t *step_dev, int64_t n,
+                    float max_grad_norm, float lr, float beta1, float beta2, float eps, float *grad_norm_out,
+                    int32_t *error_flag_dev, int32_t timeout_ms, void *cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1396,6 +1396,87 @@ int bb_ppo_adam(float *params, const float *grad, float *exp_avg, float *exp_avg
     return 0;
 }
 
+/* ---- gradient all-reduce over NVLink peer memory fused into the optimiser step (bb_ppo.h) ---- */
+struct bb_p2p {
+    int rank = 0, ws = 1, dev = 0;
+    int64_t stride = 0;           /* floats per parity slot */
+    uint32_t seq = 0;             /* calls made so far */
+    float *local = nullptr;       /* this rank's exchange buffer (cudaMalloc) */
+    bb::P2pPeers peers{};         /* every rank's buffer as seen from this device */
+    bool connected = false;
+};
+
+bb_p2p *bb_p2p_create(int32_t rank, int32_t world_size, int64_t num_floats, unsigned char handle_out[64])
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    if (world_size < 1 || world_size > bb::kP2pMaxRanks || rank < 0 || rank >= world_size || num_floats <= 0 || !handle_out) {
+        set_error("bb_p2p_create: bad arguments (world size 1..16)");
+        return nullptr;
+    }
+    if (num_floats > 8 * bb::kAdamThreads) { set_error("bb_p2p_create: at most 8192 floats"); return nullptr; }
+    bb_p2p *c = new bb_p2p();
+    c->rank = rank; c->ws = world_size;
+    c->stride = (num_floats + 31) / 32 * 32;
+    const size_t bytes = (size_t)(2 * c->stride) * sizeof(float) + 128;
+    cudaIpcMemHandle_t h;
+    if (cudaGetDevice(&c->dev) != cudaSuccess || cudaMalloc(&c->local, bytes) != cudaSuccess || cudaMemset(c->local, 0, bytes) != cudaSuccess ||
+        cudaDeviceSynchronize() != cudaSuccess || cudaIpcGetMemHandle(&h, c->local) != cudaSuccess) {
+        set_error(std::string("bb_p2p_create: ") + cudaGetErrorString(cudaGetLastError()));
+        if (c->local) cudaFree(c->local);
+        delete c;
+        return nullptr;
+    }
+    memcpy(handle_out, &h, 64);
+    c->peers.buf[rank] = c->local;
+    return c;
+}
+
+int bb_p2p_connect(bb_p2p *c, const unsigned char *handles)
+{
+    if (!c || !handles) { set_error("bb_p2p_connect: bad arguments"); return -1; }
+    if (c->connected) return 0;
+    for (int r = 0; r < c->ws; r++) {
+        if (r == c->rank) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handles + (size_t)r * 64, 64);
+        void *p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            set_error(std::string("bb_p2p_connect: cudaIpcOpenMemHandle(rank ") + std::to_string(r) + "): " + cudaGetErrorString(e));
+            return -1;
+        }
+        c->peers.buf[r] = (float *)p;
+    }
+    c->connected = true;
+    return 0;
+}
+
+void bb_p2p_destroy(bb_p2p *c)
+{
+    if (!c) return;
+    cudaDeviceSynchronize();
+    for (int r = 0; r < c->ws; r++)
+        if (r != c->rank && c->peers.buf[r]) cudaIpcCloseMemHandle(c->peers.buf[r]);
+    if (c->local) cudaFree(c->local);
+    delete c;
+}
+
+int bb_ppo_adam_p2p(bb_p2p *c, float *params, const float *grad, float *exp_avg, float *exp_avg_sq, int32_t *step_dev, int64_t n,
+                    float max_grad_norm, float lr, float beta1, float beta2, float eps, float *grad_norm_out, int32_t *error_flag_dev,
+                    int32_t timeout_ms, void *cuda_stream)
+{
+    if (!c || !params || !grad || !exp_avg || !exp_avg_sq || !step_dev || n <= 0 || n > c->stride) { set_error("bb_ppo_adam_p2p: bad arguments"); return -1; }
+    if (!c->connected && c->ws > 1) { set_error("bb_ppo_adam_p2p: bb_p2p_connect has not been called"); return -1; }
+    if (timeout_ms <= 0) timeout_ms = 2000;
+    static const bool pdl = [] { const char *s = getenv("BB_PPO_PDL"); return !(s && atoi(s) == 0); }();
+    c->seq += 1;
+    BB_CUDA_OK(launch_pdl(bb::bb_ppo_adam_p2p_kernel, 1, bb::kAdamThreads, (size_t)0, (cudaStream_t)cuda_stream, pdl, c->peers, c->rank, c->ws,
+                          c->stride, c->seq, params, grad, exp_avg, exp_avg_sq, step_dev, n, max_grad_norm, lr, beta1, beta2, eps,
+                          grad_norm_out, error_flag_dev, (uint64_t)timeout_ms * 1000000ull));
+    return 0;
+}
+
 int64_t bb_ppo_moments_workspace_bytes(void)
 {
     int blocks = 0;

@@ -618,4 +618,96 @@ __global__ void bb_randperm_keys_kernel(uint32_t *keys, int32_t *vals, int64_t n
     vals[i] = (int32_t)i;
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * bb_ppo_adam_p2p_kernel: one-shot all-reduce of the flat gradient over NVLink peer memory + clip + Adam.
+ * Exchange buffer of a rank (device memory, mapped by every peer through CUDA IPC):
+ *     float    grad[2][kP2pStride]   two parities, so that step s + 1 never overwrites what a slow peer still reads of step s
+ *     uint32_t flag[2]               sequence number last published in that parity
+ * A rank reaches the write of parity p for step s + 2 only after every peer has published step s + 1, which a peer does
+ * from a kernel launched after its step-s kernel finished reading: no reader can be overtaken.
+ * ------------------------------------------------------------------------------------------------ */
+constexpr int kP2pMaxRanks = 16;
+struct P2pPeers { float *buf[kP2pMaxRanks]; };
+BBD uint32_t ld_acquire_sys_u32(const uint32_t *p) { uint32_t v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+BBD void st_release_sys_u32(uint32_t *p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+BBD uint64_t p2p_timer_ns() { uint64_t t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
+__global__ void __launch_bounds__(kAdamThreads) bb_ppo_adam_p2p_kernel(const P2pPeers peers, int rank, int ws, int64_t stride, uint32_t seq,
+                                                                        float *params, const float *grad, float *m, float *v,
+                                                                        int32_t *stepDev, int64_t n, float maxNorm, float lr, float beta1,
+                                                                        float beta2, float eps, float *normOut, int32_t *errFlag,
+                                                                        uint64_t timeoutNs)
+{
+    __shared__ float red[kAdamThreads / 32];
+    __shared__ float sNorm;
+    __shared__ int sBad;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int par = (int)(seq & 1u);
+    float *mine = peers.buf[rank] + (int64_t)par * stride;
+    uint32_t *myFlag = reinterpret_cast<uint32_t *>(peers.buf[rank] + 2 * stride) + par;
+    if (threadIdx.x == 0) sBad = 0;
+    /* 1. publish this rank's gradient */
+    for (int64_t i = threadIdx.x; i < n; i += kAdamThreads) mine[i] = grad[i];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) st_release_sys_u32(myFlag, seq);
+    /* 2. wait for every peer's flag of this step (bounded: a missing peer must not hang the GPU) */
+    if (threadIdx.x < ws && threadIdx.x != rank) {
+        const uint32_t *f = reinterpret_cast<const uint32_t *>(peers.buf[threadIdx.x] + 2 * stride) + par;
+        const uint64_t t0 = p2p_timer_ns();
+        unsigned spins = 0;
+        while ((int32_t)(ld_acquire_sys_u32(f) - seq) < 0) {
+            if ((++spins & 255u) == 0 && p2p_timer_ns() - t0 > timeoutNs) { sBad = 1; break; }
+        }
+    }
+    __syncthreads();
+    if (sBad) { if (threadIdx.x == 0 && errFlag) *errFlag = 1; return; }
+    /* 3. sum in rank order straight from peer memory, clip, Adam (arithmetic of bb_ppo_adam_kernel) */
+    const float scale = 1.f / (float)ws;
+    constexpr int kPer = 8; /* up to 8 * 1024 parameters per call */
+    float g[kPer];
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < kPer; k++) {
+        const int64_t i = threadIdx.x + (int64_t)k * kAdamThreads;
+        float acc = 0.f;
+        if (i < n) {
+            for (int r = 0; r < ws; r++) acc += __ldcv(peers.buf[r] + (int64_t)par * stride + i);
+            acc *= scale;
+        }
+        g[k] = acc;
+        s = fmaf(acc, acc, s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float t = red[threadIdx.x];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (threadIdx.x == 0) sNorm = sqrtf(t);
+    }
+    __syncthreads();
+    const float norm = sNorm;
+    const float clip = maxNorm > 0.f ? fminf(maxNorm / (norm + 1e-6f), 1.f) : 1.f;
+    const int32_t step = stepDev[0] + 1;
+    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+    const float stepSize = (float)((double)lr / bc1);
+    const float bc2Sqrt = (float)sqrt(bc2);
+#pragma unroll
+    for (int k = 0; k < kPer; k++) {
+        const int64_t i = threadIdx.x + (int64_t)k * kAdamThreads;
+        if (i >= n) continue;
+        const float gi = g[k] * clip;
+        const float mi = m[i] + (gi - m[i]) * (1.f - beta1);
+        const float vi = fmaf(beta2, v[i], (1.f - beta2) * gi * gi);
+        m[i] = mi; v[i] = vi;
+        const float denom = sqrtf(vi) / bc2Sqrt + eps;
+        params[i] -= stepSize * (mi / denom);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { stepDev[0] = step; if (normOut) normOut[0] = norm; }
+}
+
 } // namespace bb

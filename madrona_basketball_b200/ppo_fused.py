@@ -58,6 +58,14 @@ def _bind(lib):
     lib.bb_randperm_workspace_bytes.argtypes = [ctypes.c_int64]
     lib.bb_randperm.restype = ctypes.c_int
     lib.bb_randperm.argtypes = [ctypes.c_int64, ctypes.c_uint32, ctypes.c_uint32, vp, ctypes.c_int64, vp, vp]
+    lib.bb_p2p_create.restype = vp
+    lib.bb_p2p_create.argtypes = [ctypes.c_int32, ctypes.c_int32, ctypes.c_int64, vp]
+    lib.bb_p2p_connect.restype = ctypes.c_int
+    lib.bb_p2p_connect.argtypes = [vp, vp]
+    lib.bb_p2p_destroy.restype = None
+    lib.bb_p2p_destroy.argtypes = [vp]
+    lib.bb_ppo_adam_p2p.restype = ctypes.c_int
+    lib.bb_ppo_adam_p2p.argtypes = [vp, vp, vp, vp, vp, vp, ctypes.c_int64, f32, f32, f32, f32, f32, vp, vp, ctypes.c_int32, vp]
     lib._ppo_bound = True
     return lib
 
@@ -116,6 +124,70 @@ class FusedPPO:
         self.max_grad_norm = float(max_grad_norm)
         self.seed, self._perms = int(seed) & 0xFFFFFFFF, 0   # bb_randperm stream: one draw per epoch
         self._perm_ws, self._perm_out = None, None
+        self._p2p, self._p2p_timeout_ms = None, 2000
+
+    def enable_p2p(self, timeout_ms: int = 2000) -> None:
+        """Multi-GPU: sum the gradient over NVLink peer memory inside the optimiser kernel (bb_ppo_adam_p2p) instead of one
+        NCCL all-reduce per minibatch step.  Collective call: every rank of the (single-node) default process group makes it
+        once, after torch.distributed is initialised; the 64-byte CUDA IPC handles travel through all_gather_object."""
+        import torch
+        import torch.distributed as dist
+
+        assert dist.is_available() and dist.is_initialized(), "enable_p2p needs an initialised process group"
+        ws, rank = dist.get_world_size(), dist.get_rank()
+        handle = (ctypes.c_ubyte * 64)()
+        with torch.cuda.device(self.device):
+            ctx = self._lib.bb_p2p_create(rank, ws, NUM_PARAMS, handle)
+        ok = [None] * ws
+        dist.all_gather_object(ok, bytes(handle) if ctx else None)
+        if any(h is None for h in ok):
+            if ctx:
+                self._lib.bb_p2p_destroy(ctx)
+            raise RuntimeError("bb_p2p_create failed on some rank: " + _lib.last_error())
+        blob = (ctypes.c_ubyte * (64 * ws)).from_buffer_copy(b"".join(ok))
+        with torch.cuda.device(self.device):
+            rc = self._lib.bb_p2p_connect(ctx, blob)
+        err = _lib.last_error() if rc != 0 else ""
+        rcs = [None] * ws
+        dist.all_gather_object(rcs, rc)          # also the barrier: every buffer is mapped before the first publish
+        if any(r != 0 for r in rcs):
+            self._lib.bb_p2p_destroy(ctx)
+            raise RuntimeError("bb_p2p_connect failed on some rank (CUDA IPC / peer access unavailable?): " + err)
+        self._p2p, self._p2p_timeout_ms = ctx, int(timeout_ms)
+        self.p2p_error = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._p2p_error_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._p2p_error_event = None
+
+    def disable_p2p(self) -> None:
+        """Collective: unmaps the peers' buffers (all ranks must have finished their updates)."""
+        import torch
+        import torch.distributed as dist
+
+        if self._p2p is None:
+            return
+        torch.cuda.synchronize(self.device)
+        self.check_p2p()
+        dist.barrier()
+        self._lib.bb_p2p_destroy(self._p2p)
+        self._p2p = None
+
+    def check_p2p(self) -> None:
+        """Raises if an earlier bb_ppo_adam_p2p gave up waiting for a peer (its Adam step was NOT applied)."""
+        if self._p2p is None or self._p2p_error_event is None:
+            return
+        self._p2p_error_event.synchronize()
+        if int(self._p2p_error_host[0]) != 0:
+            raise RuntimeError(f"bb_ppo_adam_p2p: a peer rank did not publish its gradient within {self._p2p_timeout_ms} ms; "
+                               "the parameters of the ranks have diverged")
+
+    def apply_p2p(self) -> None:
+        """all-reduce (mean over ranks, rank-order sum over NVLink peer memory) + clip_grad_norm_ + Adam in one kernel."""
+        rc = self._lib.bb_ppo_adam_p2p(self._p2p, self.flat.data_ptr(), self.grad.data_ptr(), self.exp_avg.data_ptr(),
+                                       self.exp_avg_sq.data_ptr(), self.step.data_ptr(), NUM_PARAMS, self.max_grad_norm, self.lr,
+                                       self.betas[0], self.betas[1], self.eps, self.grad_norm.data_ptr(), self.p2p_error.data_ptr(),
+                                       self._p2p_timeout_ms, self._stream())
+        if rc != 0:
+            raise RuntimeError("bb_ppo_adam_p2p failed: " + _lib.last_error())
 
     def randperm(self, n: int):
         """torch.randperm(n) of ppo.py:186 as bb_randperm (Threefry keys + radix sort): int32 [n], a new draw per call."""
@@ -221,6 +293,9 @@ class FusedPPO:
         act = buf.actions.view(-1, buf.actions.shape[-1])
         lp, v = buf.log_probs.view(-1), buf.values.view(-1)
         adv, ret = buf.advantages.view(-1), buf.returns.view(-1)
+        p2p = ws > 1 and self._p2p is not None
+        if p2p:
+            self.check_p2p()     # the flag copied at the end of the previous update
         if refresh_normalizer:   # the observation normaliser moved since the rollout (ppo.py:168); finish_advantages() already did it
             self.weights.refresh()
         for _ in range(update_epochs):
@@ -228,9 +303,16 @@ class FusedPPO:
             perm = self.randperm(total) if permutation == "fused" else torch.randperm(total, device=self.device, generator=generator)
             for start in range(0, mb * num_minibatches, mb):
                 self.gradient(obs, act, lp, v, adv, ret, perm[start:start + mb])
+                if p2p:
+                    self.apply_p2p()
+                    continue
                 if ws > 1:
                     dist.all_reduce(self.grad, op=dist.ReduceOp.SUM)
                 self.apply(1.0 / ws)
+        if p2p:
+            self._p2p_error_host.copy_(self.p2p_error, non_blocking=True)
+            self._p2p_error_event = torch.cuda.Event()
+            self._p2p_error_event.record(torch.cuda.current_stream(self.device))
         m = float(mb)
         return {"pg_loss": self.stats[0] / m, "v_loss": self.stats[1] / m * self.vf_coef,
                 "ent_loss": -self.stats[2] / m * self.ent_coef, "clip_frac": self.stats[3] / m, "grad_norm": self.grad_norm[0]}

@@ -33,6 +33,9 @@ def main():
                     help="every K iterations read the episode statistics (one host sync) and record the window's mean return")
     ap.add_argument("--update", default="fused", choices=["fused", "torch"],
                     help="fused: bb_ppo_grad + bb_ppo_adam (3 kernels per minibatch step); torch: autograd + torch.optim.Adam as in the reference")
+    ap.add_argument("--allreduce", default="p2p", choices=["p2p", "nccl"],
+                    help="multi-GPU fused update: p2p = gradient all-reduce inside the optimiser kernel over NVLink peer memory "
+                         "(bb_ppo_adam_p2p); nccl = one NCCL all-reduce per minibatch step + bb_ppo_adam")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -58,6 +61,8 @@ def main():
         from madrona_basketball_b200.ppo_fused import FusedPPO
         fused = FusedPPO(agent, lr=cfg.learning_rate, eps=1e-8, clip_coef=cfg.clip_coef, ent_coef=cfg.ent_coef,
                          vf_coef=cfg.vf_coef, max_grad_norm=cfg.max_grad_norm, seed=args.seed + 7919 * rank)
+        if ws > 1 and args.allreduce == "p2p":
+            fused.enable_p2p()
     else:
         opt = torch.optim.Adam(agent.parameters(), lr=cfg.learning_rate, eps=1e-8)
     weights = fused.weights if args.update == "fused" else PolicyWeights.from_module(agent)
@@ -113,7 +118,8 @@ def main():
     if rank == 0:
         steps = n * ws * T * args.iters
         print(json.dumps({
-            "what": "PPO iterations (rollout + GAE + 4x4 minibatch update), ppo.py defaults, fused rollout path, update=" + args.update,
+            "what": "PPO iterations (rollout + GAE + 4x4 minibatch update), ppo.py defaults, fused rollout path, update=" + args.update
+                    + (", allreduce=" + args.allreduce if (ws > 1 and args.update == "fused") else ""),
             "n_gpus": ws, "envs_per_gpu": n, "rollout_steps": T, "iters": args.iters,
             "env_steps_per_s": steps / float(t.item()), "s_per_iter": float(t.item()) / args.iters,
             "ms_per_iter_rank0": {"rollout": t_roll / args.iters, "advantages_normalisers": t_adv / args.iters, "update": t_upd / args.iters},
@@ -123,6 +129,8 @@ def main():
             "learning_curve_rank0": curve,
         }))
     if ws > 1:
+        if args.update == "fused":
+            fused.disable_p2p()
         dist.destroy_process_group()
 
 
