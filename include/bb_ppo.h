@@ -115,10 +115,11 @@ int bb_randperm(int64_t n, uint32_t seed, uint32_t stream, void *workspace, int6
 /* ---- gradient all-reduce fused into the optimiser step, over NVLink peer memory (multi-GPU PPO) ----
  * The reference is single-GPU; with one process per GPU the 24 KB flat gradient has to be summed across ranks before
  * every Adam step (16 times per PPO iteration).  NCCL does that in ~30 us of latency per call; here the collective is
- * part of the optimiser kernel: every rank publishes its gradient in a device buffer that its peers map through CUDA
- * IPC, raises a sequence flag (release, system scope), waits for the peers' flags, and then reads all ranks' gradients
- * straight from peer memory, adding them in rank order (every rank computes the same bits) before the clip + Adam
- * arithmetic of bb_ppo_adam.  One kernel, one NVLink round trip, no NCCL call.
+ * part of the optimiser kernel: every rank stores its gradient, as 8-byte words { value, sequence number }, straight into
+ * a slot of every peer's exchange buffer (device memory mapped through CUDA IPC; remote stores pipeline over NVLink), then
+ * polls its own local copy of the slots until every word carries the call's sequence number, and adds the ranks' values
+ * in rank order (every rank computes the same bits) before the clip + Adam arithmetic of bb_ppo_adam.  One kernel, one
+ * one-way NVLink trip, no fence, no NCCL call.
  *
  *   bb_p2p_create        allocates this rank's exchange buffer, returns an opaque context and writes the 64-byte CUDA IPC
  *                        handle of the buffer to handle_out (exchange the handles with any host-side all-gather)

@@ -1401,7 +1401,7 @@ struct bb_p2p {
     int rank = 0, ws = 1, dev = 0;
     int64_t stride = 0;           /* floats per parity slot */
     uint32_t seq = 0;             /* calls made so far */
-    float *local = nullptr;       /* this rank's exchange buffer (cudaMalloc) */
+    unsigned long long *local = nullptr; /* this rank's exchange buffer (cudaMalloc): [2][ws][stride] tagged words */
     bb::P2pPeers peers{};         /* every rank's buffer as seen from this device */
     bool connected = false;
 };
@@ -1413,11 +1413,11 @@ bb_p2p *bb_p2p_create(int32_t rank, int32_t world_size, int64_t num_floats, unsi
         set_error("bb_p2p_create: bad arguments (world size 1..16)");
         return nullptr;
     }
-    if (num_floats > 8 * bb::kAdamThreads) { set_error("bb_p2p_create: at most 8192 floats"); return nullptr; }
+    if (num_floats > bb::kP2pPer * bb::kAdamThreads) { set_error("bb_p2p_create: at most 6144 floats"); return nullptr; }
     bb_p2p *c = new bb_p2p();
     c->rank = rank; c->ws = world_size;
     c->stride = (num_floats + 31) / 32 * 32;
-    const size_t bytes = (size_t)(2 * c->stride) * sizeof(float) + 128;
+    const size_t bytes = (size_t)(2 * world_size * c->stride) * sizeof(unsigned long long);
     cudaIpcMemHandle_t h;
     if (cudaGetDevice(&c->dev) != cudaSuccess || cudaMalloc(&c->local, bytes) != cudaSuccess || cudaMemset(c->local, 0, bytes) != cudaSuccess ||
         cudaDeviceSynchronize() != cudaSuccess || cudaIpcGetMemHandle(&h, c->local) != cudaSuccess) {
@@ -1446,7 +1446,7 @@ int bb_p2p_connect(bb_p2p *c, const unsigned char *handles)
             set_error(std::string("bb_p2p_connect: cudaIpcOpenMemHandle(rank ") + std::to_string(r) + "): " + cudaGetErrorString(e));
             return -1;
         }
-        c->peers.buf[r] = (float *)p;
+        c->peers.buf[r] = (unsigned long long *)p;
     }
     c->connected = true;
     return 0;

@@ -620,16 +620,21 @@ __global__ void bb_randperm_keys_kernel(uint32_t *keys, int32_t *vals, int64_t n
 
 /* ------------------------------------------------------------------------------------------------
  * bb_ppo_adam_p2p_kernel: one-shot all-reduce of the flat gradient over NVLink peer memory + clip + Adam.
- * Exchange buffer of a rank (device memory, mapped by every peer through CUDA IPC):
- *     float    grad[2][kP2pStride]   two parities, so that step s + 1 never overwrites what a slow peer still reads of step s
- *     uint32_t flag[2]               sequence number last published in that parity
- * A rank reaches the write of parity p for step s + 2 only after every peer has published step s + 1, which a peer does
- * from a kernel launched after its step-s kernel finished reading: no reader can be overtaken.
+ * Push protocol, flag in the data (no fences, no separate flag round trip): the exchange buffer of a rank (device
+ * memory, mapped by every peer through CUDA IPC) is
+ *     uint64_t slot[2 parities][world_size writers][stride]       word = { float gradient element, uint32 sequence number }
+ * A rank stores its gradient, element by element as single 8-byte words tagged with the call's sequence number, into
+ * slot[seq & 1][its rank] of EVERY peer (remote stores are fire-and-forget and pipeline over NVLink), then polls its
+ * OWN copy of the slots (local L2) until every word carries the sequence number, and adds the ranks' values in rank
+ * order, so every rank computes the same bits.  8-byte stores are single-copy atomic: a word with the right tag holds
+ * the right value.  Two parities: a rank writes step s + 2 into a slot only after it finished step s + 1, which needed
+ * the owner's step s + 1 words, which the owner sends after its step-s kernel (the reader of that slot) has ended.
  * ------------------------------------------------------------------------------------------------ */
 constexpr int kP2pMaxRanks = 16;
-struct P2pPeers { float *buf[kP2pMaxRanks]; };
-BBD uint32_t ld_acquire_sys_u32(const uint32_t *p) { uint32_t v; asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
-BBD void st_release_sys_u32(uint32_t *p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+constexpr int kP2pPer = 6;   /* elements per thread: up to 6 * 1024 parameters */
+struct P2pPeers { unsigned long long *buf[kP2pMaxRanks]; };
+BBD unsigned long long ld_volatile_u64(const unsigned long long *p) { unsigned long long v; asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory"); return v; }
+BBD void st_volatile_u64(unsigned long long *p, unsigned long long v) { asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 BBD uint64_t p2p_timer_ns() { uint64_t t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 
 __global__ void __launch_bounds__(kAdamThreads) bb_ppo_adam_p2p_kernel(const P2pPeers peers, int rank, int ws, int64_t stride, uint32_t seq,
@@ -641,43 +646,79 @@ __global__ void __launch_bounds__(kAdamThreads) bb_ppo_adam_p2p_kernel(const P2p
     __shared__ float red[kAdamThreads / 32];
     __shared__ float sNorm;
     __shared__ int sBad;
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    const int par = (int)(seq & 1u);
-    float *mine = peers.buf[rank] + (int64_t)par * stride;
-    uint32_t *myFlag = reinterpret_cast<uint32_t *>(peers.buf[rank] + 2 * stride) + par;
     if (threadIdx.x == 0) sBad = 0;
-    /* 1. publish this rank's gradient */
-    for (int64_t i = threadIdx.x; i < n; i += kAdamThreads) mine[i] = grad[i];
-    __threadfence_system();
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int64_t parOff = (int64_t)(seq & 1u) * ws * stride;
+    /* 1. push this rank's gradient into its slot at every peer */
+    float own[kP2pPer];
+#pragma unroll
+    for (int k = 0; k < kP2pPer; k++) {
+        const int64_t i = threadIdx.x + (int64_t)k * kAdamThreads;
+        own[k] = i < n ? grad[i] : 0.f;
+    }
+    for (int d = 1; d < ws; d++) {
+        int r = rank + d; if (r >= ws) r -= ws;     /* staggered: the ranks do not all hit the same peer first */
+        unsigned long long *dst = peers.buf[r] + parOff + (int64_t)rank * stride;
+#pragma unroll
+        for (int k = 0; k < kP2pPer; k++) {
+            const int64_t i = threadIdx.x + (int64_t)k * kAdamThreads;
+            if (i < n) st_volatile_u64(dst + i, ((unsigned long long)seq << 32) | (unsigned long long)__float_as_uint(own[k]));
+        }
+    }
     __syncthreads();
-    if (threadIdx.x == 0) st_release_sys_u32(myFlag, seq);
-    /* 2. wait for every peer's flag of this step (bounded: a missing peer must not hang the GPU) */
-    if (threadIdx.x < ws && threadIdx.x != rank) {
-        const uint32_t *f = reinterpret_cast<const uint32_t *>(peers.buf[threadIdx.x] + 2 * stride) + par;
-        const uint64_t t0 = p2p_timer_ns();
+    /* 2. gather from the local slots, two writers at a time, summing in rank order (bounded wait) */
+    const unsigned long long *mine = peers.buf[rank] + parOff;
+    float g[kP2pPer];
+#pragma unroll
+    for (int k = 0; k < kP2pPer; k++) g[k] = 0.f;
+    const uint64_t t0 = p2p_timer_ns();
+    for (int r0 = 0; r0 < ws; r0 += 2) {
+        unsigned long long w[2][kP2pPer];
         unsigned spins = 0;
-        while ((int32_t)(ld_acquire_sys_u32(f) - seq) < 0) {
-            if ((++spins & 255u) == 0 && p2p_timer_ns() - t0 > timeoutNs) { sBad = 1; break; }
+        bool pending = true;
+        while (pending) {
+            pending = false;
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int r = r0 + j;
+                if (r >= ws || r == rank) continue;
+#pragma unroll
+                for (int k = 0; k < kP2pPer; k++) {
+                    const int64_t i = threadIdx.x + (int64_t)k * kAdamThreads;
+                    if (i < n) w[j][k] = ld_volatile_u64(mine + (int64_t)r * stride + i);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int r = r0 + j;
+                if (r >= ws || r == rank) continue;
+#pragma unroll
+                for (int k = 0; k < kP2pPer; k++) {
+                    const int64_t i = threadIdx.x + (int64_t)k * kAdamThreads;
+                    if (i < n && (uint32_t)(w[j][k] >> 32) != seq) pending = true;
+                }
+            }
+            if (pending && (++spins & 63u) == 0 && p2p_timer_ns() - t0 > timeoutNs) { sBad = 1; break; }
+        }
+        if (pending) break;
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            const int r = r0 + j;
+            if (r >= ws) continue;
+#pragma unroll
+            for (int k = 0; k < kP2pPer; k++) {
+                const int64_t i = threadIdx.x + (int64_t)k * kAdamThreads;
+                if (i < n) g[k] += (r == rank) ? own[k] : __uint_as_float((uint32_t)w[j][k]);
+            }
         }
     }
     __syncthreads();
     if (sBad) { if (threadIdx.x == 0 && errFlag) *errFlag = 1; return; }
-    /* 3. sum in rank order straight from peer memory, clip, Adam (arithmetic of bb_ppo_adam_kernel) */
+    /* 3. clip + Adam (arithmetic of bb_ppo_adam_kernel with gradScale = 1 / ws) */
     const float scale = 1.f / (float)ws;
-    constexpr int kPer = 8; /* up to 8 * 1024 parameters per call */
-    float g[kPer];
     float s = 0.f;
 #pragma unroll
-    for (int k = 0; k < kPer; k++) {
-        const int64_t i = threadIdx.x + (int64_t)k * kAdamThreads;
-        float acc = 0.f;
-        if (i < n) {
-            for (int r = 0; r < ws; r++) acc += __ldcv(peers.buf[r] + (int64_t)par * stride + i);
-            acc *= scale;
-        }
-        g[k] = acc;
-        s = fmaf(acc, acc, s);
-    }
+    for (int k = 0; k < kP2pPer; k++) { g[k] *= scale; s = fmaf(g[k], g[k], s); }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
@@ -696,7 +737,7 @@ __global__ void __launch_bounds__(kAdamThreads) bb_ppo_adam_p2p_kernel(const P2p
     const float stepSize = (float)((double)lr / bc1);
     const float bc2Sqrt = (float)sqrt(bc2);
 #pragma unroll
-    for (int k = 0; k < kPer; k++) {
+    for (int k = 0; k < kP2pPer; k++) {
         const int64_t i = threadIdx.x + (int64_t)k * kAdamThreads;
         if (i >= n) continue;
         const float gi = g[k] * clip;
