@@ -19,8 +19,11 @@
  *               dW2 = dH2^T A1, dWh = dZ^T A2), each thread owning a register patch of the output.
  *   epilogue    every block writes its partial gradient (all 5 972 + 4 entries) to the workspace;
  *               bb_ppo_reduce_kernel adds the partials in block order.  No atomics: bitwise reproducible.
- * fp32 FFMA: 26 kFLOP per row, 1.7 GFLOP per minibatch of 65 536 rows; agreement with torch autograd
- * (fp32) is the parity bar, so no reduced-precision tensor-core path.
+ * 26 kFLOP per row, 1.7 GFLOP per minibatch of 65 536 rows.  Agreement with torch autograd (fp32) is the parity
+ * bar, so the matrix products run on the tensor cores as 3xTF32 (mma.sync m16n8k8, every operand split hi + lo,
+ * three products, fp32 accumulation: fp32-level accuracy), see quad_mma_tf32x3 / mma_tf32x3 below: the plain FFMA
+ * version was bound by shared-memory bandwidth (73 % of the LSU wavefront peak in ncu), the fragment layout of
+ * mma.sync reads each shared value once per warp instead of once per quad.  129 -> 89 us per minibatch.
  */
 #pragma once
 #include <cub/device/device_radix_sort.cuh>
@@ -91,6 +94,111 @@ BBD void ppo_ln_bwd(float (&d)[kCh], const float (&xhat)[kCh], float rstd, const
     s2 = quad_sum(s2) * (1.f / kH);
 #pragma unroll
     for (int c = 0; c < kCh; c++) d[c] = rstd * (d[c] - s1 - xhat[c] * s2);
+}
+
+/* ---- row-phase GEMVs on the tensor cores, fp32-accurate (3xTF32) ----
+ * ncu (profiles/r01g_ppo_grad_*) showed the FFMA version bound by shared-memory bandwidth (73 % of the LSU wavefront
+ * peak): a quad thread loaded 9 float4 per 32 FFMA, and broadcast does not multiply the 128 B/clk a warp can receive.
+ * mma.sync.m16n8k8 shares fragments across the warp instead: the warp's 8 rows are rows 0..7 of the A tile (rows 8..15
+ * are zero registers, never loaded), thread (g = lane >> 2, t = lane & 3) loads x[row g][k0 + t], x[row g][k0 + t + 4]
+ * and, per 8-channel tile j, w[ch][k0 + t], w[ch][k0 + t + 4] with ch = 8j + 4 (g & 1) + (g >> 1).  That column
+ * permutation makes the accumulator pair the thread receives (tile columns 2t, 2t + 1) the channels 4 (2j) + t and
+ * 4 (2j + 1) + t — exactly the quad mapping (channel 4c + q) of the surrounding code, so nothing else moves.
+ * Every operand is split x = hi + lo with hi = tf32(x), lo = tf32(x - hi) and the product is lo*hi + hi*lo + hi*hi,
+ * accumulated in fp32: ~2^-21 relative per product, inside the parity bar against torch fp32 autograd. */
+#ifndef BB_PPO_MMA
+#define BB_PPO_MMA 63   /* bit 0: layer 1, 1: layer 2, 2: heads, 3: backward heads, 4: backward layer 2, 5: weight gradients (tile phase) */
+#endif
+#ifndef BB_PPO_TRUNC_SPLIT
+#define BB_PPO_TRUNC_SPLIT 1
+#endif
+#ifndef BB_PPO_SPLITACC
+#define BB_PPO_SPLITACC 0
+#endif
+BBD void tf32_split(float x, uint32_t &hi, uint32_t &lo)
+{
+#if BB_PPO_TRUNC_SPLIT
+    hi = __float_as_uint(x) & 0xffffe000u;                 /* the tensor core reads only the top 19 bits anyway */
+    lo = __float_as_uint(x - __uint_as_float(hi));         /* exact; its own low bits are dropped by the hardware (2^-21 |x|) */
+#else
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+    const float r = x - __uint_as_float(hi);
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+#endif
+}
+BBD void mma_tf32_half(float &c0, float &c1, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1)
+{
+    float d2, d3;
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%10,%10};"
+                 : "+f"(c0), "+f"(c1), "=f"(d2), "=f"(d3)
+                 : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1), "f"(0.f));
+}
+/* full-tile 3xTF32 product for the weight-gradient GEMMs: c += A(16x8) B(8x8), operands pre-split */
+BBD void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2])
+{
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+BBD void mma_tf32x3(float (&c)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4], const uint32_t (&bh)[2], const uint32_t (&bl)[2])
+{
+    mma_tf32(c, al, bh);
+    mma_tf32(c, ah, bl);
+    mma_tf32(c, ah, bh);
+}
+/* A fragment of G^T for the k-step whose eight rows are r0..r0+7: A[m][k] = G[row(k)][m0 + m] with row(t) = r0 + 2t,
+ * row(t + 4) = r0 + 2t + 1 (any bijection works as long as B uses the same one; this one is bank-conflict free for
+ * the 36- and 132-float row strides) */
+template <int STR>
+BBD void load_a_frag(const float *G, int ra, int m0, int g, uint32_t (&ah)[4], uint32_t (&al)[4])
+{
+    tf32_split(G[ra * STR + m0 + g], ah[0], al[0]);
+    tf32_split(G[ra * STR + m0 + g + 8], ah[1], al[1]);
+    tf32_split(G[(ra + 1) * STR + m0 + g], ah[2], al[2]);
+    tf32_split(G[(ra + 1) * STR + m0 + g + 8], ah[3], al[3]);
+}
+template <int STR>
+BBD void load_b_frag(const float *X, int ra, int n0, int g, uint32_t (&bh)[2], uint32_t (&bl)[2])
+{
+    tf32_split(X[ra * STR + n0 + g], bh[0], bl[0]);
+    tf32_split(X[(ra + 1) * STR + n0 + g], bh[1], bl[1]);
+}
+/* out[2j + e] += sum_k W[(8j + 4e + q) * WSTR + k] * xrow[k], k < K (multiple of 8), j < NT; all 32 lanes must call it */
+template <int K, int WSTR, int NT>
+BBD void quad_mma_tf32x3(const float *xrow, const float *W, int lane, float (&out)[2 * NT])
+{
+    const int g = lane >> 2, t = lane & 3;
+    const float *wbase = W + (4 * (g & 1) + (g >> 1)) * WSTR + t;
+#if BB_PPO_SPLITACC
+    float lo[2 * NT];   /* the two correction terms get their own accumulators: two independent MMA chains per tile */
+#pragma unroll
+    for (int i = 0; i < 2 * NT; i++) lo[i] = 0.f;
+#endif
+#pragma unroll 4
+    for (int k0 = 0; k0 < K; k0 += 8) {
+        uint32_t a0h, a0l, a2h, a2l;
+        tf32_split(xrow[k0 + t], a0h, a0l);
+        tf32_split(xrow[k0 + t + 4], a2h, a2l);
+#pragma unroll
+        for (int j = 0; j < NT; j++) {
+            const float *w = wbase + 8 * j * WSTR + k0;
+            uint32_t b0h, b0l, b1h, b1l;
+            tf32_split(w[0], b0h, b0l);
+            tf32_split(w[4], b1h, b1l);
+#if BB_PPO_SPLITACC
+            mma_tf32_half(lo[2 * j], lo[2 * j + 1], a0l, a2l, b0h, b1h);
+            mma_tf32_half(lo[2 * j], lo[2 * j + 1], a0h, a2h, b0l, b1l);
+#else
+            mma_tf32_half(out[2 * j], out[2 * j + 1], a0l, a2l, b0h, b1h);
+            mma_tf32_half(out[2 * j], out[2 * j + 1], a0h, a2h, b0l, b1l);
+#endif
+            mma_tf32_half(out[2 * j], out[2 * j + 1], a0h, a2h, b0h, b1h);
+        }
+    }
+#if BB_PPO_SPLITACC
+#pragma unroll
+    for (int i = 0; i < 2 * NT; i++) out[i] += lo[i];
+#endif
 }
 
 __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_policy P, const PpoArgs A)
@@ -172,6 +280,9 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
         {
 #pragma unroll
             for (int c = 0; c < kCh; c++) xh1[c] = S.b1[4 * c + q];
+#if BB_PPO_MMA & 1
+            quad_mma_tf32x3<BB_OBS_DIM, kXS, kCh / 2>(&S.x[rb][0], &S.w1[0][0], lane, xh1);
+#else
 #pragma unroll 4
             for (int k4 = 0; k4 < BB_OBS_DIM / 4; k4++) {
                 const float4 x = *reinterpret_cast<const float4 *>(&S.x[rb][k4 * 4]);
@@ -181,6 +292,7 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
                     xh1[c] = fmaf(w.w, x.w, fmaf(w.z, x.z, fmaf(w.y, x.y, fmaf(w.x, x.x, xh1[c]))));
                 }
             }
+#endif
             rstd1 = ppo_ln_fwd(xh1);
 #pragma unroll
             for (int c = 0; c < kCh; c++) {
@@ -194,6 +306,9 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
         {
 #pragma unroll
             for (int c = 0; c < kCh; c++) xh2[c] = S.b2[4 * c + q];
+#if BB_PPO_MMA & 2
+            quad_mma_tf32x3<kH, kHS, kCh / 2>(&S.a1[rb][0], &S.w2[0][0], lane, xh2);
+#else
 #pragma unroll
             for (int k4 = 0; k4 < kH / 4; k4++) {
                 const float4 h = *reinterpret_cast<const float4 *>(&S.a1[rb][k4 * 4]);
@@ -203,6 +318,7 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
                     xh2[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, xh2[c]))));
                 }
             }
+#endif
             rstd2 = ppo_ln_fwd(xh2);
 #pragma unroll
             for (int c = 0; c < kCh; c++) {
@@ -214,6 +330,16 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
         __syncwarp();
         /* ---- heads: outputs q, q+4, .., q+16 of (19 actor logits | critic) ---- */
         {
+#if BB_PPO_MMA & 4
+            float o[6];   /* o[5] = "output" 20 + q: rows of the next array, computed and dropped */
+#pragma unroll
+            for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
+            o[5] = 0.f;
+            quad_mma_tf32x3<kH, kHS, 3>(&S.a2[rb][0], &S.wh[0][0], lane, o);
+#pragma unroll
+            for (int c = 0; c < kHeadPerThread; c++) S.z[rb][4 * c + q] = o[c];
+            S.z[rb][20 + q] = 0.f;   /* the padding the backward K = 24 product reads */
+#else
             float o[kHeadPerThread];
 #pragma unroll
             for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
@@ -228,6 +354,7 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
             }
 #pragma unroll
             for (int c = 0; c < kHeadPerThread; c++) S.z[rb][4 * c + q] = o[c];
+#endif
         }
         __syncwarp();
         /* ---- loss (ppo.py:192-208) and its gradient w.r.t. the head outputs; buckets spread over the quad ---- */
@@ -309,6 +436,9 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
             float d[kCh];
 #pragma unroll
             for (int c = 0; c < kCh; c++) d[c] = 0.f;
+#if (BB_PPO_MMA & 12) == 12
+            quad_mma_tf32x3<kZS, kZS, kCh / 2>(&S.z[rb][0], &S.wht[0][0], lane, d);
+#else
 #pragma unroll
             for (int j4 = 0; j4 < kHeads / 4; j4++) {
                 const float4 g = *reinterpret_cast<const float4 *>(&S.z[rb][j4 * 4]);
@@ -318,6 +448,7 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
                     d[c] = fmaf(w.w, g.w, fmaf(w.z, g.z, fmaf(w.y, g.y, fmaf(w.x, g.x, d[c]))));
                 }
             }
+#endif
 #pragma unroll
             for (int c = 0; c < kCh; c++) if (!((mask2 >> c) & 1u)) d[c] = 0.f;
             ppo_ln_bwd(d, xh2, rstd2, S.g2, q, dg2, de2);
@@ -326,6 +457,9 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
             __syncwarp();
 #pragma unroll
             for (int c = 0; c < kCh; c++) d[c] = 0.f;
+#if BB_PPO_MMA & 16
+            quad_mma_tf32x3<kH, kHS, kCh / 2>(&S.dh2[rb][0], &S.w2t[0][0], lane, d);
+#else
 #pragma unroll
             for (int k4 = 0; k4 < kH / 4; k4++) {
                 const float4 g = *reinterpret_cast<const float4 *>(&S.dh2[rb][k4 * 4]);
@@ -335,6 +469,7 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
                     d[c] = fmaf(w.w, g.w, fmaf(w.z, g.z, fmaf(w.y, g.y, fmaf(w.x, g.x, d[c]))));
                 }
             }
+#endif
 #pragma unroll
             for (int c = 0; c < kCh; c++) if (!((mask1 >> c) & 1u)) d[c] = 0.f;
             ppo_ln_bwd(d, xh1, rstd1, S.g1, q, dg1, de1);
@@ -344,6 +479,46 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
         } /* row phase */
         __syncthreads();
         /* =========================== tile phase: weight gradients =========================== */
+#if BB_PPO_MMA & 32
+        {   /* dW1 = dH1^T X, dW2 = dH2^T A1, dWh = dZ^T A2 as 3xTF32 tensor-core products over the tile's rows (k = rows, 8 per step).
+             * Warp w owns dW1[all 32 channels][inputs 16w .. 16w+15] (2 x 2 accumulator tiles = the 16 registers the FFMA patch had),
+             * one 16 x 8 tile of dW2 and one of dWh (m-tile w >> 2, n-tile w & 3). */
+            const int g = lane >> 2, t = lane & 3, mt2 = warp >> 2, nt2 = warp & 3;
+            for (int r0 = 0; r0 < A.rowsPerTile; r0 += 8) {
+                const int ra = r0 + 2 * t;
+                uint32_t bh[2][2], bl[2][2];
+#pragma unroll
+                for (int nt = 0; nt < 2; nt++) load_b_frag<kXS>(&S.x[0][0], ra, 16 * warp + 8 * nt, g, bh[nt], bl[nt]);
+#pragma unroll
+                for (int mt = 0; mt < 2; mt++) {
+                    uint32_t ah[4], al[4];
+                    load_a_frag<kHS>(&S.dh1[0][0], ra, 16 * mt, g, ah, al);
+#pragma unroll
+                    for (int nt = 0; nt < 2; nt++) mma_tf32x3(gW1[2 * mt + nt], ah, al, bh[nt], bl[nt]);
+                }
+                {
+                    uint32_t ah[4], al[4], b2h[2], b2l[2];
+                    load_a_frag<kHS>(&S.dh2[0][0], ra, 16 * mt2, g, ah, al);
+                    load_b_frag<kHS>(&S.a1[0][0], ra, 8 * nt2, g, b2h, b2l);
+                    mma_tf32x3(gW2, ah, al, b2h, b2l);
+                    /* heads: m-tile 1 covers outputs 16..31 of which 20..23 are the zero padding and 24..31 (the next row's entries) are dropped */
+                    load_a_frag<kZS>(&S.z[0][0], ra, 16 * mt2, g, ah, al);
+                    load_b_frag<kHS>(&S.a2[0][0], ra, 8 * nt2, g, b2h, b2l);
+                    mma_tf32x3(gWh, ah, al, b2h, b2l);
+                }
+                if (tid >= 160 && tid < 160 + 2 * kH + kHeads) { /* biases: b1 | b2 | head biases */
+                    const int tb = tid - 160;
+                    const float *col = tb < kH ? &S.dh1[0][tb] : (tb < 2 * kH ? &S.dh2[0][tb - kH] : &S.z[0][tb - 2 * kH]);
+                    const int str = tb < 2 * kH ? kHS : kZS;
+                    float v[8];
+#pragma unroll
+                    for (int rr = 0; rr < 8; rr++) v[rr] = col[(r0 + rr) * str];
+#pragma unroll
+                    for (int rr = 0; rr < 8; rr++) gB += v[rr];
+                }
+            }
+        }
+#else
         {
             const int cg = warp, kg = lane;            /* dW1 patch: channels 4cg.., inputs 4kg.. */
             const int j2 = tid >> 3, k42 = tid & 7;    /* dW2 / dWh patch: output j2, inputs 4k42.. */
@@ -374,12 +549,38 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
                 }
             }
         }
+#endif
         __syncthreads(); /* the next tile rewrites the shared activations */
     }
 
     /* =========================== epilogue: this block's partial =========================== */
     float *out = A.partials + (int64_t)blockIdx.x * kPpoPartial;
     {
+#if BB_PPO_MMA & 32
+        const int g = lane >> 2, t = lane & 3, mt2 = warp >> 2, nt2 = warp & 3;
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+            for (int nt = 0; nt < 2; nt++) { /* accumulator fragment: rows g, g + 8; columns 2t, 2t + 1 */
+                float *dst = out + BB_PPO_OFF_W1 + (16 * mt + g) * BB_OBS_DIM + 16 * warp + 8 * nt + 2 * t;
+                *reinterpret_cast<float2 *>(dst) = make_float2(gW1[2 * mt + nt][0], gW1[2 * mt + nt][1]);
+                *reinterpret_cast<float2 *>(dst + 8 * BB_OBS_DIM) = make_float2(gW1[2 * mt + nt][2], gW1[2 * mt + nt][3]);
+            }
+        {
+            float *dst = out + BB_PPO_OFF_W2 + (16 * mt2 + g) * kH + 8 * nt2 + 2 * t;
+            *reinterpret_cast<float2 *>(dst) = make_float2(gW2[0], gW2[1]);
+            *reinterpret_cast<float2 *>(dst + 8 * kH) = make_float2(gW2[2], gW2[3]);
+        }
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int j = 16 * mt2 + g + 8 * h;
+            if (j < kHeads) {
+                float *dst = out + (j < BB_NUM_LOGITS ? BB_PPO_OFF_WA + j * kH : BB_PPO_OFF_WC) + 8 * nt2 + 2 * t; /* WC is not 8-byte aligned */
+                dst[0] = gWh[2 * h]; dst[1] = gWh[2 * h + 1];
+            }
+        }
+        if (tid >= 160 && tid < 160 + 2 * kH + kHeads) {
+#else
         const int cg = warp, kg = lane, j2 = tid >> 3, k42 = tid & 7;
 #pragma unroll
         for (int i = 0; i < 4; i++)
@@ -389,6 +590,7 @@ __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_po
             float *dst = out + (j2 < BB_NUM_LOGITS ? BB_PPO_OFF_WA + j2 * kH : BB_PPO_OFF_WC) + 4 * k42; /* WC is not 16-byte aligned */
             dst[0] = gWh[0]; dst[1] = gWh[1]; dst[2] = gWh[2]; dst[3] = gWh[3];
         } else if (tid >= 160 && tid < 160 + 2 * kH + kHeads) {
+#endif
             const int t = tid - 160;
             const int off = t < kH ? BB_PPO_OFF_B1 + t : (t < 2 * kH ? BB_PPO_OFF_B2 + (t - kH)
                           : (t - 2 * kH < BB_NUM_LOGITS ? BB_PPO_OFF_BA + (t - 2 * kH) : BB_PPO_OFF_BC));
