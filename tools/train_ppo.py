@@ -62,7 +62,12 @@ def main():
         fused = FusedPPO(agent, lr=cfg.learning_rate, eps=1e-8, clip_coef=cfg.clip_coef, ent_coef=cfg.ent_coef,
                          vf_coef=cfg.vf_coef, max_grad_norm=cfg.max_grad_norm, seed=args.seed + 7919 * rank)
         if ws > 1 and args.allreduce == "p2p":
-            fused.enable_p2p()
+            try:
+                fused.enable_p2p()
+            except RuntimeError as e:   # raised on every rank together (CUDA IPC / peer access unavailable): NCCL all-reduce instead
+                args.allreduce = "nccl"
+                if rank == 0:
+                    print(f"train_ppo: {e}; using --allreduce nccl", file=sys.stderr)
     else:
         opt = torch.optim.Adam(agent.parameters(), lr=cfg.learning_rate, eps=1e-8)
     weights = fused.weights if args.update == "fused" else PolicyWeights.from_module(agent)
