@@ -96,43 +96,7 @@ BBD void ppo_ln_bwd(float (&d)[kCh], const float (&xhat)[kCh], float rstd, const
     for (int c = 0; c < kCh; c++) d[c] = rstd * (d[c] - s1 - xhat[c] * s2);
 }
 
-/* ---- row-phase GEMVs on the tensor cores, fp32-accurate (3xTF32) ----
- * ncu (profiles/r01g_ppo_grad_*) showed the FFMA version bound by shared-memory bandwidth (73 % of the LSU wavefront
- * peak): a quad thread loaded 9 float4 per 32 FFMA, and broadcast does not multiply the 128 B/clk a warp can receive.
- * mma.sync.m16n8k8 shares fragments across the warp instead: the warp's 8 rows are rows 0..7 of the A tile (rows 8..15
- * are zero registers, never loaded), thread (g = lane >> 2, t = lane & 3) loads x[row g][k0 + t], x[row g][k0 + t + 4]
- * and, per 8-channel tile j, w[ch][k0 + t], w[ch][k0 + t + 4] with ch = 8j + 4 (g & 1) + (g >> 1).  That column
- * permutation makes the accumulator pair the thread receives (tile columns 2t, 2t + 1) the channels 4 (2j) + t and
- * 4 (2j + 1) + t — exactly the quad mapping (channel 4c + q) of the surrounding code, so nothing else moves.
- * Every operand is split x = hi + lo with hi = tf32(x), lo = tf32(x - hi) and the product is lo*hi + hi*lo + hi*hi,
- * accumulated in fp32: ~2^-21 relative per product, inside the parity bar against torch fp32 autograd. */
-#ifndef BB_PPO_MMA
-#define BB_PPO_MMA 63   /* bit 0: layer 1, 1: layer 2, 2: heads, 3: backward heads, 4: backward layer 2, 5: weight gradients (tile phase) */
-#endif
-#ifndef BB_PPO_TRUNC_SPLIT
-#define BB_PPO_TRUNC_SPLIT 1
-#endif
-#ifndef BB_PPO_SPLITACC
-#define BB_PPO_SPLITACC 0
-#endif
-BBD void tf32_split(float x, uint32_t &hi, uint32_t &lo)
-{
-#if BB_PPO_TRUNC_SPLIT
-    hi = __float_as_uint(x) & 0xffffe000u;                 /* the tensor core reads only the top 19 bits anyway */
-    lo = __float_as_uint(x - __uint_as_float(hi));         /* exact; its own low bits are dropped by the hardware (2^-21 |x|) */
-#else
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
-    const float r = x - __uint_as_float(hi);
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
-#endif
-}
-BBD void mma_tf32_half(float &c0, float &c1, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1)
-{
-    float d2, d3;
-    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%10,%10};"
-                 : "+f"(c0), "+f"(c1), "=f"(d2), "=f"(d3)
-                 : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1), "f"(0.f));
-}
+/* tf32_split, mma_tf32_half and quad_mma_tf32x3 (the row-phase products) live in bb_rollout.cuh: bb_policy_kernel uses them too */
 /* full-tile 3xTF32 product for the weight-gradient GEMMs: c += A(16x8) B(8x8), operands pre-split */
 BBD void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2])
 {
@@ -163,44 +127,6 @@ BBD void load_b_frag(const float *X, int ra, int n0, int g, uint32_t (&bh)[2], u
     tf32_split(X[ra * STR + n0 + g], bh[0], bl[0]);
     tf32_split(X[(ra + 1) * STR + n0 + g], bh[1], bl[1]);
 }
-/* out[2j + e] += sum_k W[(8j + 4e + q) * WSTR + k] * xrow[k], k < K (multiple of 8), j < NT; all 32 lanes must call it */
-template <int K, int WSTR, int NT>
-BBD void quad_mma_tf32x3(const float *xrow, const float *W, int lane, float (&out)[2 * NT])
-{
-    const int g = lane >> 2, t = lane & 3;
-    const float *wbase = W + (4 * (g & 1) + (g >> 1)) * WSTR + t;
-#if BB_PPO_SPLITACC
-    float lo[2 * NT];   /* the two correction terms get their own accumulators: two independent MMA chains per tile */
-#pragma unroll
-    for (int i = 0; i < 2 * NT; i++) lo[i] = 0.f;
-#endif
-#pragma unroll 4
-    for (int k0 = 0; k0 < K; k0 += 8) {
-        uint32_t a0h, a0l, a2h, a2l;
-        tf32_split(xrow[k0 + t], a0h, a0l);
-        tf32_split(xrow[k0 + t + 4], a2h, a2l);
-#pragma unroll
-        for (int j = 0; j < NT; j++) {
-            const float *w = wbase + 8 * j * WSTR + k0;
-            uint32_t b0h, b0l, b1h, b1l;
-            tf32_split(w[0], b0h, b0l);
-            tf32_split(w[4], b1h, b1l);
-#if BB_PPO_SPLITACC
-            mma_tf32_half(lo[2 * j], lo[2 * j + 1], a0l, a2l, b0h, b1h);
-            mma_tf32_half(lo[2 * j], lo[2 * j + 1], a0h, a2h, b0l, b1l);
-#else
-            mma_tf32_half(out[2 * j], out[2 * j + 1], a0l, a2l, b0h, b1h);
-            mma_tf32_half(out[2 * j], out[2 * j + 1], a0h, a2h, b0l, b1l);
-#endif
-            mma_tf32_half(out[2 * j], out[2 * j + 1], a0h, a2h, b0h, b1h);
-        }
-    }
-#if BB_PPO_SPLITACC
-#pragma unroll
-    for (int i = 0; i < 2 * NT; i++) out[i] += lo[i];
-#endif
-}
-
 __global__ void __launch_bounds__(kPpoThreads, 2) bb_ppo_grad_kernel(const bb_policy P, const PpoArgs A)
 {
     extern __shared__ __align__(16) unsigned char ppoSmemRaw[];

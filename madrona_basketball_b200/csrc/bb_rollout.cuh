@@ -93,6 +93,72 @@ BBD void layer_norm_relu(float (&v)[kCh], int q, int H, const float *g, const fl
     for (int c = 0; c < kCh; c++) v[c] = (4 * c + q < H) ? fmaxf(fmaf(v[c] * rstd, g[4 * c + q], b[4 * c + q]), 0.f) : 0.f;
 }
 
+/* ---- row-phase GEMVs on the tensor cores, fp32-accurate (3xTF32) ----
+ * ncu (profiles/r01g_ppo_grad_*) showed the FFMA version bound by shared-memory bandwidth (73 % of the LSU wavefront
+ * peak): a quad thread loaded 9 float4 per 32 FFMA, and broadcast does not multiply the 128 B/clk a warp can receive.
+ * mma.sync.m16n8k8 shares fragments across the warp instead: the warp's 8 rows are rows 0..7 of the A tile (rows 8..15
+ * are zero registers, never loaded), thread (g = lane >> 2, t = lane & 3) loads x[row g][k0 + t], x[row g][k0 + t + 4]
+ * and, per 8-channel tile j, w[ch][k0 + t], w[ch][k0 + t + 4] with ch = 8j + 4 (g & 1) + (g >> 1).  That column
+ * permutation makes the accumulator pair the thread receives (tile columns 2t, 2t + 1) the channels 4 (2j) + t and
+ * 4 (2j + 1) + t — exactly the quad mapping (channel 4c + q) of the surrounding code, so nothing else moves.
+ * Every operand is split x = hi + lo with hi = tf32(x), lo = tf32(x - hi) and the product is lo*hi + hi*lo + hi*hi,
+ * accumulated in fp32: ~2^-21 relative per product, inside the parity bar against torch fp32 autograd. */
+#ifndef BB_POL_MMA
+#define BB_POL_MMA 1   /* bb_policy_kernel: the three products on the tensor cores (0: FFMA) */
+#endif
+#ifndef BB_PPO_MMA
+#define BB_PPO_MMA 63   /* bit 0: layer 1, 1: layer 2, 2: heads, 3: backward heads, 4: backward layer 2, 5: weight gradients (tile phase) */
+#endif
+#ifndef BB_PPO_TRUNC_SPLIT
+#define BB_PPO_TRUNC_SPLIT 1
+#endif
+BBD void tf32_split(float x, uint32_t &hi, uint32_t &lo)
+{
+#if BB_PPO_TRUNC_SPLIT
+    hi = __float_as_uint(x) & 0xffffe000u;                 /* the tensor core reads only the top 19 bits anyway */
+    lo = __float_as_uint(x - __uint_as_float(hi));         /* exact; its own low bits are dropped by the hardware (2^-21 |x|) */
+#else
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+    const float r = x - __uint_as_float(hi);
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
+#endif
+}
+BBD void mma_tf32_half(float &c0, float &c1, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1)
+{
+    float d2, d3;
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%10,%10};"
+                 : "+f"(c0), "+f"(c1), "=f"(d2), "=f"(d3)
+                 : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1), "f"(0.f));
+}
+/* one k-step (8 inputs) of out[2j + e] += sum_k W[(8j + 4e + q) * WSTR + k] * x[k]: xa = x[k0 + t], xb = x[k0 + t + 4],
+ * wk = W + (4 (g & 1) + (g >> 1)) * WSTR + t + k0 */
+template <int WSTR, int NT>
+BBD void quad_mma_step(float xa, float xb, const float *wk, float (&out)[2 * NT])
+{
+    uint32_t a0h, a0l, a2h, a2l;
+    tf32_split(xa, a0h, a0l);
+    tf32_split(xb, a2h, a2l);
+#pragma unroll
+    for (int j = 0; j < NT; j++) {
+        const float *w = wk + 8 * j * WSTR;
+        uint32_t b0h, b0l, b1h, b1l;
+        tf32_split(w[0], b0h, b0l);
+        tf32_split(w[4], b1h, b1l);
+        mma_tf32_half(out[2 * j], out[2 * j + 1], a0l, a2l, b0h, b1h);
+        mma_tf32_half(out[2 * j], out[2 * j + 1], a0h, a2h, b0l, b1l);
+        mma_tf32_half(out[2 * j], out[2 * j + 1], a0h, a2h, b0h, b1h);
+    }
+}
+/* out[2j + e] += sum_k W[(8j + 4e + q) * WSTR + k] * xrow[k], k < K (multiple of 8), j < NT; all 32 lanes must call it */
+template <int K, int WSTR, int NT>
+BBD void quad_mma_tf32x3(const float *xrow, const float *W, int lane, float (&out)[2 * NT])
+{
+    const int g = lane >> 2, t = lane & 3;
+    const float *wbase = W + (4 * (g & 1) + (g >> 1)) * WSTR + t;
+#pragma unroll 4
+    for (int k0 = 0; k0 < K; k0 += 8) quad_mma_step<WSTR, NT>(xrow[k0 + t], xrow[k0 + t + 4], wbase + k0, out);
+}
+
 /* the buckets [2,8,3,2,2,2] (env.py:102) spread over the quad: q0 {0,2}, q1 {1}, q2 {3,4}, q3 {5} */
 __device__ __constant__ int kBucketOff[BB_NUM_ACTION_DIMS] = {0, 2, 10, 13, 15, 17};
 __device__ __constant__ int kBucketCnt[BB_NUM_ACTION_DIMS] = {2, 8, 3, 2, 2, 2};
@@ -143,6 +209,27 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
         float acc[kCh];
 #pragma unroll
         for (int c = 0; c < kCh; c++) acc[c] = S.b1[4 * c + q];
+#if BB_POL_MMA
+        if (brow) { /* buffer.obs[step] = obs (ppo.py:128): this thread's 8 of the row's 32 chunks */
+#pragma unroll
+            for (int i = 0; i < 8; i++) brow[4 * i + q] = orow[4 * i + q];
+        }
+        {   /* 3xTF32 tensor-core product (see quad_mma_tf32x3): the A fragment comes straight from global memory, normalised on the fly */
+            const float *xr = io.obs + r * io.obsStride;
+            const int g = lane >> 2;
+            const float *wbase = &S.w1[0][0] + (4 * (g & 1) + (g >> 1)) * kW1Stride + q;
+#pragma unroll 4
+            for (int k0 = 0; k0 < BB_OBS_DIM; k0 += 8) {
+                float xa = (xr[k0 + q] - S.mean[k0 + q]) * S.inv[k0 + q];
+                float xb = (xr[k0 + q + 4] - S.mean[k0 + q + 4]) * S.inv[k0 + q + 4];
+                if (P.obs_clamp > 0.f) {
+                    xa = fminf(fmaxf(xa, -P.obs_clamp), P.obs_clamp);
+                    xb = fminf(fmaxf(xb, -P.obs_clamp), P.obs_clamp);
+                }
+                quad_mma_step<kW1Stride, kCh / 2>(xa, xb, wbase + k0, acc);
+            }
+        }
+#else
         float4 xq = orow[0];
 #pragma unroll 2
         for (int k4 = 0; k4 < BB_OBS_DIM / 4; k4++) {
@@ -162,6 +249,7 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
                 acc[c] = fmaf(w.w, x3, fmaf(w.z, x2, fmaf(w.y, x1, fmaf(w.x, x0, acc[c]))));
             }
         }
+#endif
         layer_norm_relu(acc, q, H, S.g1, S.e1);              /* backbone.1-2 */
 #pragma unroll
         for (int c = 0; c < kCh; c++) S.hid[rb][4 * c + q] = acc[c];
@@ -169,6 +257,9 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
         /* ---- backbone.3-5: Linear(H,H) + LayerNorm + ReLU ---- */
 #pragma unroll
         for (int c = 0; c < kCh; c++) acc[c] = S.b2[4 * c + q];
+#if BB_POL_MMA
+        quad_mma_tf32x3<kH, kW2Stride, kCh / 2>(&S.hid[rb][0], &S.w2[0][0], lane, acc);
+#else
 #pragma unroll
         for (int k4 = 0; k4 < kH / 4; k4++) {
             const float4 h = *reinterpret_cast<const float4 *>(&S.hid[rb][k4 * 4]);
@@ -178,12 +269,20 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
                 acc[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, acc[c]))));
             }
         }
+#endif
         layer_norm_relu(acc, q, H, S.g2, S.e2);
         __syncwarp(); /* every read of the first hidden vector is done */
 #pragma unroll
         for (int c = 0; c < kCh; c++) S.hid[rb][4 * c + q] = acc[c];
         __syncwarp();
         /* ---- heads: outputs q, q+4, .., q+16 of (19 actor logits | critic) ---- */
+#if BB_POL_MMA
+        float o[kHeadPerThread + 1];   /* o[5]: "output" 20 + q, rows of the next shared array: computed and dropped */
+#pragma unroll
+        for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
+        o[kHeadPerThread] = 0.f;
+        quad_mma_tf32x3<kH, kW2Stride, 3>(&S.hid[rb][0], &S.wh[0][0], lane, o);
+#else
         float o[kHeadPerThread];
 #pragma unroll
         for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
@@ -196,6 +295,7 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
                 o[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, o[c]))));
             }
         }
+#endif
 #pragma unroll
         for (int c = 0; c < kHeadPerThread; c++) {
             const int j = 4 * c + q;
