@@ -218,16 +218,23 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
             const float *xr = io.obs + r * io.obsStride;
             const int g = lane >> 2;
             const float *wbase = &S.w1[0][0] + (4 * (g & 1) + (g >> 1)) * kW1Stride + q;
+            float acc2[kCh];   /* odd k-steps accumulate separately: two independent MMA chains per tile (this kernel is latency bound) */
+#pragma unroll
+            for (int c = 0; c < kCh; c++) acc2[c] = 0.f;
 #pragma unroll 4
-            for (int k0 = 0; k0 < BB_OBS_DIM; k0 += 8) {
-                float xa = (xr[k0 + q] - S.mean[k0 + q]) * S.inv[k0 + q];
-                float xb = (xr[k0 + q + 4] - S.mean[k0 + q + 4]) * S.inv[k0 + q + 4];
-                if (P.obs_clamp > 0.f) {
-                    xa = fminf(fmaxf(xa, -P.obs_clamp), P.obs_clamp);
-                    xb = fminf(fmaxf(xb, -P.obs_clamp), P.obs_clamp);
+            for (int k0 = 0; k0 < BB_OBS_DIM; k0 += 16) {
+                float xv[4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int k = k0 + q + 4 * i;
+                    xv[i] = (xr[k] - S.mean[k]) * S.inv[k];
+                    if (P.obs_clamp > 0.f) xv[i] = fminf(fmaxf(xv[i], -P.obs_clamp), P.obs_clamp);
                 }
-                quad_mma_step<kW1Stride, kCh / 2>(xa, xb, wbase + k0, acc);
+                quad_mma_step<kW1Stride, kCh / 2>(xv[0], xv[1], wbase + k0, acc);
+                quad_mma_step<kW1Stride, kCh / 2>(xv[2], xv[3], wbase + k0 + 8, acc2);
             }
+#pragma unroll
+            for (int c = 0; c < kCh; c++) acc[c] += acc2[c];
         }
 #else
         float4 xq = orow[0];
