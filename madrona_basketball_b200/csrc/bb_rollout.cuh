@@ -6,9 +6,10 @@
  * scripts/ppo.py:60-166 (rollout, compute_advantages), scripts/buffers.py, scripts/ppo_stats.py:21-36.
  *
  * bb_policy_kernel: four threads per observation row against broadcast 16-byte reads of the weights in
- * shared memory (see the kernel).  fp32 FFMA throughout: the contraction is 5.7 kFLOP per row - at 8192
- * rows a few microseconds on the CUDA cores - and
- * agreement with the torch fp32 reference to ~1e-6 matters more here than tensor-core peak.
+ * shared memory (see the kernel).  The contraction is 5.7 kFLOP per row; agreement with the torch fp32
+ * reference to ~1e-6 matters more here than tensor-core peak, so the three products run as 3xTF32
+ * (mma.sync, operands split hi + lo, fp32 accumulate: fp32-level accuracy; quad_mma_tf32x3 below), with
+ * the FFMA form kept under BB_POL_MMA=0.
  */
 #pragma once
 #include "../../include/bb_rollout.h"
