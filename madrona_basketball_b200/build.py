@@ -35,11 +35,28 @@ def find_nvcc() -> str:
     return nvcc
 
 
+HASH_PATH = LIB_PATH + ".hash"
+
+
+def source_hash(extra=()) -> str:
+    """sha256 over every source / header the library is built from + the compiler flags."""
+    import hashlib
+
+    h = hashlib.sha256()
+    for d in DEPS:
+        with open(d, "rb") as f:
+            h.update(os.path.basename(d).encode() + b"\0" + f.read())
+    h.update(" ".join(NVCC_FLAGS + list(extra)).encode())
+    return h.hexdigest()
+
+
 def needs_build() -> bool:
-    if not os.path.exists(LIB_PATH):
+    """True unless libbball.so was built from exactly the sources in the tree (content hash, not mtime: the
+    snapshot that carries a prebuilt library to the GPU box does not preserve a meaningful mtime order)."""
+    if not os.path.exists(LIB_PATH) or not os.path.exists(HASH_PATH):
         return True
-    t = os.path.getmtime(LIB_PATH)
-    return any(os.path.getmtime(d) > t for d in DEPS)
+    with open(HASH_PATH) as f:
+        return f.read().strip() != source_hash()
 
 
 def build_engine(force: bool = False, verbose: bool = False, extra=(), out: str = LIB_PATH) -> str:
@@ -51,6 +68,9 @@ def build_engine(force: bool = False, verbose: bool = False, extra=(), out: str 
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
     if verbose:
         print(res.stderr)
+    if out == LIB_PATH:
+        with open(HASH_PATH, "w") as f:
+            f.write(source_hash(extra) + "\n")
     return out
 
 

@@ -64,8 +64,12 @@ def _head_init(layer):       # agent.py:103-106
 
 
 class Agent(nn.Module):
-    def __init__(self, input_dim: int = 128, num_channels: int = 32, action_buckets=ACTION_BUCKETS):
+    def __init__(self, input_dim: int = 128, num_channels: int = 32, num_layers: int = 2, action_buckets=ACTION_BUCKETS):
+        """Same positional signature as the reference (agent.py:109); the fused kernels cover num_layers == 2
+        (the only value the reference's scripts pass: env.py:107, ppo.py:257)."""
         super().__init__()
+        if num_layers != 2:
+            raise ValueError("madrona_basketball_b200 supports the reference's 2-layer policy only")
         self.action_buckets = list(action_buckets)
         self.backbone = nn.Sequential(
             _backbone_init(nn.Linear(input_dim, num_channels)), nn.LayerNorm(num_channels), nn.ReLU(),

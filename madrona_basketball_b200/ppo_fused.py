@@ -301,7 +301,7 @@ class FusedPPO:
         for _ in range(update_epochs):
             # one permutation of the rollout rows per epoch (ppo.py:186): bb_randperm, or torch's own stream
             perm = self.randperm(total) if permutation == "fused" else torch.randperm(total, device=self.device, generator=generator)
-            for start in range(0, mb * num_minibatches, mb):
+            for start in range(0, total, mb):   # ppo.py:188: a remainder minibatch when total % num_minibatches != 0
                 self.gradient(obs, act, lp, v, adv, ret, perm[start:start + mb])
                 if p2p:
                     self.apply_p2p()
@@ -313,6 +313,6 @@ class FusedPPO:
             self._p2p_error_host.copy_(self.p2p_error, non_blocking=True)
             self._p2p_error_event = torch.cuda.Event()
             self._p2p_error_event.record(torch.cuda.current_stream(self.device))
-        m = float(mb)
+        m = float(self._last_rows)   # rows of the last minibatch (the remainder one when total % num_minibatches != 0)
         return {"pg_loss": self.stats[0] / m, "v_loss": self.stats[1] / m * self.vf_coef,
                 "ent_loss": -self.stats[2] / m * self.ent_coef, "clip_frac": self.stats[3] / m, "grad_norm": self.grad_norm[0]}

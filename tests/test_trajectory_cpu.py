@@ -70,3 +70,71 @@ def test_run_log_covers_all_worlds(tmp_path):
     d = np.load(path)
     assert d["agent_pos"].shape == (10, 3, 2, 3) and d["done"].shape == (10, 3) and int(d["num_episodes"]) == 2
     assert d["hoop_pos"].shape == (3, 2, 3)
+
+
+def _reference_viewer():
+    """The reference's scripts/viewer.py (staged copy, pygame stubbed); None when the reference is not available."""
+    import os
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "tools"))
+    import stage_reference
+
+    if not stage_reference.staged() and not stage_reference.stage(verbose=False):
+        return None
+    saved = list(sys.path)
+    sys.path[:0] = stage_reference.script_path()
+    try:
+        import viewer
+        return viewer
+    finally:
+        sys.path[:] = saved
+
+
+def test_logs_load_through_the_reference_viewer_loader(tmp_path):
+    """files written by TrajectoryRecorder go through the reference's OWN loader,
+    ViewerClass.load_and_parse_log (scripts/viewer.py:1028-1100): episode breaks, shot events and counts come out."""
+    import pytest
+
+    viewer = _reference_viewer()
+    if viewer is None:
+        pytest.skip("baseline/_ref/ not staged and /root/reference absent")
+    n, steps = 3, 700
+    orc = make_oracle(n)
+    rec = TrajectoryRecorder(_OracleSim(orc), worlds=slice(None), agent_idx=0)
+    dones = []
+    for s in range(steps):
+        orc.fill_actions(1234, s)
+        orc.step()
+        rec.record()
+        dones.append(orc.tensor("done")[:, 0].copy())
+    path = tmp_path / "run.npz"
+    rec.save_run(str(path), num_episodes=0)
+    parsed = viewer.ViewerClass.load_and_parse_log(object(), str(path), event_to_track="shoot")   # `self` is unused by the loader
+    assert parsed is not None, "the reference's loader rejected the file"
+    assert (parsed["num_steps"], parsed["num_worlds"], parsed["num_agents"]) == (steps, n, 2)
+    dones = np.array(dones)
+    for w in range(n):
+        ends = [b["end"] for b in parsed["episode_breaks"][w]]
+        assert ends == [int(i) for i in np.flatnonzero(dones[1:, w] > 0) + 1]
+        starts = [b["start"] for b in parsed["episode_breaks"][w]]
+        assert starts == [0] + [e + 1 for e in ends[:-1]]
+    assert parsed["total_episodes"] == max(int((dones[1:, w] > 0).sum()) for w in range(n)) > 0
+    assert np.array_equal(parsed["episodes_completed_log"], np.cumsum(dones, axis=0))
+    assert len(parsed["parsed_events"]) > 0                                   # random actions shoot
+    for ev in parsed["parsed_events"]:
+        assert ev["pos"].shape == (3,) and bool(ev["outcome"]) in (True, False)     # constants.py:31: shotIsGoingIn of that step
+
+    # the per-episode file of ppo.py:108-121 (world 0 only, ppo.py's fixed hoop positions)
+    orc2 = make_oracle(2)
+    rec2 = TrajectoryRecorder(_OracleSim(orc2), worlds=slice(0, 1), agent_idx=0)
+    for s in range(700):
+        orc2.fill_actions(7, s)
+        orc2.step()
+        if rec2.record():
+            break
+    ep = tmp_path / "iter_100_episode.npz"
+    rec2.save_episode(str(ep))
+    parsed2 = viewer.ViewerClass.load_and_parse_log(object(), str(ep))
+    assert parsed2 is not None and parsed2["num_worlds"] == 1 and parsed2["num_steps"] == s + 1
