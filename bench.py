@@ -32,6 +32,7 @@ WORLDS_PER_GPU = 8192
 BYTES_PER_WORLD_STEP = 1872  # 56 in + 348 state read + 348 state write + 1120 outputs
 SEED = 1234
 LARGE_WORLDS = 1 << 20       # HBM-bound regime (working set 1.9 GB >> 126 MB L2)
+PREWARM_S = 0.5              # declared device pre-warm before the timed window (config.prewarm)
 
 
 def measured_peak_gbs():
@@ -74,6 +75,8 @@ class ClockSampler:
             nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake",
         }
         while not self._stop.is_set():
+            if not self._active.wait(timeout=0.5):
+                continue
             if self._active.is_set():
                 try:
                     self.samples.append(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM))
@@ -92,6 +95,10 @@ class ClockSampler:
     def __exit__(self, *a):
         self._active.clear()
 
+    def pause(self):
+        """Parks the polling thread (it blocks on an event instead of waking every 2 ms)."""
+        self._active.clear()
+
     def report(self):
         self._stop.set()
         if self._nv is None:
@@ -101,28 +108,65 @@ class ClockSampler:
                 "reasons": sorted(self.reasons), "samples": len(s)}
 
 
-def time_cpu_arm(worlds: int, steps: int, warmup: int, threads: int):
-    """Times the oracle (CPU restatement of the reference's step) on `threads` host threads.
+def workload_string(worlds_per_gpu: int, n_gpus: int) -> str:
+    """config.workload, the same text for both arms (the driver compares them)."""
+    return (f"{worlds_per_gpu} worlds per GPU x {n_gpus} GPU = {worlds_per_gpu * n_gpus} worlds, 2 agents + ball per world, "
+            f"random actions for both agents (Threefry, seed {SEED}), sim seed 0")
 
-    The glibc-libm build of the oracle is the one timed: it is the arithmetic the reference's CPU
-    executor would run (the deterministic-math build exists for bit-exact GPU parity and is ~10 % slower)."""
+
+_CPU_BUILD = {}
+
+
+def pick_cpu_build(worlds: int, threads: int):
+    """The CPU arm times the FASTER of the oracle's two glibc-libm builds on this host: the generic -O2 one
+    (oracle/Makefile) and a -O3 -march=native one compiled on this machine (oracle.build_native).  Same results."""
+    if "kind" in _CPU_BUILD:
+        return _CPU_BUILD["kind"], _CPU_BUILD["note"]
     import oracle
 
     oracle.build()
-    orc = oracle.Oracle(worlds, start_x=31.515 / 2.0, start_y=16.764 / 2.0, libm=True)
+    rates = {}
+    for kind in (True, "native"):
+        try:
+            orc = oracle.Oracle(worlds, start_x=31.515 / 2.0, start_y=16.764 / 2.0, libm=kind)
+        except Exception as e:   # no compiler on the box: the generic build stands
+            rates[kind] = 0.0
+            continue
+        orc.run_synthetic(SEED, 0, 20, 0, threads)
+        t0 = time.perf_counter()
+        orc.run_synthetic(SEED, 20, 100, 0, threads)
+        rates[kind] = worlds * 100 / (time.perf_counter() - t0)
+        orc.close()
+    kind = "native" if rates["native"] > rates[True] else True
+    _CPU_BUILD["kind"] = kind
+    _CPU_BUILD["note"] = (f"oracle/ restatement on glibc libm, {'-O3 -march=native' if kind == 'native' else '-O2 generic'} build "
+                          f"(probe: generic {rates[True] / 1e6:.1f} M/s, native {rates['native'] / 1e6:.1f} M/s)")
+    return kind, _CPU_BUILD["note"]
+
+
+def time_cpu_arm(worlds: int, steps: int, warmup: int, threads: int, kind=True):
+    """Times the oracle (CPU restatement of the reference's step) on `threads` host threads: ONE call, every
+    thread steps its own block of worlds through all `steps` steps (no thread start-up or barrier per step: the
+    steady-state rate a CPU executor with a persistent thread pool delivers)."""
+    import oracle
+
+    orc = oracle.Oracle(worlds, start_x=31.515 / 2.0, start_y=16.764 / 2.0, libm=kind)
     orc.run_synthetic(SEED, 0, warmup, 0, threads)
     t0 = time.perf_counter()
     orc.run_synthetic(SEED, warmup, steps, 0, threads)
     dt = time.perf_counter() - t0
+    orc.close()
     return worlds * steps / dt, dt
 
 
-def time_cpu_arm_for(worlds: int, seconds: float, threads: int):
-    """Bounded sample: a short probe sizes the run to about `seconds` of CPU work."""
-    rate, _ = time_cpu_arm(worlds, 100, 10, threads)
+def time_cpu_arm_for(worlds: int, seconds: float, threads: int, multiple_of: int = 1):
+    """Bounded sample: a short probe sizes ONE run to about `seconds` of CPU work."""
+    kind, note = pick_cpu_build(worlds, threads)
+    rate, _ = time_cpu_arm(worlds, 100, 10, threads, kind)
     steps = max(200, int(rate * seconds / worlds))
-    value, dt = time_cpu_arm(worlds, steps, 10, threads)
-    return value, dt, steps
+    steps = ((steps + multiple_of - 1) // multiple_of) * multiple_of
+    value, dt = time_cpu_arm(worlds, steps, 50, threads, kind)
+    return value, dt, steps, note
 
 
 def ncu_traffic(key: str):
@@ -140,33 +184,21 @@ def run_reference(args):
     if rank != 0:
         return 0
     threads = os.cpu_count() or 1
-    worlds = WORLDS_PER_GPU * args.gpus
-    # each "step" is one pass over the whole batch.  A K-step block at 8192 worlds lasts only milliseconds
-    # (thread start-up and cold caches would dominate), so the block is repeated for about 3 s and the mean
-    # block time is reported: the CPU arm gets its steady-state rate.
-    import oracle
-
-    oracle.build()
+    worlds = args.worlds_per_gpu * args.gpus
     steps, warmup = args.steps, args.warmup
-    orc = oracle.Oracle(worlds, start_x=31.515 / 2.0, start_y=16.764 / 2.0, libm=True)
-    orc.run_synthetic(SEED, 0, warmup, 0, threads)
-    t0 = time.perf_counter()
-    orc.run_synthetic(SEED, warmup, steps, 0, threads)
-    first = time.perf_counter() - t0
-    blocks = max(1, min(2000, int(3.0 / max(first, 1e-6))))
-    t0 = time.perf_counter()
-    for b in range(blocks):
-        orc.run_synthetic(SEED, warmup + (b + 1) * steps, steps, 0, threads)
-    dt = (time.perf_counter() - t0) / blocks
-    value = worlds * steps / dt
-    sample = (f"{worlds} worlds x {steps} steps per block, mean of {blocks} consecutive blocks after {warmup} warm-up steps + 1 block; "
-              f"oracle/ restatement on glibc libm, {threads} threads, synthetic random actions")
+    # A K-step block at 8192 worlds lasts only milliseconds, so the arm runs B consecutive K-step blocks inside ONE
+    # oracle call of about args.cpu_seconds (threads started once, no barrier between steps) and reports the mean block:
+    # the steady-state rate, the same number the engine arm's cpu_baseline prints on this box.
+    value, dt, total_steps, note = time_cpu_arm_for(worlds, args.cpu_seconds, threads, multiple_of=steps)
+    blocks = total_steps // steps
+    sample = (f"{worlds} worlds x {total_steps} steps = {blocks} consecutive blocks of {steps} steps in one call ({dt:.1f} s of CPU work) "
+              f"after 50 warm-up steps; {note}; {threads} threads, synthetic random actions")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": steps, "warmup": warmup, "ms_per_step": dt / steps * 1e3, "higher_is_better": True,
+        "steps": steps, "warmup": warmup, "ms_per_step": dt / total_steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{WORLDS_PER_GPU} worlds per GPU x {args.gpus} = {worlds} worlds, random actions seed {SEED}, "
-                               "CPU restatement of the reference step (Madrona CPU executor unavailable on this box)"},
+        "config": {"workload": workload_string(args.worlds_per_gpu, args.gpus),
+                   "what": "CPU restatement of the reference step (the Madrona CPU executor cannot be built on this box)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -212,7 +244,20 @@ def run_engine(args):
         torch.cuda.synchronize()
 
     # ---------------------------------------------------------------- value: device-resident, per-step events
+    # Declared device pre-warm (stated in config.prewarm): an idle GPU needs a few hundred milliseconds of work before its
+    # clocks and the driver's launch path reach steady state; with --steps 20 --warmup 5 the timed window would otherwise
+    # sit on that ramp.  Same flush + step pairs as the timed loop, at least PREWARM_S seconds and 50 pairs, then the W
+    # warm-up steps as passed.
+    t_pw, n_pw = time.perf_counter(), 0
+    while n_pw < 50 or time.perf_counter() - t_pw < PREWARM_S:
+        flush.zero_()
+        sim.step_with_actions(actions[n_pw % (K + Wm)])
+        n_pw += 1
+        if n_pw % 16 == 0:
+            torch.cuda.synchronize()
+    torch.cuda.synchronize()
     for s in range(Wm):
+        flush.zero_()
         sim.step_with_actions(actions[s])
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
     stops = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
@@ -284,32 +329,46 @@ def run_engine(args):
     h_done = torch.empty((n, 2), dtype=torch.float32).pin_memory()
     np_act = [a.numpy() for a in h_act]
     np_rew, np_done = h_rew.numpy(), h_done.numpy()
-    def timed_host_loop(step_fn):
-        for s in range(Wm):
-            step_fn(np_act[s % ring], np_rew, np_done)
+    h_obs = torch.empty((n, 2, 128), dtype=torch.float32).pin_memory()
+    np_obs = h_obs.numpy()
+    sampler.pause()   # no NVML polling thread next to the latency-bound host loops (clocks were sampled in the regions above)
+
+    def timed_host_loop(step_fn, with_obs=False, acts=None):
+        acts = np_act if acts is None else acts
+        extra = (np_obs,) if with_obs else ()
+        Ke = max(K, 200)  # host loops are wall-clock timed: at least 200 steps so that one scheduler hiccup does not decide the number
+        for s in range(max(Wm, 20)):
+            step_fn(acts[s % ring], np_rew, np_done, *extra)
         if world_size > 1:
             dist.barrier()
-        with sampler:
-            t0 = time.perf_counter()
-            for s in range(K):
-                step_fn(np_act[(Wm + s) % ring], np_rew, np_done)  # returns when reward + done are in host memory
-            dt = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for s in range(Ke):
+            step_fn(acts[(Wm + s) % ring], np_rew, np_done, *extra)  # returns when reward + done (+ obs) are in host memory
+        dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
         if world_size > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        return total_worlds * K / float(tt.item())
+        return total_worlds * Ke / float(tt.item())
 
     # (a) launch per step: bb_step_host = one kernel launch + one stream wait per step
     e2e_launch_value = timed_host_loop(sim.step_host)
     barrier()
     # (b) persistent server: bb_serve_step = doorbell in mapped pinned memory, no launch / stream wait per step
+    e2e_obs_launch_value = timed_host_loop(sim.step_host, with_obs=True)
+    barrier()
     if args.no_serve:   # profiler runs: a resident kernel cannot live under ncu's serialised replay
-        e2e_value = e2e_launch_value
+        e2e_serve_value, e2e_obs_serve_value = None, None
     else:
         sim.serve_begin()
-        e2e_value = timed_host_loop(sim.serve_step)
+        e2e_serve_value = timed_host_loop(sim.serve_step)
+        e2e_obs_serve_value = timed_host_loop(sim.serve_step, with_obs=True)
         sim.serve_end()
         barrier()
+    # the headline is whichever host path is faster on this box at this N (the server spins one host thread per rank;
+    # with many ranks on few cores launch-per-step can win): both are reported
+    e2e_value = max(v for v in (e2e_launch_value, e2e_serve_value) if v is not None)
+    e2e_path = "bb_serve_step" if e2e_value == e2e_serve_value else "bb_step_host"
+    e2e_obs_value = max(v for v in (e2e_obs_launch_value, e2e_obs_serve_value) if v is not None)
     h2d, d2h = n * 48, n * 16
 
     # ---------------------------------------------------------------- roofline
@@ -319,6 +378,9 @@ def run_engine(args):
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": ncu_traffic(f"bb_step_kernel@{n}"), "kernel": "bb_step_kernel", "worlds_per_launch": n,
                 "algorithmic_bytes_per_launch": n * BYTES_PER_WORLD_STEP, "peak_source": peak_src,
+                "traffic_note": "ncu --set full capture with ncu's default cache control (caches flushed before the launch, like the "
+                                "timed steps): DRAM reads = the state rows; the 11.7 MB of writes stay in the 126 MB L2 for the "
+                                "lifetime of the launch, so DRAM write bytes read 0",
                 "note": "8192 worlds (15 MB) is latency/launch-bound by construction; see roofline_hbm_bound"}
 
     roofline_large = None
@@ -357,10 +419,10 @@ def run_engine(args):
                                   "p90 = steps where most warps also run the shot / reset paths"}
         del bsim, big, bact
         threads = os.cpu_count() or 1
-        cv, cdt, cpu_steps = time_cpu_arm_for(args.worlds_per_gpu, args.cpu_seconds, threads)
+        cv, cdt, cpu_steps, cnote = time_cpu_arm_for(args.worlds_per_gpu, args.cpu_seconds, threads)
         cpu_baseline = {"value": cv, "unit": UNIT, "cores": threads, "kind": "port",
-                        "sample": f"{args.worlds_per_gpu} worlds x {cpu_steps} steps, {cdt:.1f} s of CPU work on {threads} threads; oracle/ "
-                                  "restatement on glibc libm (the reference's Madrona CPU executor cannot be built: submodule absent)"}
+                        "sample": f"{args.worlds_per_gpu} worlds x {cpu_steps} steps in one call, {cdt:.1f} s of CPU work on {threads} threads; "
+                                  f"{cnote} (the reference's Madrona CPU executor cannot be built: submodule absent)"}
 
     clocks = sampler.report()
     if rank == 0:
@@ -368,16 +430,23 @@ def run_engine(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": K, "warmup": Wm,
             "ms_per_step": max_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{args.worlds_per_gpu} worlds per GPU x {n_gpus} GPU = {total_worlds} worlds, 2 agents + ball per world, "
-                                   f"random actions for both agents (Threefry, seed {SEED}), sim seed 0",
+            "config": {"workload": workload_string(args.worlds_per_gpu, n_gpus),
                        "l2": "flushed before every timed step (256 MiB memset outside the per-step CUDA events)",
+                       "prewarm": f"{n_pw} untimed flush+step pairs ({PREWARM_S} s) before the W warm-up steps, so that the timed window "
+                                  "does not sit on the clock / launch-path ramp of an idle GPU",
                        "parallelism": f"world-sharded x{n_gpus}, no collective in the step"},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "what": "bb_serve_step per step (persistent server kernel, doorbell in mapped pinned memory): action rows "
-                            "read from pinned host memory over PCIe, fused step, reward+done written back to pinned host "
-                            "memory, call returns when they are there; synchronous, one step in flight",
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "path": e2e_path,
+                    "what": "per step: int32 action rows [N,2,6] read from pinned host memory over PCIe, fused step, reward + done "
+                            "written back to pinned host memory, the call returns when they are there; synchronous, one step in "
+                            "flight.  The 1024 B/world observation rows STAY ON THE DEVICE: the reference's consumer of them is "
+                            "a torch policy on the same device (env.py:75-79, ppo.py:66); see e2e_with_obs for the host-consumer case",
+                    "serve": {"value": e2e_serve_value, "unit": UNIT,
+                              "what": "bb_serve_step: persistent server kernel, doorbell in mapped pinned memory, no launch / stream wait per step"},
                     "launch_per_step": {"value": e2e_launch_value, "unit": UNIT,
-                                        "what": "same through bb_step_host: one kernel launch + one stream wait per step"}},
+                                        "what": "bb_step_host: one kernel launch + one stream wait per step"}},
+            "e2e_with_obs": {"value": e2e_obs_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h + n * 1024,
+                             "serve": e2e_obs_serve_value, "launch_per_step": e2e_obs_launch_value,
+                             "what": "same, with both agents' observation rows mirrored to pinned host memory too (a policy on the host)"},
             "gpu_launches": int(gpu_launches),
             "clocks": clocks,
             "roofline": roofline,

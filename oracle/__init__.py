@@ -53,11 +53,40 @@ def build(force: bool = False) -> None:
 _LIBS: Dict[str, ctypes.CDLL] = {}
 
 
-def _load(libm: bool) -> ctypes.CDLL:
-    name = "liboracle_libm.so" if libm else "liboracle.so"
+def build_native() -> str:
+    """The glibc-libm build once more, tuned for THIS host (-O3 -march=native, still -ffp-contract=off): the binary the
+    CPU arm of bench.py times, so that the baseline is not handicapped by a generic -O2 build.  Compiled on the machine
+    that runs it (the file name carries a hash of the CPU's feature flags: a library built in the container is never
+    loaded on a GPU box with a different CPU)."""
+    import hashlib
+
+    flags = ""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith(("flags", "model name")):
+                    flags += line
+                    if line.startswith("flags"):
+                        break
+    except OSError:
+        pass
+    tag = hashlib.sha256(flags.encode()).hexdigest()[:12]
+    out_dir = os.path.join(_HERE, "_native")
+    os.makedirs(out_dir, exist_ok=True)
+    path = os.path.join(out_dir, f"liboracle_libm_native_{tag}.so")
+    src = os.path.join(_HERE, "bb_oracle.cpp")
+    if not os.path.exists(path) or os.path.getmtime(path) < os.path.getmtime(src):
+        cmd = ["g++", "-std=c++17", "-O3", "-march=native", "-ffp-contract=off", "-fPIC", "-shared", "-pthread", "-DBB_USE_LIBM",
+               src, "-o", path, "-lm"]
+        subprocess.run(cmd, check=True, capture_output=True)
+    return path
+
+
+def _load(libm) -> ctypes.CDLL:
+    name = "native" if libm == "native" else ("liboracle_libm.so" if libm else "liboracle.so")
     if name in _LIBS:
         return _LIBS[name]
-    path = os.path.join(_HERE, name)
+    path = build_native() if libm == "native" else os.path.join(_HERE, name)
     if not os.path.exists(path):
         build()
     lib = ctypes.CDLL(path)
@@ -131,7 +160,7 @@ class Oracle:
 
     def __init__(self, num_worlds: int, discrete_x: int = 32, discrete_y: int = 17,
                  start_x: float = 31.515 / 2.0, start_y: float = 16.764 / 2.0,
-                 rand_seed: int = 0, flags: int = FLAG_TAG_MASK, libm: bool = False):
+                 rand_seed: int = 0, flags: int = FLAG_TAG_MASK, libm=False):
         self._lib = _load(libm)
         cfg = _Config(num_worlds, discrete_x, discrete_y, start_x, start_y, rand_seed, flags)
         self._h = self._lib.orc_create(ctypes.byref(cfg))

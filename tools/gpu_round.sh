@@ -1,10 +1,19 @@
+# One gpurun call of a round: GPU tests, both bench arms, floors, ncu launch list + --set full captures.
+#   gpurun --timeout 1500 -- 'bash tools/gpu_round.sh r02a'
+TAG=${1:-r02}
+O=gpurun_out
 set -x
-nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
-nproc > gpurun_out/nproc.txt
-python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
-python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?" >> gpurun_out/bench.err
-python bench.py --impl reference --steps 50 --warmup 5 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
-python bench.py --steps 5 --warmup 3 --cpu-seconds 0.2 --no-serve > gpurun_out/plain_bench.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 1000 --csv --log-file gpurun_out/launches_bench.csv python bench.py --steps 5 --warmup 3 --cpu-seconds 0.2 --no-serve > gpurun_out/ncu_bench.log 2>&1
-python tools/profile_step.py --worlds 1048576 --steps 72 > gpurun_out/plain_prof.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:bb_step_kernel -s 68 -c 2 -o gpurun_out/prof_step_1m python tools/profile_step.py --worlds 1048576 --steps 72 > gpurun_out/ncu_prof.log 2>&1
-python tools/profile_step.py --worlds 8192 --steps 72 > gpurun_out/plain_prof8k.log 2>&1 && ncu --set full --clock-control none --import-source on -k regex:bb_step_kernel -s 68 -c 2 -o gpurun_out/prof_step_8k python tools/profile_step.py --worlds 8192 --steps 72 > gpurun_out/ncu_prof8k.log 2>&1
-tail -3 gpurun_out/pytest_gpu.log; cat gpurun_out/bench.json; tail -2 gpurun_out/bench.err
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $O/${TAG}_smi.txt 2>&1
+nproc > $O/${TAG}_nproc.txt
+timeout 900 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest_gpu.log 2>&1; echo "pytest rc=$?" >> $O/${TAG}_pytest_gpu.log
+cp $O/ref_ppo_py_sps.json $O/${TAG}_ref_ppo_py_sps.json 2>/dev/null
+timeout 600 python bench.py --impl reference --steps 20 --warmup 5 > $O/${TAG}_bench_ref.json 2> $O/${TAG}_bench_ref.err
+timeout 600 python bench.py --steps 20 --warmup 5 > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?" >> $O/${TAG}_bench.err
+timeout 300 python tools/probe_floor.py > $O/${TAG}_floor.json 2> $O/${TAG}_floor.err
+if [ -z "$NO_NCU" ]; then
+timeout 300 python bench.py --steps 5 --warmup 3 --cpu-seconds 0.2 --no-serve > $O/${TAG}_plain_bench.log 2>&1 && timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/${TAG}_launches_bench.csv python bench.py --steps 5 --warmup 3 --cpu-seconds 0.2 --no-serve > $O/${TAG}_ncu_bench.log 2>&1
+for W in 8192 65536 1048576; do
+timeout 120 python tools/profile_step.py --worlds $W --steps 72 > $O/${TAG}_plain_prof_$W.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:bb_step_kernel -s 68 -c 1 -f -o $O/${TAG}_prof_step_$W python tools/profile_step.py --worlds $W --steps 72 > $O/${TAG}_ncu_prof_$W.log 2>&1
+done
+fi
+tail -3 $O/${TAG}_pytest_gpu.log; cat $O/${TAG}_bench.json; tail -2 $O/${TAG}_bench.err; cat $O/${TAG}_floor.json
