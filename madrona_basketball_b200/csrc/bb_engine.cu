@@ -16,6 +16,7 @@
  * float parity with the CPU oracle needs unfused multiply-add).
  */
 #include <cuda_runtime.h>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -78,117 +79,134 @@ struct StepParams {
 };
 
 /* ------------------------------ obs image --------------------------------- *
- * Observation rows (game.cpp:1256-1460, layout SURVEY App. A) are 55 % of the
- * step's bytes.  The lane pair of a world writes the ~100 distinct values of that
- * world once into a shared-memory "image" (feature k at word p(k) of a 109-word,
- * odd-stride row); then the warp emits both agents' 512-byte rows for its 16
- * worlds with 16-byte coalesced stores, lane L owning columns 4L..4L+3.  p(k)
- * puts k, k+4, k+8.. in consecutive words so those gathers are conflict-free.
- * Agent 1's row is a block permutation of agent 0's (self <-> opponent blocks,
- * scores and hoops swapped), so one image serves both rows. */
-/* kFeat = 108 feature slots: 0..103 row-0 image, 104..106 row-1 vec_to, 107 zero */
-constexpr int kFeatStride = 109;  /* odd */
-constexpr int kZeroFeat = 107;
+ * Observation rows (game.cpp:1256-1460, layout SURVEY App. A) are 55 % of the step's bytes.  Both 512-byte rows of a
+ * world are assembled in shared memory IN OUTPUT ORDER as 16-byte chunks (chunk c = columns 4c..4c+3; columns 104..127
+ * are zero and have no chunk), every chunk written with one 16-byte shared store and read back with one 16-byte shared
+ * load by the lane that stores it to global memory (lane L owns columns 4L..4L+3 of every row: each store instruction
+ * writes 512 contiguous bytes).  Lane (world, agent a) writes what it holds in registers: chunks 0..15 and 25 of its
+ * OWN row (game / ball / hoop header and its self block, game.cpp:1257-1322) and chunks 16..24 of its PARTNER's row
+ * (the partner's opponent block describes this agent, game.cpp:1378-1422; the block sits 38 columns further, i.e. two
+ * words off the self block's chunk phase, which is why it is written a second time rather than re-read misaligned).
+ * Same code in both lanes: no divergence, no table lookups.
+ *
+ * Image geometry (float4 units): world stride 58, row stride 27.  A quarter-warp of a 16-byte store is 4 worlds x 2
+ * rows -> float4 indices 58 j + 27 a + c -> bank groups (2 j + 3 a + c) mod 8, all different: conflict-free stores;
+ * loads read 26 consecutive float4.  kWPR worlds of the warp are staged per round (16: one round, 14.5 KB per warp,
+ * the latency-bound launch shapes; 8: two rounds, 7.3 KB per warp, the 16-warps-per-SM shape). */
 constexpr int kWorldsPerWarp = 16;
+constexpr int kImgWorld4 = 58;  /* float4 per world slot ( = 2 mod 8) */
+constexpr int kImgRow4 = 27;    /* row 1 of a world starts here (odd) */
+constexpr int kObsChunks = 26;  /* chunks with content: columns 0..103 */
 
-__host__ __device__ inline int feat_pos(int k) { return (k & 3) * 27 + (k >> 2); }
+BBD float4 f4(float a, float b, float c, float d) { return make_float4(a, b, c, d); }
 
-/* obs column -> feature, row of agent 0 */
-__host__ __device__ inline int row0_src(int cidx) { return (cidx >= 103 || (cidx >= 26 && cidx <= 29)) ? kZeroFeat : cidx; }
-/* obs column -> feature, row of agent 1 */
-__host__ __device__ inline int row1_src(int cidx)
+/* Derived floats of one agent's block (game.cpp:1293-1312), each computed once per step. */
+struct ObsDerived {
+    Vec3 vn; float vdot, accel;      /* velocity direction, dot with facing, acceleration factor */
+    Vec3 hoopDir; float hoopDist;    /* towards the hoop this agent attacks */
+    Vec3 ballDir; float ballDist;
+    Vec3 toMe; float dist;           /* the PARTNER's vec_to_agent / distance (game.cpp:1334,1381-1383): unit vector from the
+                                      * partner to this agent, and their distance (the same float in both directions) */
+};
+
+BBD ObsDerived obs_derive(const Lane &L, Vec3 opos, const SimConst &c)
 {
-    if (cidx >= 103) return kZeroFeat;
-    if (cidx == 5) return 6;
-    if (cidx == 6) return 5;
-    if (cidx >= 17 && cidx <= 19) return cidx + 3;
-    if (cidx >= 20 && cidx <= 22) return cidx - 3;
-    if (cidx >= 23 && cidx <= 25) return cidx + 38;
-    if (cidx >= 26 && cidx <= 29) return kZeroFeat;
-    if (cidx >= 30 && cidx <= 60) return cidx + 38;
-    if (cidx >= 61 && cidx <= 63) return cidx - 38;
-    if (cidx >= 64 && cidx <= 66) return cidx + 40;
-    if (cidx == 67) return 67;
-    if (cidx >= 68 && cidx <= 98) return cidx - 38;
-    return cidx;
+    const AgentS &A = L.A;
+    ObsDerived d;
+    const Vec3 zero = v3(0.f, 0.f, 0.f);
+    const bool moving = L.vel2 > 1e-6f;
+    /* normalize(v) = v * (1 / sqrt(length2(v))) with the sqrt shared with length(v) */
+    d.vn = moving ? A.vel * f_div(1.f, L.speed) : zero;
+    d.vdot = moving ? dot(d.vn, L.facing) : 0.f;
+    d.accel = (d.vdot <= 0.8f) ? 0.1f : 1.f;
+    const Vec3 dh = v3(L.me ? c.hoopX[0] : c.hoopX[1], c.hoopY, 0.f) - A.pos;
+    d.hoopDist = f_sqrt(len2(dh));
+    d.hoopDir = (d.hoopDist > 1e-6f) ? dh * f_div(1.f, d.hoopDist) : zero;
+    const Vec3 db = L.B.pos - A.pos;
+    d.ballDist = f_sqrt(len2(db));
+    d.ballDir = (d.ballDist > 1e-6f) ? db * f_div(1.f, d.ballDist) : zero;
+    const Vec3 v = A.pos - opos;
+    const float l2 = len2(v);
+    d.dist = f_sqrt(l2);
+    d.toMe = (l2 > 1e-6f) ? v * f_div(1.f, d.dist) : zero;
+    return d;
 }
 
-BBD void put(float *img, int k, float v) { img[feat_pos(k)] = v; }
-BBD void put3(float *img, int k, Vec3 v) { put(img, k, v.x); put(img, k + 1, v.y); put(img, k + 2, v.z); }
-
-/* System 18 (fillObservationsSystem, game.cpp:1175-1461): each lane writes its own
- * agent's 38-float block (self block of its row == opponent block of the partner's
- * row, game.cpp:1290-1322 / 1380-1421); lane 0 adds the game / ball / hoop header,
- * lane 1 the agent-to-agent vectors and the one-hots. */
-BBD void write_obs_image(float *img, const Lane &L, Vec3 opos, int32_t oInb, const SimConst &c)
+/* System 18 (fillObservationsSystem, game.cpp:1175-1461) for the lane's world: 26 chunk stores.
+ * own / other: float4 base of this agent's row / of the partner's row in the image. */
+BBD void write_obs_chunks(float4 *own, float4 *other, const Lane &L, const ObsDerived &d, Vec3 opos, int32_t oInb, const SimConst &c)
 {
     const AgentS &A = L.A;
     const BallS &B = L.B;
-    const int base = L.me ? 61 : 23;
-    {
-        Vec3 ov = rotate_vec(A.q, v3(0.f, 1.f, 0.f));
-        bool moving = len2(A.vel) > 1e-6f;
-        Vec3 vn = moving ? normalize(A.vel) : v3(0.f, 0.f, 0.f);
-        float vdot = moving ? dot(vn, ov) : 0.f;
-        Vec3 dh = v3(L.me ? c.hoopX[0] : c.hoopX[1], c.hoopY, 0.f) - A.pos; /* the hoop this agent attacks */
-        float hoopDist = len(dh);
-        Vec3 hoopDir = (hoopDist > 1e-6f) ? normalize(dh) : v3(0.f, 0.f, 0.f);
-        Vec3 db = B.pos - A.pos;
-        float ballDist = len(db);
-        Vec3 ballDir = (ballDist > 1e-6f) ? normalize(db) : v3(0.f, 0.f, 0.f);
-        /* offsets inside the block; [3..6] differ between self and opponent view (written below) */
-        put3(img, base + 0, A.pos);
-        put(img, base + 7, A.q.w); put(img, base + 8, A.q.x); put(img, base + 9, A.q.y); put(img, base + 10, A.q.z);
-        put3(img, base + 11, ov);
-        put3(img, base + 14, vn);
-        put(img, base + 17, len(A.vel));
-        put(img, base + 18, vdot);
-        put(img, base + 19, (vdot <= 0.8f) ? 0.1f : 1.f);
-        put3(img, base + 20, hoopDir);
-        put(img, base + 23, hoopDist);
-        put3(img, base + 24, ballDir);
-        put(img, base + 27, ballDist);
-        put(img, base + 28, (float)A.imInb);
-        put(img, base + 29, A.cooldown);
-        put(img, base + 30, A.maxSpeed);
-        put(img, base + 31, A.quickness);
-        put(img, base + 32, A.shooting);
-        put(img, base + 33, A.ftPct);
-        put(img, base + 34, A.reaction);
-        put(img, base + 35, A.curShot);
-        put(img, base + 36, (float)A.pointsWorth);
-        put(img, base + 37, (float)A.hasBall);
-    }
-    if (L.me == 0) {
-        const GameS &g = L.G;
-        put(img, 0, g.gameClock); put(img, 1, g.shotClock); put(img, 2, g.period);
-        put(img, 3, (float)g.inbInProgress); put(img, 4, g.inboundClock);
-        put(img, 5, g.team0Score); put(img, 6, g.team1Score);
-        put3(img, 7, B.pos); put3(img, 10, B.vel);
-        put(img, 13, (float)B.isGrabbed); put(img, 14, (float)B.inFlight);
-        put(img, 15, (float)B.spv); put(img, 16, (float)B.ltTeam);
-        put3(img, 17, hoop_pos(c, 1)); /* agent 0 attacks hoop 1 */
-        put3(img, 20, hoop_pos(c, 0));
+    const GameS &g = L.G;
+    const bool me = L.me != 0;
+    const Vec3 f = L.facing;
+    /* one-hots (game.cpp:1441-1452): ball holder; inbounder = last agent (index order) with imInbounding */
+    const int32_t id0 = L.idBase + 3, id1 = L.idBase + 4;
+    const int32_t inb0 = me ? oInb : A.imInb, inb1 = me ? A.imInb : oInb;
+    int32_t inbounder = -1;
+    if ((float)inb0 > 0.5f) inbounder = id0;
+    if ((float)inb1 > 0.5f) inbounder = id1;
+    const float oh99 = (id0 == B.holder) ? 1.f : 0.f, oh100 = (id1 == B.holder) ? 1.f : 0.f;
+    const float oh101 = (id0 == inbounder) ? 1.f : 0.f, oh102 = (id1 == inbounder) ? 1.f : 0.f;
+    const float atkX = me ? c.hoopX[0] : c.hoopX[1], defX = me ? c.hoopX[1] : c.hoopX[0];
+    const float imInb = (float)A.imInb, pw = (float)A.pointsWorth, has = (float)A.hasBall;
+    /* own row: header (columns 0..22) and self block (23..60) */
+    own[0] = f4(g.gameClock, g.shotClock, g.period, (float)g.inbInProgress);
+    own[1] = f4(g.inboundClock, me ? g.team1Score : g.team0Score, me ? g.team0Score : g.team1Score, B.pos.x);
+    own[2] = f4(B.pos.y, B.pos.z, B.vel.x, B.vel.y);
+    own[3] = f4(B.vel.z, (float)B.isGrabbed, (float)B.inFlight, (float)B.spv);
+    own[4] = f4((float)B.ltTeam, atkX, c.hoopY, 0.f);
+    own[5] = f4(defX, c.hoopY, 0.f, A.pos.x);
+    own[6] = f4(A.pos.y, A.pos.z, 0.f, 0.f);
+    own[7] = f4(0.f, 0.f, A.q.w, A.q.x);
+    own[8] = f4(A.q.y, A.q.z, f.x, f.y);
+    own[9] = f4(f.z, d.vn.x, d.vn.y, d.vn.z);
+    own[10] = f4(L.speed, d.vdot, d.accel, d.hoopDir.x);
+    own[11] = f4(d.hoopDir.y, d.hoopDir.z, d.hoopDist, d.ballDir.x);
+    own[12] = f4(d.ballDir.y, d.ballDir.z, d.ballDist, imInb);
+    own[13] = f4(A.cooldown, A.maxSpeed, A.quickness, A.shooting);
+    own[14] = f4(A.ftPct, A.reaction, A.curShot, pw);
+    own[15] = f4(has, opos.x, opos.y, opos.z);            /* 60 | opponent block [0..2] = the partner's position */
+    own[25] = f4(oh100, oh101, oh102, 0.f);
+    /* partner's row: its opponent block (columns 64..98) describes this agent; column 99 */
+    other[16] = f4(d.toMe.x, d.toMe.y, d.toMe.z, d.dist);
+    other[17] = f4(A.q.w, A.q.x, A.q.y, A.q.z);
+    other[18] = f4(f.x, f.y, f.z, d.vn.x);
+    other[19] = f4(d.vn.y, d.vn.z, L.speed, d.vdot);
+    other[20] = f4(d.accel, d.hoopDir.x, d.hoopDir.y, d.hoopDir.z);
+    other[21] = f4(d.hoopDist, d.ballDir.x, d.ballDir.y, d.ballDir.z);
+    other[22] = f4(d.ballDist, imInb, A.cooldown, A.maxSpeed);
+    other[23] = f4(A.quickness, A.shooting, A.ftPct, A.reaction);
+    other[24] = f4(A.curShot, pw, has, oh99);
+}
+
+/* Coalesced emission of both observation rows of `count` staged worlds (image slots 0..count-1) to the rows of worlds
+ * world0 .. world0+count-1.  kCount > 0: compile-time count, fully unrolled (one LDS.128 + one STG.128 per row). */
+template <int kCount>
+BBD void emit_obs_rows(const float4 *img, float *obs, int64_t world0, int count, int lane)
+{
+    float4 *dst = reinterpret_cast<float4 *>(obs + world0 * 256) + lane;
+    const bool has = lane < kObsChunks;
+    const float4 *src = img + (has ? lane : 0);
+    const float4 zero = f4(0.f, 0.f, 0.f, 0.f);
+    if (kCount > 0) {
+#pragma unroll
+        for (int j = 0; j < kCount; j++) {
+#pragma unroll
+            for (int r = 0; r < 2; r++) {
+                float4 v = zero;
+                if (has) v = src[j * kImgWorld4 + r * kImgRow4];
+                dst[j * 64 + r * 32] = v;
+            }
+        }
     } else {
-        /* vec_to_agent / distance (game.cpp:1334,1381-1383) seen from agent 0 and from agent 1 */
-        Vec3 v01 = A.pos - opos;
-        Vec3 v10 = opos - A.pos;
-        float l2 = len2(v01);
-        float dist = f_sqrt(l2);
-        Vec3 n01 = v3(0.f, 0.f, 0.f), n10 = v3(0.f, 0.f, 0.f);
-        if (l2 > 1e-6f) { float inv = f_div(1.f, dist); n01 = v01 * inv; n10 = v10 * inv; }
-        put3(img, 64, n01); put(img, 67, dist);
-        put3(img, 104, n10);
-        /* one-hots (game.cpp:1441-1452): ball holder; inbounder = last agent with imInbounding */
-        const int32_t id0 = L.idBase + 3, id1 = L.idBase + 4;
-        int32_t inbounder = -1;
-        if ((float)oInb > 0.5f) inbounder = id0;
-        if ((float)A.imInb > 0.5f) inbounder = id1;
-        put(img, 99, (id0 == B.holder) ? 1.f : 0.f);
-        put(img, 100, (id1 == B.holder) ? 1.f : 0.f);
-        put(img, 101, (id0 == inbounder) ? 1.f : 0.f);
-        put(img, 102, (id1 == inbounder) ? 1.f : 0.f);
-        put(img, kZeroFeat, 0.f);
+        for (int j = 0; j < count; j++) {
+            float4 v0 = zero, v1 = zero;
+            if (has) { v0 = src[j * kImgWorld4]; v1 = src[j * kImgWorld4 + kImgRow4]; }
+            dst[j * 64] = v0;
+            dst[j * 64 + 32] = v1;
+        }
     }
 }
 
@@ -390,39 +408,16 @@ BBD void prefetch_state_rows(const StepParams &p, int64_t world0, int worlds, in
 /* ------------------------------ kernels ----------------------------------- */
 constexpr int kMaxThreads = 128;
 constexpr int kInitThreads = 128;
-__host__ __device__ constexpr int smem_bytes_for(int threads) { return (threads / 32) * kWorldsPerWarp * kFeatStride * 4; }
-
-/* image word of every observation column, rows of agent 0 / agent 1 (filled by bb_create) */
-__constant__ uint8_t kEmitWord[2][128];
-
-/* Coalesced emission of both observation rows of the warp's worlds from the image. */
-BBD void emit_obs_rows(const float *warpImg, float *obs, int64_t warpWorld0, int nValid, int lane)
-{
-    int off[2][4];
-    {
-        const uchar4 o0 = reinterpret_cast<const uchar4 *>(kEmitWord[0])[lane];
-        const uchar4 o1 = reinterpret_cast<const uchar4 *>(kEmitWord[1])[lane];
-        off[0][0] = o0.x; off[0][1] = o0.y; off[0][2] = o0.z; off[0][3] = o0.w;
-        off[1][0] = o1.x; off[1][1] = o1.y; off[1][2] = o1.z; off[1][3] = o1.w;
-    }
-    float4 *dst = reinterpret_cast<float4 *>(obs + warpWorld0 * 256) + lane;
-#pragma unroll 4
-    for (int j = 0; j < nValid; j++) {
-        const float *img = warpImg + j * kFeatStride;
-        float4 r0 = make_float4(img[off[0][0]], img[off[0][1]], img[off[0][2]], img[off[0][3]]);
-        float4 r1 = make_float4(img[off[1][0]], img[off[1][1]], img[off[1][2]], img[off[1][3]]);
-        dst[j * 64] = r0;
-        dst[j * 64 + 32] = r1;
-    }
-}
+/* dynamic shared memory of a launch: one image of kWPR world slots per warp */
+__host__ __device__ constexpr int smem_bytes_for(int threads, int wpr) { return (threads / 32) * wpr * kImgWorld4 * 16; }
 
 #ifndef BB_MIN_BLOCKS_128
 #define BB_MIN_BLOCKS_128 4 /* resident 128-thread blocks per SM the register budget is cut for */
 #endif
 /* One Manager::step() for the 16 worlds [warpWorld0, warpWorld0 + 16) on the calling warp:
- * lane = (world (lane >> 1), agent (lane & 1)).  warpImg: this warp's observation image. */
-template <bool kSync>
-BBD void step_tile(const StepParams &p, const StepIo &io, float *warpImg, int64_t warpWorld0, int lane)
+ * lane = (world (lane >> 1), agent (lane & 1)).  warpImg: this warp's observation image (kWPR world slots). */
+template <bool kSync, int kWPR>
+BBD void step_tile(const StepParams &p, const StepIo &io, float4 *warpImg, int64_t warpWorld0, int lane)
 {
     const int64_t w = warpWorld0 + (lane >> 1);
     const bool valid = w < p.numWorlds;
@@ -434,32 +429,47 @@ BBD void step_tile(const StepParams &p, const StepIo &io, float *warpImg, int64_
     const bool tag = (p.sc.flags & BB_FLAG_TAG_MASK) != 0;
     const bool fast = __all_sync(kFullMask, tag && L.G.isOneOnOne == 1 && L.G.inbInProgress == 0);
     if (fast) pair_step_fast<kSync>(L, p.sc);                /* systems 1-17 */
-    else { Lane T = L; slow_step(&T, &p.sc, tag, kSync); L = T; } /* only the copy's address escapes */
+    else { Lane T = L; slow_step(&T, &p.sc, tag, kSync); L = T; finish_derived(L); } /* only the copy's address escapes */
     __syncwarp();
     const Vec3 opos = xorv(L.A.pos);
     const int32_t oInb = xori(L.A.imInb);
-    write_obs_image(warpImg + (lane >> 1) * kFeatStride, L, opos, oInb, p.sc); /* system 18 */
-    pair_reward(L, opos);                                    /* system 19 */
+    const ObsDerived d = obs_derive(L, opos, p.sc);
+    pair_reward(L, d.dist);                                  /* system 19 (reads nothing system 18 writes) */
     if (valid) store_lane(L, p, io, w);
-    __syncwarp();
     if (warpWorld0 >= p.numWorlds) return;
-    int64_t remain = p.numWorlds - warpWorld0;
-    int nValid = remain >= kWorldsPerWarp ? kWorldsPerWarp : (int)remain;
-    emit_obs_rows(warpImg, p.col.obs, warpWorld0, nValid, lane);
-    if (io.obsOut) emit_obs_rows(warpImg, io.obsOut, warpWorld0, nValid, lane);
+    const int64_t remain = p.numWorlds - warpWorld0;
+    const int nValid = remain >= kWorldsPerWarp ? kWorldsPerWarp : (int)remain;
+    /* system 18: stage kWPR worlds' rows in the image, emit them, next round */
+#pragma unroll
+    for (int rd = 0; rd < kWorldsPerWarp / kWPR; rd++) {
+        if (kWPR == kWorldsPerWarp || (lane >> 4) == rd) {
+            float4 *slot = warpImg + ((lane >> 1) & (kWPR - 1)) * kImgWorld4;
+            write_obs_chunks(slot + me * kImgRow4, slot + (me ^ 1) * kImgRow4, L, d, opos, oInb, p.sc);
+        }
+        __syncwarp();
+        const int left = nValid - rd * kWPR; /* staged worlds of this round that exist */
+        if (left >= kWPR) {
+            emit_obs_rows<kWPR>(warpImg, p.col.obs, warpWorld0 + rd * kWPR, kWPR, lane);
+            if (io.obsOut) emit_obs_rows<kWPR>(warpImg, io.obsOut, warpWorld0 + rd * kWPR, kWPR, lane);
+        } else if (left > 0) {
+            emit_obs_rows<0>(warpImg, p.col.obs, warpWorld0 + rd * kWPR, left, lane);
+            if (io.obsOut) emit_obs_rows<0>(warpImg, io.obsOut, warpWorld0 + rd * kWPR, left, lane);
+        }
+        if (rd + 1 < kWorldsPerWarp / kWPR) __syncwarp(); /* the next round overwrites the slots */
+    }
 }
 
-/* One Manager::step(): thread t = (world t/2, agent t%2).  blockDim.x is any multiple of
- * 32 up to kMaxT; dynamic shared memory = smem_bytes_for(blockDim.x).  kSync: see phase_sync. */
-template <int kMaxT, bool kSync>
+/* One Manager::step(): thread t = (world t/2, agent t%2).  blockDim.x is any multiple of 32 up to kMaxT; dynamic shared
+ * memory = smem_bytes_for(blockDim.x, kWPR).  kSync: see phase_sync; kWPR: worlds per observation round (16 or 8). */
+template <int kMaxT, bool kSync, int kWPR>
 __global__ void __launch_bounds__(kMaxT, BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_kernel(const __grid_constant__ StepParams p)
 {
-    extern __shared__ float smem[];
+    extern __shared__ float4 smem4[];
     /* programmatic dependent launch (bb_rollout): let the next kernel of the chain be scheduled early, and wait here for
      * the previous one to complete; both are no-ops for an ordinary launch */
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float *warpImg = smem + warp * kWorldsPerWarp * kFeatStride;
+    float4 *warpImg = smem4 + warp * kWPR * kImgWorld4;
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t warpWorld0 = (t - lane) >> 1;
     if (!kSync && warpWorld0 >= p.numWorlds) return; /* whole warp past the end (with barriers it shadows the last world) */
@@ -468,7 +478,7 @@ __global__ void __launch_bounds__(kMaxT, BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_ste
         const int64_t w0 = ((int64_t)blockIdx.x + p.prefetchBlocks) * wpb;
         if (w0 + wpb <= p.numWorlds) prefetch_state_rows(p, w0, wpb, lane);
     }
-    step_tile<kSync>(p, p.io, warpImg, warpWorld0, lane);
+    step_tile<kSync, kWPR>(p, p.io, warpImg, warpWorld0, lane);
 }
 
 /* ------------------------------ persistent server -------------------------- *
@@ -509,12 +519,12 @@ constexpr int kServeThreads = 32;
 __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_constant__ StepParams p, ServeHostCtl *hc, ServeDevCtl *dc,
                                                                   int32_t startSeq, uint64_t idleTimeoutNs)
 {
-    extern __shared__ float smem[];
+    extern __shared__ float4 smem4[];
     __shared__ int32_t sSeq;
     __shared__ StepIo sIo;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int warpsPerBlock = blockDim.x >> 5;
-    float *warpImg = smem + warp * kWorldsPerWarp * kFeatStride;
+    float4 *warpImg = smem4 + warp * kWorldsPerWarp * kImgWorld4;
     const int64_t numTiles = (p.numWorlds + kWorldsPerWarp - 1) / kWorldsPerWarp;
     int32_t seq = startSeq;
     uint64_t tSeen = 0;
@@ -560,7 +570,7 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
         if (sSeq == kServeExit) break;
         const StepIo io = sIo;
         for (int64_t tile = (int64_t)blockIdx.x * warpsPerBlock + warp; tile < numTiles; tile += (int64_t)gridDim.x * warpsPerBlock)
-            step_tile<false>(p, io, warpImg, tile * kWorldsPerWarp, lane);
+            step_tile<false, kWorldsPerWarp>(p, io, warpImg, tile * kWorldsPerWarp, lane);
         __syncthreads();
         if (threadIdx.x == 0) {
             __threadfence(); /* release (gpu scope): this block's writes before the count; the last block's
@@ -680,7 +690,7 @@ struct bb_engine {
     void *colPtr[26];
     bb::StepParams params;
     cudaStream_t hostStream; /* bb_step_host / setters */
-    int blockThreads, phaseSync, prefetchBlocks;
+    int blockThreads, phaseSync, prefetchBlocks, obsRound;
     int64_t launches;
     /* bb_step_n: graph of stepGraphN step kernels */
     cudaGraphExec_t stepGraphExec;
@@ -767,18 +777,31 @@ void host_threefry(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1, uint32_t 
  * schedulers (1 warp per block) until every SM holds a few.  Large counts are instruction-fetch /
  * HBM bound: big blocks whose warps re-align at phase barriers.  BB_BLOCK_THREADS (32..512) and
  * BB_PHASE_SYNC (0/1) override for tuning. */
-void pick_launch_shape(int64_t n_worlds, int *threads, int *sync)
+/* kLen2Le* / kLen2Ge* (bb_world.cuh) against this host's correctly rounded sqrtf: T is the last float whose root is
+ * still <= c (resp. the first whose root is >= c). */
+bool check_sqrt_thresholds()
+{
+    auto le_ok = [](float T, float c) { return sqrtf(T) <= c && !(sqrtf(nextafterf(T, INFINITY)) <= c); };
+    auto ge_ok = [](float T, float c) { return sqrtf(T) >= c && !(sqrtf(nextafterf(T, -INFINITY)) >= c); };
+    return le_ok(bb::kLen2LeHoopZone, bb::kHoopZone) && le_ok(bb::kLen2LeAgentSize, bb::kAgentSize) &&
+           ge_ok(bb::kLen2GeArc, bb::kArcRadius);
+}
+
+void pick_launch_shape(int64_t n_worlds, int *threads, int *sync, int *obs_round)
 {
     const int64_t warps = (n_worlds * 2 + 31) / 32;
-    if (warps <= 148 * 8) { *threads = 32; *sync = 0; }
-    else if (warps <= 148 * 32) { *threads = 64; *sync = 0; }
-    else { *threads = 128; *sync = 1; }
+    /* obs_round: worlds staged per observation round (image size per warp: 14.5 KB at 16, 7.3 KB at 8) */
+    if (warps <= 148 * 8) { *threads = 32; *sync = 0; *obs_round = 16; }
+    else if (warps <= 148 * 32) { *threads = 64; *sync = 0; *obs_round = 16; }
+    else { *threads = 128; *sync = 1; *obs_round = 8; }
     if (const char *s = getenv("BB_BLOCK_THREADS")) {
         int v = atoi(s);
         if (v >= 32 && v <= 512 && v % 32 == 0) *threads = v;
     }
     if (const char *s = getenv("BB_PHASE_SYNC")) *sync = atoi(s) != 0;
+    if (const char *s = getenv("BB_OBS_ROUND")) { int v = atoi(s); if (v == 8 || v == 16) *obs_round = v; }
     if (*threads == 32) *sync = 0;
+    if (*threads > 128) *obs_round = 8;
 }
 
 /* launch with programmaticStreamSerialization: the kernel may start while its predecessor in the stream is still
@@ -808,16 +831,21 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
     p.prefetchBlocks = host_mapped ? 0 : e->prefetchBlocks; /* no L2 prefetch of host-mapped rows */
     const int threads = e->blockThreads;
     const int blocks = (int)((e->N * 2 + threads - 1) / threads);
-    const int smem = bb::smem_bytes_for(threads);
-    if (pdl && threads <= 128 && !e->phaseSync) {
-        BB_CUDA_OK(launch_pdl(bb::bb_step_kernel<128, false>, blocks, threads, (size_t)smem, stream, true, p));
-    } else if (threads <= 128) {
-        if (e->phaseSync) bb::bb_step_kernel<128, true><<<blocks, threads, smem, stream>>>(p);
-        else bb::bb_step_kernel<128, false><<<blocks, threads, smem, stream>>>(p);
+    const int wpr = e->obsRound;
+    const int smem = bb::smem_bytes_for(threads, wpr);
+    pdl = pdl && threads <= 128 && !e->phaseSync;
+#define BB_LAUNCH_STEP(MAXT, SYNC, WPR)                                                                          \
+    do {                                                                                                         \
+        if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_step_kernel<MAXT, SYNC, WPR>, blocks, threads, (size_t)smem, stream, true, p)); \
+        else bb::bb_step_kernel<MAXT, SYNC, WPR><<<blocks, threads, smem, stream>>>(p);                          \
+    } while (0)
+    if (threads <= 128) {
+        if (e->phaseSync) { if (wpr == 8) BB_LAUNCH_STEP(128, true, 8); else BB_LAUNCH_STEP(128, true, 16); }
+        else              { if (wpr == 8) BB_LAUNCH_STEP(128, false, 8); else BB_LAUNCH_STEP(128, false, 16); }
     } else {
-        if (e->phaseSync) bb::bb_step_kernel<512, true><<<blocks, threads, smem, stream>>>(p);
-        else bb::bb_step_kernel<512, false><<<blocks, threads, smem, stream>>>(p);
+        if (e->phaseSync) BB_LAUNCH_STEP(512, true, 8); else BB_LAUNCH_STEP(512, false, 8);
     }
+#undef BB_LAUNCH_STEP
     e->launches++;
     BB_CUDA_OK(cudaGetLastError());
     return 0;
@@ -907,22 +935,25 @@ bb_engine *bb_create(const bb_config *cfg)
     e->params.numWorlds = e->N;
     e->params.prefetchBlocks = 0;
 
-    pick_launch_shape(e->N, &e->blockThreads, &e->phaseSync);
+    pick_launch_shape(e->N, &e->blockThreads, &e->phaseSync, &e->obsRound);
+    if (!check_sqrt_thresholds()) {
+        set_error("bb_create: the squared-length thresholds of bb_world.cuh do not match this host's sqrtf");
+        cudaFree(e->slab);
+        delete e;
+        return nullptr;
+    }
     /* L2 prefetch of a later block's rows: measured SLOWER on B200 (2^20 worlds: 340 us -> 380-390 us at
      * distances of 296..2368 blocks, gpurun exp1), so it is off unless BB_PREFETCH_BLOCKS asks for it. */
     e->prefetchBlocks = 0;
     if (const char *s = getenv("BB_PREFETCH_BLOCKS")) e->prefetchBlocks = atoi(s);
-    if (bb::smem_bytes_for(512) > 48 * 1024) {
-        cudaFuncSetAttribute(bb::bb_step_kernel<512, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::smem_bytes_for(512));
-        cudaFuncSetAttribute(bb::bb_step_kernel<512, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::smem_bytes_for(512));
-    }
-    {
-        uint8_t words[2][128];
-        for (int cidx = 0; cidx < 128; cidx++) {
-            words[0][cidx] = (uint8_t)bb::feat_pos(bb::row0_src(cidx));
-            words[1][cidx] = (uint8_t)bb::feat_pos(bb::row1_src(cidx));
-        }
-        cudaMemcpyToSymbol(bb::kEmitWord, words, sizeof words);
+    { /* the 16-world image of a 128-thread block is 58 KB: above the 48 KB default */
+        const int big = bb::smem_bytes_for(512, 8);
+        cudaFuncSetAttribute(bb::bb_step_kernel<128, true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_step_kernel<128, true, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_step_kernel<128, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_step_kernel<128, false, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_step_kernel<512, true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_step_kernel<512, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
     }
     if (cudaStreamCreateWithFlags(&e->hostStream, cudaStreamNonBlocking) != cudaSuccess) {
         set_error("bb_create: cudaStreamCreate failed");
@@ -1031,7 +1062,7 @@ int bb_step_host(bb_engine *e, const int32_t *actions_host, float *reward_host, 
 
 static int serve_launch(bb_engine *e)
 {
-    const int smem = bb::smem_bytes_for(bb::kServeThreads);
+    const int smem = bb::smem_bytes_for(bb::kServeThreads, bb::kWorldsPerWarp);
     int perSm = 0, sms = 0;
     BB_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, bb::bb_serve_kernel, bb::kServeThreads, smem));
     BB_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.gpu_id));

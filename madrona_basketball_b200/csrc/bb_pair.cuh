@@ -34,7 +34,20 @@ struct Lane {
     int32_t idBase;
     int32_t me;      /* 0 / 1: agent index == team index == defended hoop */
     bool didReset;
+    /* derived values of the lane's agent, valid from the end of systems 1-17 on (set by pair_step_fast, or by
+     * finish_derived after the slow path): what collision, defence, observations and reward would each recompute */
+    Vec3 facing;     /* q.rotateVec({0,1,0}) */
+    float vel2, speed; /* length2 / length of the velocity */
+    bool qDirty;     /* the orientation changed after `facing` was taken (shot, reset) */
 };
+
+BBD void finish_derived(Lane &L)
+{
+    L.facing = rotate_vec(L.A.q, v3(0.f, 1.f, 0.f));
+    L.vel2 = len2(L.A.vel);
+    L.speed = f_sqrt(L.vel2);
+    L.qDirty = false;
+}
 
 /* Partner exchange.  Always warp-wide: the fast / slow choice is made per WARP
  * (the slow path is valid for every world), so all 32 lanes reach every exchange. */
@@ -136,7 +149,7 @@ BBD void pair_shoot_turn(Lane &L, const SimConst &c, int k, Vec3 apos, Vec3 dpos
         going_in = closest_sq <= radius * radius;
     }
     Quat rot = rotation_between(v3(0.f, 1.f, 0.f), shot, c);
-    if (acting) L.A.q = rot;
+    if (acting) { L.A.q = rot; L.qDirty = true; }
     BallS &B = L.B;
     const int32_t aid = L.idBase + 3 + k;
     if (B.holder == aid) {
@@ -186,6 +199,7 @@ BBD void pair_reset_world(Lane &L, const SimConst &c)
     A.q = i ? c.spawnQ[1] : c.spawnQ[0];
     A.cooldown = 0.f; A.points = 0.f; A.fouls = 0.f;
     A.vel = v3(0.f, 0.f, 0.f);
+    L.vel2 = 0.f; L.speed = 0.f; L.qDirty = true; /* sqrt(0) == 0 */
     /* the three draws of helper.cpp:121,122,132, replicated */
     Vec3 base = v3(c.startX + (0.f * 2.f), c.startY, 0.f);
     float xd = pair_uniform(L, c, -kStartDev, kStartDev);
@@ -224,12 +238,18 @@ BBD void pair_collision(Lane &L, Vec3 opos)
     const float hw = kShoulderWidth / 2.0f, hd = kAgentDepth / 2.0f;
     const int me = L.me;
     const Vec3 c = L.A.pos;
-    const Vec3 f = rotate_vec(L.A.q, v3(0.f, 1.f, 0.f));
+    const Vec3 f = L.facing;
     const Vec3 r = v3(f.y, -f.x, 0.f);
     const Vec3 hwv = r * hw, hdv = f * hd;
     const Vec3 mv[4] = {c - hdv + hwv, c - hdv - hwv, c + hdv - hwv, c + hdv + hwv};
     const Vec3 ov[4] = {xorv(mv[0]), xorv(mv[1]), xorv(mv[2]), xorv(mv[3])};
-    const Vec3 axes[2] = {normalize(r), normalize(f)};
+    /* normalize(r), normalize(f): length2(r) = (f.y*f.y + f.x*f.x) + 0 and length2(f) = (f.x*f.x + f.y*f.y) + f.z*f.z are the
+     * same float whenever f.z is +-0 (IEEE addition commutes) -- always, for the z-rotations the game produces -- so the
+     * two axes share one 1/sqrt; a warp that holds any other orientation computes r's own. */
+    const float invf = f_div(1.f, f_sqrt(len2(f)));
+    float invr = invf;
+    if (__any_sync(kFullMask, f.z != 0.f)) invr = f_div(1.f, f_sqrt(len2(r)));
+    const Vec3 axes[2] = {r * invr, f * invf};
     bool coll = true;
     float minOv = FLT_MAX;
     Vec3 mtv = v3(0.f, 0.f, 0.f);
@@ -304,7 +324,7 @@ BBD void pair_defense(Lane &L, Vec3 opos, int32_t ohas, const SimConst &c)
     }
     D.move = 1;
     D.moveAngle = best_k;
-    Vec3 ov = rotate_vec(D.q, v3(0.f, 1.f, 0.f));
+    Vec3 ov = L.facing;
     float ang = bb_acosf(clampf(dot(ov, dir), -1.f, 1.f));
     if (ang > kPi / 8.f) {
         float cr = ov.x * mv.y - ov.y * mv.x;
@@ -317,10 +337,11 @@ BBD void pair_defense(Lane &L, Vec3 opos, int32_t ohas, const SimConst &c)
 }
 
 /* rewardSystem (game.cpp:811-870) for the lane's agent */
-BBD void pair_reward(Lane &L, Vec3 opos)
+/* dist_other: |other.pos - pos| (game.cpp:825); the caller passes the agent-to-agent distance the observation rows
+ * already hold -- the squared differences are the same floats in either direction */
+BBD void pair_reward(Lane &L, float dist_other)
 {
     AgentS &A = L.A;
-    float dist_other = len(opos - A.pos);
     if ((float)L.me == L.G.teamInPoss) {
         if (L.G.gameClock > 5.f) {
             const int32_t id = my_id(L);
@@ -352,13 +373,16 @@ BBD void pair_step_fast(Lane &L, const SimConst &c)
     const int me = L.me;
     sys_tick(A);                       /* 1 */
     sys_action_mask<true>(A, g);       /* 2 */
-    sys_move_agent(A, c);              /* 3 */
+    sys_move_agent(A, c, L.facing);    /* 3 */
+    L.qDirty = false;
+    L.vel2 = len2(A.vel);
+    L.speed = f_sqrt(L.vel2);
     /* 4 grab, 5 pass: can_grab == can_pass == 0 under the tag mask -> both return at once */
     phase_sync<kSync>();
     Vec3 opos = xorv(A.pos);
     {                                  /* 6 shoot: agent 0's turn, then agent 1's */
         const int32_t wants = (A.canShoot != 0 && A.shoot != 0) ? 1 : 0;
-        const float vlen = len(A.vel);
+        const float vlen = L.speed;
         const int32_t ovmove = xori(A.move), owants = xori(wants);
         const float ovlen = xorf(vlen);
 #pragma unroll 1
@@ -374,7 +398,7 @@ BBD void pair_step_fast(Lane &L, const SimConst &c)
         const int32_t holds = (A.hasBall == 1 && B.isGrabbed == 1 && B.holder == my_id(L)) ? 1 : 0;
         const int32_t oholds = xori(holds);
         if (holds) B.pos = A.pos; else if (oholds) B.pos = opos;
-        if (!(len(B.vel) == 0.f || B.isGrabbed == 1)) {
+        if (!(len2(B.vel) == 0.f || B.isGrabbed == 1)) { /* sqrt(x) == 0 <=> x == 0 */
             float nx = clampf(B.pos.x + B.vel.x, 0.f, c.width);
             float ny = clampf(B.pos.y + B.vel.y, 0.f, c.height);
             float nz = B.pos.z + B.vel.z;
@@ -386,8 +410,7 @@ BBD void pair_step_fast(Lane &L, const SimConst &c)
 #pragma unroll
     for (int h = 0; h < 2; h++) {      /* 9 score (game.cpp:873-953), 1-v-1 branch */
         float dx = B.pos.x - c.hoopX[h], dy = B.pos.y - c.hoopY;
-        float dist = f_sqrt(dx * dx + dy * dy);
-        if (dist <= kHoopZone && (float)B.inFlight == 1.f) {
+        if (dx * dx + dy * dy <= kLen2LeHoopZone && (float)B.inFlight == 1.f) { /* sqrt(..) <= kHoopZone */
             int32_t points = B.spv;
             if (my_id(L) == B.sbAgent) A.points += (float)((me == h) ? -B.spv : B.spv);
             if (L.idBase + h == g.team0Hoop) g.team1Score += (float)points;
@@ -408,7 +431,7 @@ BBD void pair_step_fast(Lane &L, const SimConst &c)
         }
     }
     {                                  /* 11 updateLastTouch (game.cpp:1034-1051): the later agent wins */
-        const int32_t touch = (len(B.pos - A.pos) <= kAgentSize) ? 1 : 0;
+        const int32_t touch = (len2(B.pos - A.pos) <= kLen2LeAgentSize) ? 1 : 0; /* length <= kAgentSize */
         const int32_t otouch = xori(touch);
         const int32_t t0 = me ? otouch : touch, t1 = me ? touch : otouch;
         if (t1) { B.ltAgent = L.idBase + 4; B.ltTeam = 1; }
@@ -425,6 +448,7 @@ BBD void pair_step_fast(Lane &L, const SimConst &c)
     }
     /* 13 inboundViolation: needs inboundingInProgress > 0.5 -> nothing on this path */
     if (L.resetNow != 0) { pair_reset_world(L, c); L.resetNow = 0; } /* 14 */
+    if (__any_sync(kFullMask, L.qDirty)) L.facing = rotate_vec(A.q, v3(0.f, 1.f, 0.f)); /* the orientation is final here */
     A.pointsWorth = shot_point_value(A.pos, v3(me ? c.hoopX[0] : c.hoopX[1], c.hoopY, 0.f)); /* 15 */
     phase_sync<kSync>();
     opos = xorv(A.pos);

@@ -89,6 +89,16 @@ BBD float len(Vec3 a) { return f_sqrt(len2(a)); }
 BBD Vec3 normalize(Vec3 a) { float inv = f_div(1.f, f_sqrt(len2(a))); return a * inv; }
 BBD float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 
+/* Distance tests without the square root.  IEEE sqrt is monotone, so for a constant c the set
+ * { s >= 0 : sqrt_rn(s) <= c } is an interval [0, T] and { s : sqrt_rn(s) >= c } is [T', inf): comparing the squared
+ * length with T / T' gives the SAME verdict as the reference's `length() <= c` for every float (NaN included: both sides
+ * compare false).  T = largest float with sqrtf(T) <= c, T' = smallest with sqrtf(T') >= c; bb_create re-derives them
+ * with the host's sqrtf and refuses to start on a mismatch (check_sqrt_thresholds), tests/test_abi_cpu.py sweeps 2e5
+ * neighbouring floats on each side. */
+constexpr float kLen2LeHoopZone = 0x1.47ae16p-7f;   /* length <= kHoopZone (0.1f)   */
+constexpr float kLen2LeAgentSize = 0x1.47ae16p-5f;  /* length <= kAgentSize (0.2f)  */
+constexpr float kLen2GeArc = 0x1.a3573cp+5f;        /* length >= kArcRadius (7.24f) */
+
 BBD Quat qmul(Quat a, Quat b)
 {
     Quat r;
@@ -224,14 +234,14 @@ BBD Vec3 vector_to_center(Vec3 pos, const SimConst &c) { return normalize(v3(c.s
 /* helper.cpp:50-81 */
 BBD int32_t shot_point_value(Vec3 shot_pos, Vec3 hoop)
 {
-    float dist = len(shot_pos - hoop);
+    const float dist2 = len2(shot_pos - hoop); /* `dist >= kArcRadius` as a test on the squared length, see kLen2GeArc */
     bool corner = (shot_pos.y < kCourtMinY + kCorner3Side) || (shot_pos.y > kCourtMinY + kCourtWid - kCorner3Side);
     if (corner) {
         bool left = hoop.x < kWorldW / 2.0f;
         if (left) { if (shot_pos.x <= kCourtMinX + kCorner3Len) return 3; }
         else      { if (shot_pos.x >= kCourtMinX + kCourtLen - kCorner3Len) return 3; }
     }
-    if (dist >= kArcRadius) return 3;
+    if (dist2 >= kLen2GeArc) return 3;
     return 2;
 }
 
@@ -399,19 +409,22 @@ BBD void sys_action_mask(AgentS &A, const GameS &g)
 }
 
 /* game.cpp:410-486 */
-BBD void sys_move_agent(AgentS &A, const SimConst &c)
+/* facing: q.rotateVec({0,1,0}) of the orientation after the turn (game.cpp:439), handed back so the lane-pair
+ * path can reuse it for collision / defence / observations while the orientation stays what it is here */
+BBD void sys_move_agent(AgentS &A, const SimConst &c, Vec3 &facing)
 {
     if (A.rotate != 0) {
         Quat t = (A.rotate == 1) ? c.turnPos : c.turnNeg;
         A.q = qmul(t, A.q);
     }
+    Vec3 ov = rotate_vec(A.q, v3(0.f, 1.f, 0.f));
+    facing = ov;
     if (A.canMove == 0) return;
     float s, co;
     if ((uint32_t)A.moveAngle < 8u) { s = c.moveSin[A.moveAngle]; co = c.moveCos[A.moveAngle]; }
     else { float ang = (float)A.moveAngle * kAngleBetweenDirs; s = bb_sinf(ang); co = bb_cosf(ang); }
     Vec3 delta = (v3(s, -co, 0.f) * A.quickness) * (float)A.move;
     float maxS = A.maxSpeed;
-    Vec3 ov = rotate_vec(A.q, v3(0.f, 1.f, 0.f));
     float d = 0.f;
     if (len2(A.vel) > 1e-6f) d = dot(normalize(A.vel), ov);
     if (d < -0.1f) { maxS *= .1f; delta = delta * .1f; }
@@ -803,7 +816,7 @@ BBD void step_world_logic(World &W, const SimConst &c)
 #pragma unroll
     for (int i = 0; i < 2; i++) sys_action_mask<kTagMask>(W.a[i], W.g);
 #pragma unroll
-    for (int i = 0; i < 2; i++) sys_move_agent(W.a[i], c);
+    for (int i = 0; i < 2; i++) { Vec3 facing; sys_move_agent(W.a[i], c, facing); }
     if (!kTagMask) {
 #pragma unroll
         for (int i = 0; i < 2; i++) sys_grab(W, i);
