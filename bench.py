@@ -227,14 +227,23 @@ def run_engine(args):
 
     K, Wm = args.steps, args.warmup
     total_worlds = args.worlds_per_gpu * n_gpus
-    shard = ShardedSimulator(total_worlds, rank=rank, world_size=n_gpus, gpu_id=local_rank)
-    sim, n = shard.sim, shard.num_worlds
+    n = args.worlds_per_gpu
+    # `value` times K back-to-back step launches between ONE pair of CUDA events, as the bench contract words it.  So that
+    # no launch finds its rows in the 126 MB L2 ("inputs larger than L2"), the rank owns R independent shards of `n` worlds
+    # (R x n x 1872 B >= 2.5 x L2) and every launch advances the next shard, round-robin: by the time a shard comes round
+    # again 2.5 L2 sizes of other rows have passed through the cache.  One launch = one Manager::step() over n worlds.
+    l2_bytes = torch.cuda.get_device_properties(dev).L2_cache_size
+    R = max(2, -(-int(2.5 * l2_bytes) // (n * BYTES_PER_WORLD_STEP)))
+    shards = [ShardedSimulator(total_worlds * R, rank=rank * R + i, world_size=n_gpus * R, gpu_id=local_rank) for i in range(R)]
+    shard = shards[0]
+    sim = shard.sim
+    assert all(sh.num_worlds == n for sh in shards)
     sampler = ClockSampler(local_rank)
 
-    # inputs resident in HBM before the timed region: one action batch per step
+    # inputs resident in HBM before the timed region: one action batch per step and shard slot
     actions = torch.empty((K + Wm, n, 2, 6), dtype=torch.int32, device=dev)
     for s in range(K + Wm):
-        shard.fill_actions(SEED, s, out=actions[s])
+        shards[s % R].fill_actions(SEED, s, out=actions[s])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     torch.cuda.synchronize()
 
@@ -243,43 +252,75 @@ def run_engine(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---------------------------------------------------------------- value: device-resident, per-step events
+    # ---------------------------------------------------------------- value: device-resident, cold rows, K launches in one event pair
     # Declared device pre-warm (stated in config.prewarm): an idle GPU needs a few hundred milliseconds of work before its
     # clocks and the driver's launch path reach steady state; with --steps 20 --warmup 5 the timed window would otherwise
-    # sit on that ramp.  Same flush + step pairs as the timed loop, at least PREWARM_S seconds and 50 pairs, then the W
-    # warm-up steps as passed.
+    # sit on that ramp.  Same launches as the timed loop, at least PREWARM_S seconds, then the W warm-up steps as passed.
+    # launches pre-bound (pointer / stream look-ups done once): a Python-level step_with_actions call costs ~10 us of host
+    # time, more than the kernel lasts, and the timed loop must not be host-bound
+    bound = {}
+
+    def launch(shard_idx, batch):
+        key = (shard_idx, batch)
+        if key not in bound:
+            bound[key] = shards[shard_idx].sim.bind_step_with_actions(actions[batch])
+        bound[key]()
+
     t_pw, n_pw = time.perf_counter(), 0
-    while n_pw < 50 or time.perf_counter() - t_pw < PREWARM_S:
-        flush.zero_()
-        sim.step_with_actions(actions[n_pw % (K + Wm)])
+    while n_pw < 4 * R or time.perf_counter() - t_pw < PREWARM_S:
+        launch(n_pw % R, n_pw % (K + Wm))
         n_pw += 1
-        if n_pw % 16 == 0:
+        if n_pw % 64 == 0:
             torch.cuda.synchronize()
     torch.cuda.synchronize()
     for s in range(Wm):
-        flush.zero_()
-        sim.step_with_actions(actions[s])
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    stops = [torch.cuda.Event(enable_timing=True) for _ in range(K)]
-    launches0 = sim.launch_count()
+        launch((n_pw + s) % R, s)
+    first = (n_pw + Wm) % R
+    timed = [shards[(first + s) % R].sim.bind_step_with_actions(actions[Wm + s]) for s in range(K)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = sum(sh.sim.launch_count() for sh in shards)
     barrier()
     with sampler:
         wall0 = time.perf_counter()
-        for s in range(K):
-            flush.zero_()                      # L2 flush, outside the events
-            starts[s].record()
-            sim.step_with_actions(actions[Wm + s])
-            stops[s].record()
+        e0.record()
+        for call in timed:
+            call()
+        e1.record()
         barrier()
         wall = time.perf_counter() - wall0
-    gpu_launches = sim.launch_count() - launches0
-    step_ms = [a.elapsed_time(b) for a, b in zip(starts, stops)]
-    dev_ms = float(sum(step_ms))
+    gpu_launches = sum(sh.sim.launch_count() for sh in shards) - launches0
+    dev_ms = float(e0.elapsed_time(e1))
     t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
     if world_size > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     max_ms = float(t.item())
     value = total_worlds * K / (max_ms * 1e-3)
+
+    # ---------------------------------------------------------------- latency of ONE isolated step, L2 flushed (informational)
+    # Round 1's `value`: a 256 MiB memset before every step and one event pair around each launch.  It carries the
+    # launch + event floor of an idle stream, which `null_floor_us` measures with an empty-handed 1-element kernel in the
+    # same place; kept so that the two rounds can be compared.
+    one = torch.zeros(1, device=dev)
+    lat = {}
+    for name, fn in (("null_floor_us", lambda s: one.add_(1.0)), ("step_us", lambda s: sim.step_with_actions(actions[s % (K + Wm)]))):
+        reps = max(K, 50)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
+        for s in range(3):
+            flush.zero_()
+            fn(s)
+        torch.cuda.synchronize()
+        for s in range(reps):
+            flush.zero_()
+            ev[s][0].record()
+            fn(s)
+            ev[s][1].record()
+        torch.cuda.synchronize()
+        ms = sorted(a.elapsed_time(b) for a, b in ev)
+        lat[name] = {"mean": 1e3 * sum(ms) / len(ms), "median": 1e3 * ms[len(ms) // 2]}
+    tl = torch.tensor([lat["step_us"]["mean"]], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(tl, op=dist.ReduceOp.MAX)
+    flushed_value = total_worlds / (float(tl.item()) * 1e-6)
 
     # ---------------------------------------------------------------- L2-warm, graph-launched (informational)
     g = torch.cuda.CUDAGraph()
@@ -293,7 +334,6 @@ def run_engine(args):
             sim.step_with_actions(actions[Wm + s])
     g.replay()
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with sampler:
         e0.record()
         g.replay()
@@ -328,6 +368,8 @@ def run_engine(args):
     h_rew = torch.empty((n, 2), dtype=torch.float32).pin_memory()
     h_done = torch.empty((n, 2), dtype=torch.float32).pin_memory()
     np_act = [a.numpy() for a in h_act]
+    h_act8 = [actions[s].to(torch.uint8).cpu().pin_memory() for s in range(ring)]   # packed rows (declared extension)
+    np_act8 = [a.numpy() for a in h_act8]
     np_rew, np_done = h_rew.numpy(), h_done.numpy()
     h_obs = torch.empty((n, 2, 128), dtype=torch.float32).pin_memory()
     np_obs = h_obs.numpy()
@@ -356,20 +398,26 @@ def run_engine(args):
     # (b) persistent server: bb_serve_step = doorbell in mapped pinned memory, no launch / stream wait per step
     e2e_obs_launch_value = timed_host_loop(sim.step_host, with_obs=True)
     barrier()
+    e2e_launch8_value = timed_host_loop(sim.step_host, acts=np_act8)
+    barrier()
     if args.no_serve:   # profiler runs: a resident kernel cannot live under ncu's serialised replay
-        e2e_serve_value, e2e_obs_serve_value = None, None
+        e2e_serve_value, e2e_obs_serve_value, e2e_serve8_value = None, None, None
     else:
         sim.serve_begin()
         e2e_serve_value = timed_host_loop(sim.serve_step)
+        e2e_serve8_value = timed_host_loop(sim.serve_step, acts=np_act8)
         e2e_obs_serve_value = timed_host_loop(sim.serve_step, with_obs=True)
         sim.serve_end()
         barrier()
-    # the headline is whichever host path is faster on this box at this N (the server spins one host thread per rank;
-    # with many ranks on few cores launch-per-step can win): both are reported
-    e2e_value = max(v for v in (e2e_launch_value, e2e_serve_value) if v is not None)
-    e2e_path = "bb_serve_step" if e2e_value == e2e_serve_value else "bb_step_host"
+    # the headline is whichever host path is fastest on this box at this N (the server spins one host thread per rank;
+    # with many ranks on few cores launch-per-step can win): all are reported
+    paths = {"bb_serve_step_u8": e2e_serve8_value, "bb_step_host_u8": e2e_launch8_value,
+             "bb_serve_step": e2e_serve_value, "bb_step_host": e2e_launch_value}
+    e2e_path = max((k for k in paths if paths[k] is not None), key=lambda k: paths[k])
+    e2e_value = paths[e2e_path]
+    e2e_i32_value = max(v for v in (e2e_launch_value, e2e_serve_value) if v is not None)
     e2e_obs_value = max(v for v in (e2e_obs_launch_value, e2e_obs_serve_value) if v is not None)
-    h2d, d2h = n * 48, n * 16
+    h2d, d2h = n * (12 if e2e_path.endswith("_u8") else 48), n * 16
 
     # ---------------------------------------------------------------- roofline
     peak, peak_src = measured_peak_gbs()
@@ -387,7 +435,7 @@ def run_engine(args):
     cpu_baseline = None
     if rank == 0 and n_gpus == 1:
         # HBM-bound regime: 2^20 worlds on one GPU, same kernel
-        del sim, shard
+        del sim, shard, shards
         big = ShardedSimulator(LARGE_WORLDS, rank=0, world_size=1, gpu_id=local_rank)
         bsim = big.sim
         # Step time depends on the episode phase (every world shares one RNG stream and spawn, so shots and
@@ -431,20 +479,27 @@ def run_engine(args):
             "ms_per_step": max_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_string(args.worlds_per_gpu, n_gpus),
-                       "l2": "flushed before every timed step (256 MiB memset outside the per-step CUDA events)",
-                       "prewarm": f"{n_pw} untimed flush+step pairs ({PREWARM_S} s) before the W warm-up steps, so that the timed window "
-                                  "does not sit on the clock / launch-path ramp of an idle GPU",
+                       "l2": f"inputs larger than L2: every launch advances the next of {R} independent {n}-world shards on this GPU "
+                             f"({R * n * BYTES_PER_WORLD_STEP / 1e6:.0f} MB of rows per cycle against a {l2_bytes / 1e6:.0f} MB L2), so each of the K timed "
+                             "launches reads its rows from HBM; K launches back to back between one pair of CUDA events",
+                       "prewarm": f"{n_pw} untimed launches of the same cycle ({PREWARM_S} s) before the W warm-up steps, so that the timed "
+                                  "window does not sit on the clock / launch-path ramp of an idle GPU",
                        "parallelism": f"world-sharded x{n_gpus}, no collective in the step"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "path": e2e_path,
-                    "what": "per step: int32 action rows [N,2,6] read from pinned host memory over PCIe, fused step, reward + done "
-                            "written back to pinned host memory, the call returns when they are there; synchronous, one step in "
-                            "flight.  The 1024 B/world observation rows STAY ON THE DEVICE: the reference's consumer of them is "
-                            "a torch policy on the same device (env.py:75-79, ppo.py:66); see e2e_with_obs for the host-consumer case",
-                    "serve": {"value": e2e_serve_value, "unit": UNIT,
-                              "what": "bb_serve_step: persistent server kernel, doorbell in mapped pinned memory, no launch / stream wait per step"},
-                    "launch_per_step": {"value": e2e_launch_value, "unit": UNIT,
-                                        "what": "bb_step_host: one kernel launch + one stream wait per step"}},
-            "e2e_with_obs": {"value": e2e_obs_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h + n * 1024,
+                    "what": "per step: action rows read from pinned host memory over PCIe, fused step, reward + done written back "
+                            "to pinned host memory, the call returns when they are there; synchronous, one step in flight.  value = "
+                            "the fastest of the four host paths below (named in `path`); the *_u8 paths take the rows PACKED, u8 "
+                            "[N,2,6] (12 B/world, a declared extension of the C ABI: every field the policy emits is < 8), the "
+                            "others the reference's int32 rows (48 B/world; int32_rows.value).  The 1024 B/world observation rows "
+                            "STAY ON THE DEVICE: the reference's consumer of them is a torch policy on the same device "
+                            "(env.py:75-79, ppo.py:66); see e2e_with_obs for the host-consumer case",
+                    "int32_rows": {"value": e2e_i32_value, "unit": UNIT, "h2d_bytes_per_step": n * 48,
+                                   "serve": e2e_serve_value, "launch_per_step": e2e_launch_value,
+                                   "what": "the reference's Action dtype: bb_serve_step (persistent server kernel, doorbell in mapped pinned "
+                                           "memory, no launch / stream wait per step) and bb_step_host (one launch + one stream wait per step)"},
+                    "u8_rows": {"serve": e2e_serve8_value, "launch_per_step": e2e_launch8_value, "unit": UNIT, "h2d_bytes_per_step": n * 12,
+                                "what": "bb_serve_step_u8 / bb_step_host_u8"}},
+            "e2e_with_obs": {"value": e2e_obs_value, "unit": UNIT, "h2d_bytes_per_step": n * 48, "d2h_bytes_per_step": d2h + n * 1024,
                              "serve": e2e_obs_serve_value, "launch_per_step": e2e_obs_launch_value,
                              "what": "same, with both agents' observation rows mirrored to pinned host memory too (a policy on the host)"},
             "gpu_launches": int(gpu_launches),
@@ -452,6 +507,10 @@ def run_engine(args):
             "roofline": roofline,
             "roofline_hbm_bound": roofline_large,
             "cpu_baseline": cpu_baseline,
+            "step_latency_flushed": {"value": flushed_value, "unit": UNIT, "step_us": lat["step_us"], "null_floor_us": lat["null_floor_us"],
+                                     "what": "round 1's `value`: ONE isolated launch after a 256 MiB L2-flush memset, one event pair per step "
+                                             "(max over ranks of the mean); null_floor_us = a 1-element torch kernel timed the same way on "
+                                             "this box, i.e. the launch + event floor that number contains (informational)"},
             "l2_warm_graph": {"value": warm_value, "unit": UNIT,
                               "what": "same K steps replayed as one CUDA graph, no L2 flush (informational)"},
             "graph_step_n": {"value": step_n_value, "unit": UNIT,

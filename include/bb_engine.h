@@ -110,6 +110,13 @@ int bb_step_with_actions(bb_engine *e, const int32_t *actions_dev, void *cuda_st
 int bb_step_host(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host,
                  float *obs_host);
 
+/* bb_step_host / bb_serve_step with PACKED action rows: u8 [N,2,6], one byte per Action field (every field the
+ * policy can emit is < 8: scripts/env.py:96-102; `rotate = -1`, which only hardCodeDefenseSystem writes, has no packed
+ * form).  A declared extension for host-driven loops: the step reads a quarter of the bytes over PCIe (12 B instead of
+ * 48 B per world); the Action column still ends up as the int32 rows the reference exports.  Pinned buffers only. */
+int bb_step_host_u8(bb_engine *e, const uint8_t *actions_host, float *reward_host, float *done_host,
+                    float *obs_host);
+
 /* Persistent-server variant of bb_step_host for latency-bound host-driven loops (no reference
  * counterpart).  bb_serve_begin leaves one resident kernel on the device; each bb_serve_step rings
  * a doorbell in mapped pinned memory, the kernel runs one Manager::step() (action rows read from
@@ -124,6 +131,8 @@ int bb_step_host(bb_engine *e, const int32_t *actions_host, float *reward_host, 
 int bb_serve_begin(bb_engine *e);
 int bb_serve_step(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host,
                   float *obs_host);
+int bb_serve_step_u8(bb_engine *e, const uint8_t *actions_host, float *reward_host, float *done_host,
+                     float *obs_host);
 int bb_serve_end(bb_engine *e);
 /* Tuning aid: GPU-side nanoseconds between "doorbell seen" and "last block done" of the last served step. */
 long long bb_serve_last_gpu_ns(bb_engine *e);

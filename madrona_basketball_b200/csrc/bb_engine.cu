@@ -68,6 +68,7 @@ struct StepIo {
     float *doneOut;
     float *obsOut;            /* mirror of Observations, [N,2,128] (mapped pinned host) */
     int actionsVolatile;      /* persistent server: the host rewrites actionSrc between steps -> ld.cv */
+    int actionsU8;            /* actionSrc holds packed bytes, u8 [N,2,6] (bb_step_host_u8 / bb_serve_step_u8) */
 };
 
 struct StepParams {
@@ -222,7 +223,12 @@ BBD void load_lane(Lane &L, const StepParams &p, const StepIo &io, int64_t w, in
     L.idBase = (int32_t)(w * 5);
     L.me = me;
     L.didReset = false;
-    {
+    if (io.actionsU8) { /* six bytes per agent, 2-byte aligned */
+        const unsigned short *ap = reinterpret_cast<const unsigned short *>(reinterpret_cast<const uint8_t *>(io.actionSrc) + r * 6);
+        const unsigned h0 = ap[0], h1 = ap[1], h2 = ap[2];
+        A.move = (int32_t)(h0 & 0xffu); A.moveAngle = (int32_t)(h0 >> 8); A.rotate = (int32_t)(h1 & 0xffu);
+        A.grab = (int32_t)(h1 >> 8); A.pass = (int32_t)(h2 & 0xffu); A.shoot = (int32_t)(h2 >> 8);
+    } else {
         const int2 *ap = reinterpret_cast<const int2 *>((io.actionSrc ? io.actionSrc : C.action) + r * 6);
         int2 a0, a1, a2;
         if (io.actionsVolatile) { a0 = __ldcv(ap); a1 = __ldcv(ap + 1); a2 = __ldcv(ap + 2); }
@@ -314,9 +320,7 @@ BBD void store_lane(const Lane &L, const StepParams &p, const StepIo &io, int64_
         C.cooldown[r] = A.cooldown;
         *reinterpret_cast<float2 *>(C.stats + r * 2) = make_float2(A.points, A.fouls);
         C.curStep[r] = A.curStep;
-        C.reward[r] = A.reward;
         C.done[r] = A.done;
-        if (io.rewardOut) io.rewardOut[r] = A.reward;
         if (io.doneOut) io.doneOut[r] = A.done;
     }
     {
@@ -349,6 +353,15 @@ BBD void store_lane(const Lane &L, const StepParams &p, const StepIo &io, int64_
     }
 }
 
+/* Reward is final only after system 19; everything else is stored right after system 17 so that the stores drain
+ * while the observation values are computed */
+BBD void store_reward(const Lane &L, const StepParams &p, const StepIo &io, int64_t w)
+{
+    const int64_t r = w * 2 + L.me;
+    p.col.reward[r] = L.A.reward;
+    if (io.rewardOut) io.rewardOut[r] = L.A.reward;
+}
+
 /* thread-per-world store of a freshly generated world (init kernel only) */
 BBD void store_world(const World &W, const StepParams &p, int64_t w)
 {
@@ -359,6 +372,7 @@ BBD void store_world(const World &W, const StepParams &p, int64_t w)
         L.A = W.a[i];
         L.me = i;
         store_lane(L, p, p.io, w);
+        store_reward(L, p, p.io, w);
         const Columns &C = p.col;
         const int64_t r = w * 2 + i;
         C.reset[r] = W.a[i].reset;
@@ -433,9 +447,10 @@ BBD void step_tile(const StepParams &p, const StepIo &io, float4 *warpImg, int64
     __syncwarp();
     const Vec3 opos = xorv(L.A.pos);
     const int32_t oInb = xori(L.A.imInb);
+    if (valid) store_lane(L, p, io, w);                      /* state after systems 1-17 (18 and 19 write only obs / reward) */
     const ObsDerived d = obs_derive(L, opos, p.sc);
     pair_reward(L, d.dist);                                  /* system 19 (reads nothing system 18 writes) */
-    if (valid) store_lane(L, p, io, w);
+    if (valid) store_reward(L, p, io, w);
     if (warpWorld0 >= p.numWorlds) return;
     const int64_t remain = p.numWorlds - warpWorld0;
     const int nValid = remain >= kWorldsPerWarp ? kWorldsPerWarp : (int)remain;
@@ -462,7 +477,7 @@ BBD void step_tile(const StepParams &p, const StepIo &io, float4 *warpImg, int64
 /* One Manager::step(): thread t = (world t/2, agent t%2).  blockDim.x is any multiple of 32 up to kMaxT; dynamic shared
  * memory = smem_bytes_for(blockDim.x, kWPR).  kSync: see phase_sync; kWPR: worlds per observation round (16 or 8). */
 template <int kMaxT, bool kSync, int kWPR>
-__global__ void __launch_bounds__(kMaxT, BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_kernel(const __grid_constant__ StepParams p)
+__global__ void __launch_bounds__(kMaxT, kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_kernel(const __grid_constant__ StepParams p)
 {
     extern __shared__ float4 smem4[];
     /* programmatic dependent launch (bb_rollout): let the next kernel of the chain be scheduled early, and wait here for
@@ -501,7 +516,8 @@ struct ServeHostCtl { /* mapped pinned host memory */
     unsigned long long tSeen, tDone; /* %globaltimer when block 0 saw the doorbell / the last block finished (tuning) */
 };
 constexpr unsigned long long kServeExitWord = ~0ull;
-constexpr unsigned long long kServePtrMask = (1ull << 48) - 1;
+constexpr unsigned long long kServePtrMask = (1ull << 47) - 1;
+constexpr unsigned long long kServeU8Bit = 1ull << 47; /* word[0]: the action rows are packed bytes */
 struct ServeDevCtl { /* device memory */
     int32_t seq;
     unsigned int doneCount;
@@ -550,6 +566,7 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
                     dc->io.actionSrc = (const int32_t *)(w0 & kServePtrMask); dc->io.rewardOut = (float *)(w1 & kServePtrMask);
                     dc->io.doneOut = (float *)(w2 & kServePtrMask); dc->io.obsOut = (float *)(w3 & kServePtrMask);
                     dc->io.actionsVolatile = 0;
+                    dc->io.actionsU8 = (w0 & kServeU8Bit) ? 1 : 0;
                 }
                 st_release_gpu(&dc->seq, got);
             } else {
@@ -563,7 +580,7 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
             if (got != kServeExit) {
                 const volatile StepIo *src = &dc->io;
                 sIo.actionSrc = src->actionSrc; sIo.rewardOut = src->rewardOut; sIo.doneOut = src->doneOut;
-                sIo.obsOut = src->obsOut; sIo.actionsVolatile = 0;
+                sIo.obsOut = src->obsOut; sIo.actionsVolatile = 0; sIo.actionsU8 = src->actionsU8;
             }
         }
         __syncthreads();
@@ -690,7 +707,7 @@ struct bb_engine {
     void *colPtr[26];
     bb::StepParams params;
     cudaStream_t hostStream; /* bb_step_host / setters */
-    int blockThreads, phaseSync, prefetchBlocks, obsRound;
+    int blockThreads, phaseSync, prefetchBlocks, obsRound, pdlDefault;
     int64_t launches;
     /* bb_step_n: graph of stepGraphN step kernels */
     cudaGraphExec_t stepGraphExec;
@@ -820,10 +837,11 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), int blocks, int threads, size_t
 }
 
 int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, float *reward_out = nullptr,
-                float *done_out = nullptr, bool host_mapped = false, bool pdl = false)
+                float *done_out = nullptr, bool host_mapped = false, bool pdl = false, bool actions_u8 = false)
 {
     bb::StepParams p = e->params;
     p.io.actionSrc = actions_dev;
+    p.io.actionsU8 = actions_u8 ? 1 : 0;
     p.io.rewardOut = reward_out;
     p.io.doneOut = done_out;
     p.io.obsOut = nullptr;
@@ -839,7 +857,9 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
         if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_step_kernel<MAXT, SYNC, WPR>, blocks, threads, (size_t)smem, stream, true, p)); \
         else bb::bb_step_kernel<MAXT, SYNC, WPR><<<blocks, threads, smem, stream>>>(p);                          \
     } while (0)
-    if (threads <= 128) {
+    if (threads == 32 && wpr == 16) { /* the latency-bound shape: one-warp blocks, no register cap worth having */
+        BB_LAUNCH_STEP(32, false, 16);
+    } else if (threads <= 128) {
         if (e->phaseSync) { if (wpr == 8) BB_LAUNCH_STEP(128, true, 8); else BB_LAUNCH_STEP(128, true, 16); }
         else              { if (wpr == 8) BB_LAUNCH_STEP(128, false, 8); else BB_LAUNCH_STEP(128, false, 16); }
     } else {
@@ -936,6 +956,8 @@ bb_engine *bb_create(const bb_config *cfg)
     e->params.prefetchBlocks = 0;
 
     pick_launch_shape(e->N, &e->blockThreads, &e->phaseSync, &e->obsRound);
+    e->pdlDefault = 1;
+    if (const char *s = getenv("BB_PDL")) e->pdlDefault = atoi(s) != 0;
     if (!check_sqrt_thresholds()) {
         set_error("bb_create: the squared-length thresholds of bb_world.cuh do not match this host's sqrtf");
         cudaFree(e->slab);
@@ -992,7 +1014,23 @@ void bb_destroy(bb_engine *e)
     delete e;
 }
 
-int bb_step(bb_engine *e, void *cuda_stream) { return launch_step(e, nullptr, (cudaStream_t)cuda_stream); }
+/* Ordinary (uncaptured) step launches carry the programmatic-stream-serialization attribute: the kernel's blocks may be
+ * scheduled while the previous kernel of the stream drains, and wait at their first instruction (griddepcontrol.wait)
+ * until that kernel has completed and flushed -- whatever kernel it is -- so only launch latency overlaps, never data.
+ * Not inside a foreign stream capture (a captured first node has no predecessor to hang the edge on); BB_PDL=0 disables. */
+static bool pdl_for(bb_engine *e, cudaStream_t s)
+{
+    if (!e->pdlDefault) return false;
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &st) != cudaSuccess) { cudaGetLastError(); return false; }
+    return st == cudaStreamCaptureStatusNone;
+}
+
+int bb_step(bb_engine *e, void *cuda_stream)
+{
+    if (e->serving) { set_error("bb_step: the persistent server is running (bb_serve_end first)"); return -1; }
+    return launch_step(e, nullptr, (cudaStream_t)cuda_stream, nullptr, nullptr, false, pdl_for(e, (cudaStream_t)cuda_stream));
+}
 
 int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream)
 {
@@ -1024,7 +1062,8 @@ int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream)
 
 int bb_step_with_actions(bb_engine *e, const int32_t *actions_dev, void *cuda_stream)
 {
-    return launch_step(e, actions_dev, (cudaStream_t)cuda_stream);
+    if (e->serving) { set_error("bb_step_with_actions: the persistent server is running (bb_serve_end first)"); return -1; }
+    return launch_step(e, actions_dev, (cudaStream_t)cuda_stream, nullptr, nullptr, false, pdl_for(e, (cudaStream_t)cuda_stream));
 }
 
 /* Device alias of a pinned (page-locked, mapped) host buffer, or NULL for pageable memory.
@@ -1038,8 +1077,21 @@ static void *mapped_alias(const void *host)
     return nullptr;
 }
 
+static int step_host_impl(bb_engine *e, const void *actions_host, bool u8, float *reward_host, float *done_host, float *obs_host);
+
 int bb_step_host(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host, float *obs_host)
 {
+    return step_host_impl(e, actions_host, false, reward_host, done_host, obs_host);
+}
+
+int bb_step_host_u8(bb_engine *e, const uint8_t *actions_host, float *reward_host, float *done_host, float *obs_host)
+{
+    return step_host_impl(e, actions_host, true, reward_host, done_host, obs_host);
+}
+
+static int step_host_impl(bb_engine *e, const void *actions_host, bool u8, float *reward_host, float *done_host, float *obs_host)
+{
+    if (e->serving) { set_error("bb_step_host: the persistent server is running (bb_serve_end first)"); return -1; }
     cudaStream_t s = e->hostStream;
     const bb::Columns &C = e->params.col;
     /* Pinned buffers: the kernel itself moves the bytes over PCIe (reads the action rows from, and
@@ -1048,9 +1100,11 @@ int bb_step_host(bb_engine *e, const int32_t *actions_host, float *reward_host, 
     const int32_t *act_dev = (const int32_t *)mapped_alias(actions_host);
     float *rew_dev = (float *)mapped_alias(reward_host);
     float *done_dev = (float *)mapped_alias(done_host);
-    if (actions_host && !act_dev)
+    if (actions_host && !act_dev) {
+        if (u8) { set_error("bb_step_host_u8: the packed action rows must be pinned (page-locked, mapped) host memory"); return -1; }
         BB_CUDA_OK(cudaMemcpyAsync(C.action, actions_host, (size_t)e->N * 48, cudaMemcpyHostToDevice, s));
-    if (launch_step(e, act_dev, s, rew_dev, done_dev, act_dev != nullptr) != 0) return -1;
+    }
+    if (launch_step(e, act_dev, s, rew_dev, done_dev, act_dev != nullptr, false, u8 && act_dev != nullptr) != 0) return -1;
     if (reward_host && !rew_dev) BB_CUDA_OK(cudaMemcpyAsync(reward_host, C.reward, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
     if (done_host && !done_dev) BB_CUDA_OK(cudaMemcpyAsync(done_host, C.done, (size_t)e->N * 8, cudaMemcpyDeviceToHost, s));
     if (obs_host) BB_CUDA_OK(cudaMemcpyAsync(obs_host, C.obs, (size_t)e->N * 1024, cudaMemcpyDeviceToHost, s));
@@ -1107,7 +1161,19 @@ int bb_serve_begin(bb_engine *e)
     return serve_launch(e);
 }
 
+static int serve_step_impl(bb_engine *e, const void *actions_host, bool u8, float *reward_host, float *done_host, float *obs_host);
+
 int bb_serve_step(bb_engine *e, const int32_t *actions_host, float *reward_host, float *done_host, float *obs_host)
+{
+    return serve_step_impl(e, actions_host, false, reward_host, done_host, obs_host);
+}
+
+int bb_serve_step_u8(bb_engine *e, const uint8_t *actions_host, float *reward_host, float *done_host, float *obs_host)
+{
+    return serve_step_impl(e, actions_host, true, reward_host, done_host, obs_host);
+}
+
+static int serve_step_impl(bb_engine *e, const void *actions_host, bool u8, float *reward_host, float *done_host, float *obs_host)
 {
     if (!e->serving) { set_error("bb_serve_step: call bb_serve_begin first"); return -1; }
     bb::ServeHostCtl *hc = e->serveHost;
@@ -1136,8 +1202,9 @@ int bb_serve_step(bb_engine *e, const int32_t *actions_host, float *reward_host,
     const unsigned long long tag = (unsigned long long)((unsigned)seq & 0xffffu) << 48;
     const void *ptrs[4] = {act_dev, rew_dev, done_dev, obs_dev};
     for (int i = 0; i < 4; i++) {
-        if ((unsigned long long)(uintptr_t)ptrs[i] & ~bb::kServePtrMask) { set_error("bb_serve_step: buffer alias beyond 48 bits"); return -1; }
-        __atomic_store_n(&hc->word[i], tag | (unsigned long long)(uintptr_t)ptrs[i], __ATOMIC_RELEASE);
+        if ((unsigned long long)(uintptr_t)ptrs[i] & ~bb::kServePtrMask) { set_error("bb_serve_step: buffer alias beyond 47 bits"); return -1; }
+        const unsigned long long flag = (i == 0 && u8 && act_dev) ? bb::kServeU8Bit : 0ull;
+        __atomic_store_n(&hc->word[i], tag | flag | (unsigned long long)(uintptr_t)ptrs[i], __ATOMIC_RELEASE);
     }
     /* spin on the completion word the last block writes into this page */
     uint64_t spins = 0;

@@ -129,10 +129,27 @@ class SimpleGridworldSimulator:
         assert actions.is_cuda and actions.is_contiguous() and actions.numel() == self.num_worlds * 12
         self._check(self._lib.bb_step_with_actions(self._h, actions.data_ptr(), self._stream()), "bb_step_with_actions")
 
+    def bind_step_with_actions(self, actions):
+        """step_with_actions(actions) with the argument checks, pointer and stream look-ups done ONCE: returns a
+        zero-argument callable that enqueues the step on the stream that is current now.  For loops that launch faster
+        than a Python-level call with tensor indexing can (a step kernel lasts a few microseconds)."""
+        assert actions.is_cuda and actions.is_contiguous() and actions.numel() == self.num_worlds * 12
+        fn, h, ptr, st = self._lib.bb_step_with_actions, self._h, actions.data_ptr(), self._stream()
+        check = self._check
+
+        def call():
+            if fn(h, ptr, st) != 0:
+                check(-1, "bb_step_with_actions")
+        return call
+
     def step_host(self, actions: Optional[np.ndarray], reward: Optional[np.ndarray] = None,
                   done: Optional[np.ndarray] = None, obs: Optional[np.ndarray] = None) -> None:
         """Extension: host-buffer step (H2D actions, step, D2H results), synchronous."""
         n, ptr = self.num_worlds, self._host_ptr
+        if actions is not None and actions.dtype == np.uint8:   # packed rows (bb_step_host_u8)
+            self._check(self._lib.bb_step_host_u8(self._h, ptr(actions, np.uint8, n * 12), ptr(reward, np.float32, n * 2),
+                                                  ptr(done, np.float32, n * 2), ptr(obs, np.float32, n * 256)), "bb_step_host_u8")
+            return
         self._check(self._lib.bb_step_host(self._h, ptr(actions, np.int32, n * 12), ptr(reward, np.float32, n * 2),
                                            ptr(done, np.float32, n * 2), ptr(obs, np.float32, n * 256)), "bb_step_host")
 
@@ -157,8 +174,12 @@ class SimpleGridworldSimulator:
                    done: Optional[np.ndarray] = None, obs: Optional[np.ndarray] = None) -> None:
         """Extension: one host-buffer step through the persistent server (pinned buffers only)."""
         n = self.num_worlds
-        rc = self._lib.bb_serve_step(self._h, self._host_ptr(actions, np.int32, n * 12), self._host_ptr(reward, np.float32, n * 2),
-                                     self._host_ptr(done, np.float32, n * 2), self._host_ptr(obs, np.float32, n * 256))
+        if actions.dtype == np.uint8:   # packed rows (bb_serve_step_u8)
+            rc = self._lib.bb_serve_step_u8(self._h, self._host_ptr(actions, np.uint8, n * 12), self._host_ptr(reward, np.float32, n * 2),
+                                            self._host_ptr(done, np.float32, n * 2), self._host_ptr(obs, np.float32, n * 256))
+        else:
+            rc = self._lib.bb_serve_step(self._h, self._host_ptr(actions, np.int32, n * 12), self._host_ptr(reward, np.float32, n * 2),
+                                         self._host_ptr(done, np.float32, n * 2), self._host_ptr(obs, np.float32, n * 256))
         if rc != 0:
             self._check(rc, "bb_serve_step")
 

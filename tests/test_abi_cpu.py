@@ -155,3 +155,28 @@ def test_library_builds_from_clean_sources(tmp_path):
         assert "sm_100a" in elf and "sm_90" not in elf, elf
     # the shipped library is the one these sources produce (content hash written by the build)
     assert not build.needs_build(), "madrona_basketball_b200/libbball.so is stale w.r.t. the sources in the tree"
+
+
+def test_squared_length_thresholds_equal_the_sqrt_tests():
+    """bb_world.cuh replaces `length() <= c` / `>= c` by a test on the squared length (kLen2Le* / kLen2Ge*): for every float
+    around the threshold the two verdicts must agree (numpy's float32 sqrt is correctly rounded, like the device's
+    __fsqrt_rn and the oracle's sqrtf)."""
+    import re
+
+    import numpy as np
+
+    src = open(os.path.join(ROOT, "madrona_basketball_b200", "csrc", "bb_world.cuh")).read()
+    consts = {m.group(1): float.fromhex(m.group(2)) for m in re.finditer(r"constexpr float (kLen2\w+) = (0x[0-9a-fp.+-]+)f;", src)}
+    cases = [("kLen2LeHoopZone", np.float32(0.1), "le"), ("kLen2LeAgentSize", np.float32(0.2), "le"), ("kLen2GeArc", np.float32(7.24), "ge")]
+    assert set(consts) == {c[0] for c in cases}
+    for name, c, kind in cases:
+        T = np.float32(consts[name])
+        assert float(T) == consts[name]                      # the literal is a float32
+        bits = np.array([T]).view(np.uint32)[0]
+        s = np.arange(int(bits) - 100000, int(bits) + 100000, dtype=np.uint32).view(np.float32)
+        root = np.sqrt(s)
+        assert root.dtype == np.float32
+        if kind == "le":
+            assert np.array_equal(root <= c, s <= T), name
+        else:
+            assert np.array_equal(root >= c, s >= T), name

@@ -241,6 +241,39 @@ def test_persistent_server_steps_match_launch_per_step(n):
     assert_states_equal(engine_state(b), engine_state(a), f"after server N={n}")
 
 
+@pytest.mark.parametrize("n", [37, 8192])
+def test_packed_u8_action_rows_match_int32_rows(n):
+    """bb_step_host_u8 / bb_serve_step_u8 (declared extension): the same actions as bytes evolve the worlds exactly like the
+    int32 rows; the Action column ends up as the int32 rows the reference exports; ordinary steps refuse to run while the
+    server is resident."""
+    import torch
+
+    a, b, c = make_engine(n), make_engine(n), make_engine(n)
+    act = torch.empty((n, 2, 6), dtype=torch.int32, device="cuda")
+    hu8 = torch.empty((n, 2, 6), dtype=torch.uint8).pin_memory()
+    hrew = torch.empty((n, 2)).pin_memory(); hdone = torch.empty((n, 2)).pin_memory()
+    hrew2 = torch.empty((n, 2)).pin_memory(); hdone2 = torch.empty((n, 2)).pin_memory()
+    c.serve_begin()
+    with pytest.raises(RuntimeError, match="persistent server"):
+        c.step()
+    for s in range(40):
+        a.fill_actions(SEED, s, out=act); a.step_with_actions(act)
+        torch.cuda.current_stream().synchronize()
+        hu8.copy_(act.to(torch.uint8))
+        b.step_host(hu8.numpy(), hrew.numpy(), hdone.numpy())
+        c.serve_step(hu8.numpy(), hrew2.numpy(), hdone2.numpy())
+        ref = a.reward_tensor().to_torch().cpu().numpy().view(np.int32)
+        assert np.array_equal(hrew.numpy().view(np.int32), ref), s
+        assert np.array_equal(hrew2.numpy().view(np.int32), ref), s
+        assert np.array_equal(hdone.numpy(), a.done_tensor().to_torch().cpu().numpy()), s
+    c.serve_end()
+    torch.cuda.synchronize()
+    assert_states_equal(engine_state(b), engine_state(a), "step_host_u8")
+    assert_states_equal(engine_state(c), engine_state(a), "serve_step_u8")
+    with pytest.raises(RuntimeError, match="pinned"):
+        b.step_host(np.zeros((n, 2, 6), np.uint8))
+
+
 def test_persistent_server_idle_exit_and_restart(monkeypatch):
     import time
 
