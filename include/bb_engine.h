@@ -136,6 +136,10 @@ int bb_serve_step_u8(bb_engine *e, const uint8_t *actions_host, float *reward_ho
 int bb_serve_end(bb_engine *e);
 /* Tuning aid: GPU-side nanoseconds between "doorbell seen" and "last block done" of the last served step. */
 long long bb_serve_last_gpu_ns(bb_engine *e);
+/* Tuning aid: eight GPU-side time marks (ns, relative to "doorbell seen") of the last served step: after the acquire
+ * fence, after the release to the other blocks, block 0's tile start / end, the last block's tile end, its counter
+ * increment, and just before the completion word leaves. */
+int bb_serve_last_marks(bb_engine *e, long long out[8]);
 
 /* Manager::*Tensor() (mgr.cpp:317-445) / Impl::exportTensor (mgr.cpp:121-126):
  * device pointer + declared dtype/shape of a column.  The engine owns the memory

@@ -13,7 +13,7 @@ SYMBOLS = [
     "bb_create", "bb_destroy", "bb_step", "bb_step_n", "bb_step_with_actions", "bb_step_host", "bb_export",
     "bb_set_action", "bb_trigger_reset", "bb_fill_actions", "bb_checksum", "bb_launch_count",
     "bb_num_worlds", "bb_last_error", "bb_math_eval", "bb_serve_begin", "bb_serve_step", "bb_serve_end",
-    "bb_serve_last_gpu_ns", "bb_step_host_u8", "bb_serve_step_u8",
+    "bb_serve_last_gpu_ns", "bb_step_host_u8", "bb_serve_step_u8", "bb_serve_last_marks",
 ]
 
 
@@ -62,6 +62,8 @@ def load() -> ctypes.CDLL:
     lib.bb_serve_step.argtypes = [vp, vp, vp, vp, vp]
     lib.bb_serve_end.restype = ctypes.c_int
     lib.bb_serve_end.argtypes = [vp]
+    lib.bb_serve_last_marks.restype = ctypes.c_int
+    lib.bb_serve_last_marks.argtypes = [vp, ctypes.POINTER(ctypes.c_longlong)]
     for name in ("bb_step_host_u8", "bb_serve_step_u8"):
         getattr(lib, name).restype = ctypes.c_int
         getattr(lib, name).argtypes = [vp, vp, vp, vp, vp]

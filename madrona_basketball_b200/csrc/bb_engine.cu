@@ -67,7 +67,8 @@ struct StepIo {
     float *rewardOut;         /* mirrors of Reward / Done, [N,2] (mapped pinned host): host-buffer steps */
     float *doneOut;
     float *obsOut;            /* mirror of Observations, [N,2,128] (mapped pinned host) */
-    int actionsVolatile;      /* persistent server: the host rewrites actionSrc between steps -> ld.cv */
+    int actionsHost;          /* actionSrc is mapped pinned HOST memory: a warp fetches its tile's rows with 16-byte
+                               * uncached loads (few, wide PCIe reads) and hands them out through shared memory */
     int actionsU8;            /* actionSrc holds packed bytes, u8 [N,2,6] (bb_step_host_u8 / bb_serve_step_u8) */
 };
 
@@ -215,7 +216,8 @@ BBD void emit_obs_rows(const float4 *img, float *obs, int64_t world0, int count,
 
 /* Lane (w, me): its agent's rows + the world's ball / GameState / clock / RNG rows
  * (the pair reads the same world addresses: one broadcast transaction). */
-BBD void load_lane(Lane &L, const StepParams &p, const StepIo &io, int64_t w, int me)
+/* staged: the action rows of the warp's 16 worlds in shared memory (row = lane), or NULL: read them in place */
+BBD void load_lane(Lane &L, const StepParams &p, const StepIo &io, int64_t w, int me, const uint32_t *staged, int lane)
 {
     const Columns &C = p.col;
     const int64_t r = w * 2 + me; /* agent row */
@@ -224,15 +226,15 @@ BBD void load_lane(Lane &L, const StepParams &p, const StepIo &io, int64_t w, in
     L.me = me;
     L.didReset = false;
     if (io.actionsU8) { /* six bytes per agent, 2-byte aligned */
-        const unsigned short *ap = reinterpret_cast<const unsigned short *>(reinterpret_cast<const uint8_t *>(io.actionSrc) + r * 6);
+        const unsigned short *ap = staged ? reinterpret_cast<const unsigned short *>(staged) + lane * 3
+                                          : reinterpret_cast<const unsigned short *>(reinterpret_cast<const uint8_t *>(io.actionSrc) + r * 6);
         const unsigned h0 = ap[0], h1 = ap[1], h2 = ap[2];
         A.move = (int32_t)(h0 & 0xffu); A.moveAngle = (int32_t)(h0 >> 8); A.rotate = (int32_t)(h1 & 0xffu);
         A.grab = (int32_t)(h1 >> 8); A.pass = (int32_t)(h2 & 0xffu); A.shoot = (int32_t)(h2 >> 8);
     } else {
-        const int2 *ap = reinterpret_cast<const int2 *>((io.actionSrc ? io.actionSrc : C.action) + r * 6);
-        int2 a0, a1, a2;
-        if (io.actionsVolatile) { a0 = __ldcv(ap); a1 = __ldcv(ap + 1); a2 = __ldcv(ap + 2); }
-        else { a0 = ap[0]; a1 = ap[1]; a2 = ap[2]; }
+        const int2 *ap = staged ? reinterpret_cast<const int2 *>(staged) + lane * 3
+                                : reinterpret_cast<const int2 *>((io.actionSrc ? io.actionSrc : C.action) + r * 6);
+        const int2 a0 = ap[0], a1 = ap[1], a2 = ap[2];
         A.move = a0.x; A.moveAngle = a0.y; A.rotate = a1.x; A.grab = a1.y; A.pass = a2.x; A.shoot = a2.y;
     }
     A.reset = C.reset[r];
@@ -437,8 +439,20 @@ BBD void step_tile(const StepParams &p, const StepIo &io, float4 *warpImg, int64
     const bool valid = w < p.numWorlds;
     const int me = lane & 1;
     Lane L;
+    /* host-resident action rows (bb_step_host*, bb_serve_*): the tile's rows are one contiguous, 16-byte aligned segment
+     * (768 B of int32 rows, 192 B packed); 48 / 12 lanes fetch 16 bytes each past the caches and the pair reads its six
+     * fields from shared memory -- instead of three 2- or 8-byte loads per lane over PCIe */
+    const uint32_t *staged = nullptr;
+    if (io.actionsHost && warpWorld0 + kWorldsPerWarp <= p.numWorlds) {
+        const int bytesPerWorld = io.actionsU8 ? 12 : 48;
+        const uint4 *src = reinterpret_cast<const uint4 *>(reinterpret_cast<const uint8_t *>(io.actionSrc) + warpWorld0 * bytesPerWorld);
+        uint4 *dst = reinterpret_cast<uint4 *>(warpImg);
+        for (int i = lane; i < bytesPerWorld; i += 32) dst[i] = __ldcv(src + i); /* 16 worlds x bytesPerWorld / 16 B */
+        __syncwarp();
+        staged = reinterpret_cast<const uint32_t *>(warpImg);
+    }
     /* tail lanes shadow the last world so that every shuffle stays warp-wide; they never store */
-    load_lane(L, p, io, valid ? w : p.numWorlds - 1, me);
+    load_lane(L, p, io, valid ? w : p.numWorlds - 1, me, staged, lane);
     __syncwarp(); /* all of the pair's loads precede any of its stores */
     const bool tag = (p.sc.flags & BB_FLAG_TAG_MASK) != 0;
     const bool fast = __all_sync(kFullMask, tag && L.G.isOneOnOne == 1 && L.G.inbInProgress == 0);
@@ -514,12 +528,17 @@ struct ServeHostCtl { /* mapped pinned host memory */
     int32_t complete;        /* device -> host: last completed sequence number */
     int32_t alive;           /* device -> host: 1 while the server runs */
     unsigned long long tSeen, tDone; /* %globaltimer when block 0 saw the doorbell / the last block finished (tuning) */
+    /* tuning marks (%globaltimer, ns) of the last step: [0] doorbell seen by block 0, [1] after its acquire fence,
+     * [2] release to the other blocks done, [3] block 0 starts its tile, [4] block 0 done with its tile, [5] last block
+     * done with its tile, [6] last block past its counter increment, [7] just before the completion word is written */
+    unsigned long long mark[8];
 };
 constexpr unsigned long long kServeExitWord = ~0ull;
 constexpr unsigned long long kServePtrMask = (1ull << 47) - 1;
 constexpr unsigned long long kServeU8Bit = 1ull << 47; /* word[0]: the action rows are packed bytes */
 struct ServeDevCtl { /* device memory */
     int32_t seq;
+    int32_t stepDone;        /* last sequence number whose completion word has been sent */
     unsigned int doneCount;
     StepIo io;
 };
@@ -533,7 +552,7 @@ BBD uint64_t global_timer_ns() { uint64_t t; asm volatile("mov.u64 %0, %%globalt
 
 constexpr int kServeThreads = 32;
 __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_constant__ StepParams p, ServeHostCtl *hc, ServeDevCtl *dc,
-                                                                  int32_t startSeq, uint64_t idleTimeoutNs)
+                                                                  int32_t startSeq, uint64_t idleTimeoutNs, int flags)
 {
     extern __shared__ float4 smem4[];
     __shared__ int32_t sSeq;
@@ -544,6 +563,7 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
     const int64_t numTiles = (p.numWorlds + kWorldsPerWarp - 1) / kWorldsPerWarp;
     int32_t seq = startSeq;
     uint64_t tSeen = 0;
+    const bool marks = (flags & 4) != 0; /* BB_SERVE_FLAGS bit 2: write the tuning marks (a few extra posted writes per step) */
     for (;;) {
         const int32_t want = seq + 1;
         if (threadIdx.x == 0) {
@@ -553,6 +573,8 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
                 unsigned polls = 0;
                 const unsigned long long tag = (unsigned long long)((unsigned)want & 0xffffu);
                 unsigned long long w0, w1, w2, w3;
+                /* one sample (two 16-byte reads) in flight at a time: several outstanding reads of the same host line
+                 * serialise on PCIe and delay everything else on the link (measured: 4 in flight cost 5 us per step) */
                 for (;;) {
                     asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(&hc->word[0]) : "memory");
                     asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(&hc->word[2]) : "memory");
@@ -561,14 +583,17 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
                     if ((++polls & 31u) == 0 && global_timer_ns() - t0 > idleTimeoutNs) { got = kServeExit; break; }
                 }
                 tSeen = global_timer_ns();
+                if (marks) { hc->mark[0] = tSeen; hc->tSeen = tSeen; }
                 asm volatile("fence.acq_rel.sys;" ::: "memory"); /* acquire: the host's action rows precede its doorbell */
+                if (marks) hc->mark[1] = global_timer_ns();
                 if (got != kServeExit) {
                     dc->io.actionSrc = (const int32_t *)(w0 & kServePtrMask); dc->io.rewardOut = (float *)(w1 & kServePtrMask);
                     dc->io.doneOut = (float *)(w2 & kServePtrMask); dc->io.obsOut = (float *)(w3 & kServePtrMask);
-                    dc->io.actionsVolatile = 0;
                     dc->io.actionsU8 = (w0 & kServeU8Bit) ? 1 : 0;
+                    dc->io.actionsHost = ((w0 & kServePtrMask) != 0 && ((w0 & kServePtrMask) & 15ull) == 0) ? 1 : 0;
                 }
                 st_release_gpu(&dc->seq, got);
+                if (marks) hc->mark[2] = global_timer_ns();
             } else {
                 for (;;) {
                     got = ld_acquire_gpu(&dc->seq);
@@ -580,26 +605,32 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
             if (got != kServeExit) {
                 const volatile StepIo *src = &dc->io;
                 sIo.actionSrc = src->actionSrc; sIo.rewardOut = src->rewardOut; sIo.doneOut = src->doneOut;
-                sIo.obsOut = src->obsOut; sIo.actionsVolatile = 0; sIo.actionsU8 = src->actionsU8;
+                sIo.obsOut = src->obsOut; sIo.actionsHost = src->actionsHost; sIo.actionsU8 = src->actionsU8;
             }
         }
         __syncthreads();
         if (sSeq == kServeExit) break;
         const StepIo io = sIo;
+        if (marks && blockIdx.x == 0 && threadIdx.x == 0) hc->mark[3] = global_timer_ns();
         for (int64_t tile = (int64_t)blockIdx.x * warpsPerBlock + warp; tile < numTiles; tile += (int64_t)gridDim.x * warpsPerBlock)
             step_tile<false, kWorldsPerWarp>(p, io, warpImg, tile * kWorldsPerWarp, lane);
         __syncthreads();
         if (threadIdx.x == 0) {
+            const uint64_t tTile = marks ? global_timer_ns() : 0;
+            if (marks && blockIdx.x == 0) hc->mark[4] = tTile;
             __threadfence(); /* release (gpu scope): this block's writes before the count; the last block's
-                              * system-scope fence below is cumulative over everything it has observed */
+                              * system-scope release below is cumulative over everything it has observed */
             const unsigned old = atomicAdd(&dc->doneCount, 1u);
             if (old == gridDim.x - 1) { /* last block of this step */
                 dc->doneCount = 0;      /* nobody touches it again before the host rings the next doorbell */
-                if (blockIdx.x == 0) hc->tSeen = tSeen; /* tuning aid; only block 0 knows it */
-                hc->tDone = global_timer_ns();
-                __threadfence_system();
-                st_release_sys(&hc->complete, want);
+                if (marks) { hc->mark[5] = tTile; hc->mark[6] = global_timer_ns(); hc->tDone = hc->mark[6]; hc->mark[7] = hc->mark[6]; }
+                st_release_sys(&hc->complete, want); /* release at system scope: one fence, inside the store */
+                st_release_gpu(&dc->stepDone, want);
             }
+            /* block 0 goes back to polling the host only once the step is complete: doorbell reads that share the link
+             * with the last blocks' reward / done writes and the completion word delay them */
+            if (blockIdx.x == 0 && !(flags & 2))
+                while (ld_acquire_gpu(&dc->stepDone) != want) __nanosleep(100);
         }
         seq = want;
     }
@@ -845,7 +876,7 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
     p.io.rewardOut = reward_out;
     p.io.doneOut = done_out;
     p.io.obsOut = nullptr;
-    p.io.actionsVolatile = 0;
+    p.io.actionsHost = (host_mapped && actions_dev && ((uintptr_t)actions_dev & 15u) == 0) ? 1 : 0;
     p.prefetchBlocks = host_mapped ? 0 : e->prefetchBlocks; /* no L2 prefetch of host-mapped rows */
     const int threads = e->blockThreads;
     const int blocks = (int)((e->N * 2 + threads - 1) / threads);
@@ -1139,7 +1170,9 @@ static int serve_launch(bb_engine *e)
     p.prefetchBlocks = 0;
     bb::ServeHostCtl *hc_dev = nullptr;
     BB_CUDA_OK(cudaHostGetDevicePointer((void **)&hc_dev, e->serveHost, 0));
-    bb::bb_serve_kernel<<<grid, bb::kServeThreads, smem, e->serveStream>>>(p, hc_dev, e->serveDev, e->serveSeq, idle_ns);
+    int flags = 0;
+    if (const char *s = getenv("BB_SERVE_FLAGS")) flags = atoi(s);
+    bb::bb_serve_kernel<<<grid, bb::kServeThreads, smem, e->serveStream>>>(p, hc_dev, e->serveDev, e->serveSeq, idle_ns, flags);
     e->launches++;
     BB_CUDA_OK(cudaGetLastError());
     e->serving = true;
@@ -1224,6 +1257,13 @@ static int serve_step_impl(bb_engine *e, const void *actions_host, bool u8, floa
 
 /* tuning aid: GPU-side nanoseconds between "doorbell seen" and "last block done" of the last step */
 long long bb_serve_last_gpu_ns(bb_engine *e) { return e->serveHost ? (long long)(e->serveHost->tDone - e->serveHost->tSeen) : -1; }
+/* tuning aid: the eight %globaltimer marks of the last served step (see ServeHostCtl::mark), relative to mark 0 */
+int bb_serve_last_marks(bb_engine *e, long long out[8])
+{
+    if (!e->serveHost) return -1;
+    for (int i = 0; i < 8; i++) out[i] = (long long)(e->serveHost->mark[i] - e->serveHost->mark[0]);
+    return 0;
+}
 
 int bb_serve_end(bb_engine *e)
 {

@@ -183,6 +183,22 @@ class SimpleGridworldSimulator:
         if rc != 0:
             self._check(rc, "bb_serve_step")
 
+    def bind_serve_step(self, actions: np.ndarray, reward: Optional[np.ndarray] = None, done: Optional[np.ndarray] = None,
+                        obs: Optional[np.ndarray] = None):
+        """serve_step with its buffer checks and pointer look-ups done once: a zero-argument callable for loops where the
+        ~2 us of per-call Python argument handling matter (the served step itself takes ~18 us at 8192 worlds)."""
+        n = self.num_worlds
+        u8 = actions.dtype == np.uint8
+        fn = self._lib.bb_serve_step_u8 if u8 else self._lib.bb_serve_step
+        args = (self._h, self._host_ptr(actions, np.uint8 if u8 else np.int32, n * 12), self._host_ptr(reward, np.float32, n * 2),
+                self._host_ptr(done, np.float32, n * 2), self._host_ptr(obs, np.float32, n * 256))
+        check = self._check
+
+        def call():
+            if fn(*args) != 0:
+                check(-1, "bb_serve_step")
+        return call
+
     def serve_end(self) -> None:
         self._check(self._lib.bb_serve_end(self._h), "bb_serve_end")
 

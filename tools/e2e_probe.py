@@ -7,6 +7,7 @@ import torch
 from madrona_basketball_b200.shard import ShardedSimulator
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
+MARKS = (int(os.environ.get("BB_SERVE_FLAGS", "0")) & 4) != 0
 sh = ShardedSimulator(n, rank=0, world_size=1, gpu_id=0)
 sim = sh.sim
 lib, h = sim._lib, sim._h
@@ -26,6 +27,10 @@ def loop(name, fn, sync=True):
     print(f"{name:55s} {(time.perf_counter() - t) / R * 1e6:7.2f} us/step")
 
 def dev_async(): lib.bb_step_with_actions(h, dact.data_ptr(), stream)
+torch.cuda.synchronize(); t = time.perf_counter()
+for _ in range(400): dev_async()
+t1 = time.perf_counter(); torch.cuda.synchronize(); t2 = time.perf_counter()
+print(f"400 async launches: host enqueue {(t1 - t) / 400 * 1e6:.2f} us each, until drained {(t2 - t) / 400 * 1e6:.2f} us each")
 loop("device actions, async launches (no wait)", dev_async)
 def dev_sync():
     lib.bb_step_with_actions(h, dact.data_ptr(), stream); torch.cuda.current_stream().synchronize()
@@ -40,11 +45,29 @@ loop("bb_step_host pageable (staged copies)", lambda: lib.bb_step_host(h, ua, ur
 na, nr, nd = pact.numpy(), prew.numpy(), pdone.numpy()
 loop("sim.step_host(numpy pinned) python wrapper", lambda: sim.step_host(na, nr, nd))
 
+u8 = dact.to(torch.uint8).cpu().pin_memory(); p8 = u8.data_ptr()
+loop("bb_step_host_u8 pinned packed rows", lambda: lib.bb_step_host_u8(h, p8, pr, pd, None))
 lib.bb_serve_begin(h)
+loop("bb_serve_step_u8 pinned packed rows", lambda: lib.bb_serve_step_u8(h, p8, pr, pd, None), sync=False)
+loop("bb_serve_step_u8 packed rows only (no reward/done)", lambda: lib.bb_serve_step_u8(h, p8, None, None, None), sync=False)
+n8, = (u8.numpy(),)
+loop("sim.serve_step(numpy u8) python wrapper", lambda: sim.serve_step(n8, nr, nd), sync=False)
+def marks(name, fn):
+    m = (ctypes.c_longlong * 8)()
+    acc = np.zeros(8); wall = []
+    for _ in range(300):
+        t0 = time.perf_counter_ns(); fn(); wall.append(time.perf_counter_ns() - t0)
+        lib.bb_serve_last_marks(h, m); acc += np.array(list(m), dtype=np.float64)
+    acc /= 300
+    print(f"{name}: host call {np.mean(wall) / 1e3:.2f} us (median {np.median(wall) / 1e3:.2f}); GPU marks (us after doorbell seen): "
+          f"fence {acc[1] / 1e3:.2f}, released {acc[2] / 1e3:.2f}, blk0 tile start {acc[3] / 1e3:.2f} end {acc[4] / 1e3:.2f}, "
+          f"last blk tile end {acc[5] / 1e3:.2f}, counted {acc[6] / 1e3:.2f}, before flag {acc[7] / 1e3:.2f}")
+if MARKS: marks("serve u8 + reward/done", lambda: lib.bb_serve_step_u8(h, p8, pr, pd, None))
+if MARKS: marks("serve no io", lambda: lib.bb_serve_step_u8(h, None, None, None, None))
+# host-side enqueue cost of an asynchronous launch vs GPU time per launch
 loop("bb_serve_step pinned (persistent server)", lambda: lib.bb_serve_step(h, pa, pr, pd, None), sync=False)
 loop("bb_serve_step actions only", lambda: lib.bb_serve_step(h, pa, None, None, None), sync=False)
 loop("bb_serve_step nothing (doorbell + step + completion)", lambda: lib.bb_serve_step(h, None, None, None, None), sync=False)
-lib.bb_serve_last_gpu_ns.restype = ctypes.c_longlong; lib.bb_serve_last_gpu_ns.argtypes = [ctypes.c_void_p]
 acc = []
 for _ in range(200):
     lib.bb_serve_step(h, pa, pr, pd, None); acc.append(lib.bb_serve_last_gpu_ns(h))

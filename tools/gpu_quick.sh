@@ -19,3 +19,4 @@ if [ -n "$PREFETCH_TEST" ]; then
 for P in 0 592 1184 2368; do echo "prefetch blocks $P"; BB_PREFETCH_BLOCKS=$P timeout 120 python tools/bench_step.py --worlds 32768 65536 131072 --reps 200; done > $O/${TAG}_prefetch.log 2>&1
 cat $O/${TAG}_prefetch.log
 fi
+if [ -n "$E2E" ]; then timeout 300 python tools/e2e_probe.py > $O/${TAG}_e2e_probe.log 2>&1; cat $O/${TAG}_e2e_probe.log; fi
