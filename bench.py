@@ -207,6 +207,87 @@ def run_reference(args):
     return 0
 
 
+def rotating_rate(n, total_worlds, n_gpus, rank, local_rank, K, Wm, prewarm_s, seed_base=0):
+    """World-steps/s of K back-to-back launches over R independent n-world shards on this GPU (inputs larger than L2),
+    max over ranks.  The measurement `value` uses, as a function (strong-scaling points)."""
+    import torch
+    import torch.distributed as dist
+
+    from madrona_basketball_b200.shard import ShardedSimulator
+
+    dev = torch.device("cuda", local_rank)
+    l2_bytes = torch.cuda.get_device_properties(dev).L2_cache_size
+    R = max(2, -(-int(2.5 * l2_bytes) // (n * BYTES_PER_WORLD_STEP)))
+    shards = [ShardedSimulator(total_worlds * R, rank=rank * R + i, world_size=n_gpus * R, gpu_id=local_rank) for i in range(R)]
+    acts = torch.empty((min(K + Wm, 8), n, 2, 6), dtype=torch.int32, device=dev)
+    for s in range(acts.shape[0]):
+        shards[s % R].fill_actions(SEED, seed_base + s, out=acts[s])
+    calls = [[sh.sim.bind_step_with_actions(acts[b]) for b in range(acts.shape[0])] for sh in shards]
+    t0, i = time.perf_counter(), 0
+    while i < 2 * R or time.perf_counter() - t0 < prewarm_s:
+        calls[i % R][i % acts.shape[0]]()
+        i += 1
+        if i % 64 == 0:
+            torch.cuda.synchronize()
+    for s in range(Wm):
+        calls[(i + s) % R][s % acts.shape[0]]()
+    first = (i + Wm) % R
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if n_gpus > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for s in range(K):
+        calls[(first + s) % R][s % acts.shape[0]]()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if n_gpus > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    del calls, shards
+    return {"value": total_worlds * K / (ms * 1e-3), "unit": UNIT, "worlds_per_gpu": n, "us_per_step": ms / K * 1e3, "shards_per_gpu": R,
+            "hbm_frac": n * BYTES_PER_WORLD_STEP / (ms / K * 1e-3) / 1e9 / measured_peak_gbs()[0]}
+
+
+def stress_rate(total_worlds, n_gpus, rank, local_rank, steps=100, warm=20):
+    """BASELINE.json configs[4]: reset / collision stress: every step agent 1 is teleported next to agent 0
+    through the writable exported agent_pos view, so agentCollisionSystem fires each step and the world resets every
+    second step.  Per-step events (the teleport write and the action fill are outside them), max over ranks of the sum."""
+    import torch
+    import torch.distributed as dist
+
+    from madrona_basketball_b200.shard import ShardedSimulator
+
+    dev = torch.device("cuda", local_rank)
+    sh = ShardedSimulator(total_worlds, rank=rank, world_size=n_gpus, gpu_id=local_rank)
+    sim, n = sh.sim, sh.num_worlds
+    acts = torch.empty((4, n, 2, 6), dtype=torch.int32, device=dev)
+    pos = sim.agent_pos_tensor().to_torch()
+    off = pos.new_tensor([0.05, 0.0, 0.0])
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for s in range(warm + steps):
+        sh.fill_actions(SEED, s, out=acts[s % 4])
+        pos[:, 1] = pos[:, 0] + off
+        if s >= warm:
+            ev[s - warm][0].record()
+        sim.step_with_actions(acts[s % 4])
+        if s >= warm:
+            ev[s - warm][1].record()
+    torch.cuda.synchronize()
+    t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev)], dtype=torch.float64, device=dev)
+    if n_gpus > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    draws = int(sim.tensor("rng_count").to_torch().min().item())
+    del sim, sh
+    return {"value": total_worlds * steps / (ms * 1e-3), "unit": UNIT, "worlds": total_worlds, "worlds_per_gpu": n,
+            "us_per_step": ms / steps * 1e3, "hbm_frac": n * BYTES_PER_WORLD_STEP / (ms / steps * 1e-3) / 1e9 / measured_peak_gbs()[0],
+            "min_rng_draws_per_world": draws,
+            "what": "configs[4]: agent 1 teleported onto agent 0 before every step (collision each step, reset every second step); "
+                    "working set > L2 at this size, per-step CUDA events"}
+
+
 def run_engine(args):
     import numpy as np
     import torch
@@ -476,6 +557,38 @@ def run_engine(args):
                         "sample": f"{args.worlds_per_gpu} worlds x {cpu_steps} steps in one call, {cdt:.1f} s of CPU work on {threads} threads; "
                                   f"{cnote} (the reference's Madrona CPU executor cannot be built: submodule absent)"}
 
+    # ---------------------------------------------------------------- informational keys for the other BASELINE.json configs
+    extras = {}
+    if not args.no_extras:
+        if n_gpus > 1 and 65536 % n_gpus == 0:
+            # configs[2] as STRONG scaling: 65 536 worlds / N per GPU (the weak headline above matches it only at N = 8)
+            extras["strong_65536"] = rotating_rate(65536 // n_gpus, 65536, n_gpus, rank, local_rank, K, Wm, 0.2, seed_base=1000)
+            extras["strong_65536"]["what"] = "BASELINE configs[2]: 65 536 worlds sharded over the N GPUs, same measurement as `value`"
+        if n_gpus == 8:
+            extras["stress_2p20"] = stress_rate(1 << 20, n_gpus, rank, local_rank)
+        # configs[3]: data-parallel PPO (scripts/ppo.py:226-376 one process per GPU), gradient all-reduce with NCCL (default) and
+        # fused into the Adam kernel over NVLink peer memory; the parity of the two exchange paths is checked in-process
+        from madrona_basketball_b200 import ppo_train
+
+        ppo = {}
+        r_nccl = ppo_train.run_iterations(iters=args.ppo_iters, warmup=3, allreduce="nccl")
+        ppo["env_steps_per_s_nccl"] = r_nccl["env_steps_per_s"]
+        ppo["ms_per_iter_rank0"] = r_nccl["ms_per_iter_rank0"]
+        ppo["replica_param_spread_nccl"] = r_nccl["replica_param_spread"]
+        if n_gpus > 1:
+            try:
+                ppo.update(ppo_train.check_p2p_against_nccl(64))
+                r_p2p = ppo_train.run_iterations(iters=args.ppo_iters, warmup=3, allreduce="p2p")
+                ppo["env_steps_per_s_p2p"] = r_p2p["env_steps_per_s"]
+                ppo["replica_param_spread_p2p"] = r_p2p["replica_param_spread"]
+                if "note" in r_p2p:
+                    ppo["note"] = r_p2p["note"]
+            except RuntimeError as e:   # CUDA IPC unavailable on this box: the NCCL path is the product default
+                ppo["p2p_unavailable"] = str(e)[:200]
+        ppo["what"] = (f"{args.ppo_iters} PPO iterations of 8192 envs x 32 steps per GPU (rollout + GAE + 4 epochs x 4 minibatches, ppo.py "
+                       "defaults) through bb_rollout / bb_gae / bb_ppo_grad / bb_ppo_adam; whole-job env-steps/s, wall clock, max over ranks")
+        extras["ppo"] = ppo
+
     clocks = sampler.report()
     if rank == 0:
         line = {
@@ -522,6 +635,7 @@ def run_engine(args):
                                      "kernels, device-resident actions (scripts/run.py loop), no L2 flush (informational)"},
             "wall_s_timed_region": wall,
         }
+        line.update(extras)
         emit(line)
     if world_size > 1:
         dist.destroy_process_group()
@@ -556,6 +670,8 @@ def main():
     ap.add_argument("--worlds-per-gpu", type=int, default=WORLDS_PER_GPU)
     ap.add_argument("--no-serve", action="store_true", help="e2e through bb_step_host only (use under ncu)")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="CPU work of the cpu_baseline sample")
+    ap.add_argument("--no-extras", action="store_true", help="skip strong_65536 / stress_2p20 / ppo (profiler runs)")
+    ap.add_argument("--ppo-iters", type=int, default=20)
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -776,6 +776,9 @@ __global__ void __launch_bounds__(kAdamThreads) bb_ppo_adam_p2p_kernel(const P2p
     __shared__ int sBad;
     if (threadIdx.x == 0) sBad = 0;
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    /* sticky: once a call has given up on a peer this rank neither pushes nor applies again, so its peers run into
+     * their own timeout on the next call and every rank raises -- no replica keeps training on diverged parameters */
+    if (errFlag && *errFlag != 0) return;
     const int64_t parOff = (int64_t)(seq & 1u) * ws * stride;
     /* 1. push this rank's gradient into its slot at every peer */
     float own[kP2pPer];

@@ -313,6 +313,7 @@ class FusedPPO:
             self._p2p_error_host.copy_(self.p2p_error, non_blocking=True)
             self._p2p_error_event = torch.cuda.Event()
             self._p2p_error_event.record(torch.cuda.current_stream(self.device))
+            self.check_p2p()     # before anything (the next rollout) consumes the weights: a timed-out step raises HERE
         m = float(self._last_rows)   # rows of the last minibatch (the remainder one when total % num_minibatches != 0)
         return {"pg_loss": self.stats[0] / m, "v_loss": self.stats[1] / m * self.vf_coef,
                 "ent_loss": -self.stats[2] / m * self.ent_coef, "clip_frac": self.stats[3] / m, "grad_norm": self.grad_norm[0]}

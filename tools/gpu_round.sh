@@ -11,7 +11,7 @@ timeout 600 python bench.py --impl reference --steps 20 --warmup 5 > $O/${TAG}_b
 timeout 600 python bench.py --steps 20 --warmup 5 > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?" >> $O/${TAG}_bench.err
 timeout 300 python tools/probe_floor.py > $O/${TAG}_floor.json 2> $O/${TAG}_floor.err
 if [ -z "$NO_NCU" ]; then
-timeout 300 python bench.py --steps 5 --warmup 3 --cpu-seconds 0.2 --no-serve > $O/${TAG}_plain_bench.log 2>&1 && timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/${TAG}_launches_bench.csv python bench.py --steps 5 --warmup 3 --cpu-seconds 0.2 --no-serve > $O/${TAG}_ncu_bench.log 2>&1
+timeout 300 python bench.py --steps 5 --warmup 3 --cpu-seconds 0.2 --no-serve --no-extras > $O/${TAG}_plain_bench.log 2>&1 && timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/${TAG}_launches_bench.csv python bench.py --steps 5 --warmup 3 --cpu-seconds 0.2 --no-serve --no-extras > $O/${TAG}_ncu_bench.log 2>&1
 for W in 8192 65536 1048576; do
 timeout 120 python tools/profile_step.py --worlds $W --steps 72 > $O/${TAG}_plain_prof_$W.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:bb_step_kernel -s 68 -c 1 -f -o $O/${TAG}_prof_step_$W python tools/profile_step.py --worlds $W --steps 72 > $O/${TAG}_ncu_prof_$W.log 2>&1
 done
