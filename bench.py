@@ -33,6 +33,7 @@ BYTES_PER_WORLD_STEP = 1872  # 56 in + 348 state read + 
 SEED = 1234
 LARGE_WORLDS = 1 << 20       # HBM-bound regime (working set 1.9 GB >> 126 MB L2)
 PREWARM_S = 0.5              # declared device pre-warm before the timed window (config.prewarm)
+SPACER_MEMSETS = 6           # 256 MiB memsets (~45 us each) queued ahead of the timed window while the host enqueues its K launches
 
 
 def measured_peak_gbs():
@@ -236,6 +237,9 @@ def rotating_rate(n, total_worlds, n_gpus, rank, local_rank, K, Wm, prewarm_s, s
     if n_gpus > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    spacer = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for _ in range(SPACER_MEMSETS):   # see run_engine: the K launches are queued behind these before the window opens
+        spacer.zero_()
     e0.record()
     for s in range(K):
         calls[(first + s) % R][s % acts.shape[0]]()
@@ -363,6 +367,11 @@ def run_engine(args):
     barrier()
     with sampler:
         wall0 = time.perf_counter()
+        # The K launches are enqueued while the GPU is still busy with SPACER L2-flush memsets issued just before the first
+        # event, so the timed window holds K step kernels the stream already has in its queue: device time, not the host's
+        # enqueue pace or its scheduling jitter (5 us per launch from Python, more than a third of a step).
+        for _ in range(SPACER_MEMSETS):
+            flush.zero_()
         e0.record()
         for call in timed:
             call()
@@ -598,7 +607,8 @@ def run_engine(args):
             "config": {"workload": workload_string(args.worlds_per_gpu, n_gpus),
                        "l2": f"inputs larger than L2: every launch advances the next of {R} independent {n}-world shards on this GPU "
                              f"({R * n * BYTES_PER_WORLD_STEP / 1e6:.0f} MB of rows per cycle against a {l2_bytes / 1e6:.0f} MB L2), so each of the K timed "
-                             "launches reads its rows from HBM; K launches back to back between one pair of CUDA events",
+                             "launches reads its rows from HBM; K launches back to back between one pair of CUDA events, enqueued "
+                             f"behind {SPACER_MEMSETS} x 256 MiB memsets (which also flush L2) so that the window is device time, not host enqueue pace",
                        "prewarm": f"{n_pw} untimed launches of the same cycle ({PREWARM_S} s) before the W warm-up steps, so that the timed "
                                   "window does not sit on the clock / launch-path ramp of an idle GPU",
                        "parallelism": f"world-sharded x{n_gpus}, no collective in the step"},
