@@ -287,6 +287,9 @@ BBD void load_lane(Lane &L, const StepParams &p, const StepIo &io, int64_t w, in
     }
     L.resetNow = C.worldClock[w];
     L.rng = C.rngCount[w];
+    L.dirty = 0;
+    L.cooldownOld = A.cooldown; L.curShotOld = A.curShot; L.pointsWorthOld = A.pointsWorth;
+    L.resetNowOld = L.resetNow; L.rngOld = L.rng;
     /* mask / reward / done are fully rewritten by tick and actionMask */
 }
 
@@ -308,50 +311,59 @@ BBD void store_lane(const Lane &L, const StepParams &p, const StepIo &io, int64_
         tp[1] = __float_as_int(me ? 255.f : 0.f); tp[2] = __float_as_int(me ? 0.f : 100.f); tp[3] = __float_as_int(me ? 100.f : 255.f);
         tp[4] = L.idBase + me;
     }
+    const uint32_t dirty = L.dirty;
+    auto bits = [](float x) { return __float_as_int(x); };
     {
         float *pp = C.agentPos + r * 3;
         pp[0] = A.pos.x; pp[1] = A.pos.y; pp[2] = A.pos.z;
         float *vp = C.agentVel + r * 3;
         vp[0] = A.vel.x; vp[1] = A.vel.y; vp[2] = A.vel.z;
-        *reinterpret_cast<float4 *>(C.orientation + r * 4) = make_float4(A.q.w, A.q.x, A.q.y, A.q.z);
+        if (dirty & kDirtyQ) *reinterpret_cast<float4 *>(C.orientation + r * 4) = make_float4(A.q.w, A.q.x, A.q.y, A.q.z);
     }
     {
-        int32_t *ip = C.possession + r * 3;
-        ip[0] = A.hasBall; ip[1] = A.ballId; ip[2] = A.pointsWorth;
-        *reinterpret_cast<int2 *>(C.inbounding + r * 2) = make_int2(A.imInb, A.allowedToMove);
-        C.cooldown[r] = A.cooldown;
-        *reinterpret_cast<float2 *>(C.stats + r * 2) = make_float2(A.points, A.fouls);
+        if ((dirty & kDirtyPoss) || A.pointsWorth != L.pointsWorthOld) {
+            int32_t *ip = C.possession + r * 3;
+            ip[0] = A.hasBall; ip[1] = A.ballId; ip[2] = A.pointsWorth;
+        }
+        if (dirty & kDirtyInb) *reinterpret_cast<int2 *>(C.inbounding + r * 2) = make_int2(A.imInb, A.allowedToMove);
+        if (bits(A.cooldown) != bits(L.cooldownOld)) C.cooldown[r] = A.cooldown;
+        if (dirty & kDirtyStats) *reinterpret_cast<float2 *>(C.stats + r * 2) = make_float2(A.points, A.fouls);
         C.curStep[r] = A.curStep;
         C.done[r] = A.done;
         if (io.doneOut) io.doneOut[r] = A.done;
     }
     {
         float *tp = C.attributes + r * 9;
-        tp[0] = A.maxSpeed; tp[1] = A.quickness; tp[2] = A.shooting; tp[3] = A.ftPct; tp[4] = A.reaction;
-        tp[5] = A.target.x; tp[6] = A.target.y; tp[7] = A.target.z; tp[8] = A.curShot;
+        if (dirty & kDirtyAttr) { tp[0] = A.maxSpeed; tp[1] = A.quickness; tp[2] = A.shooting; tp[3] = A.ftPct; tp[4] = A.reaction; }
+        if (dirty & kDirtyTarget) { tp[5] = A.target.x; tp[6] = A.target.y; tp[7] = A.target.z; }
+        if (bits(A.curShot) != bits(L.curShotOld)) tp[8] = A.curShot;
     }
     if (me == 0) { /* replicated world state: lane 0 writes the ball, lane 1 the singletons */
         const BallS &B = L.B;
         float *bp = C.ballPos + w * 3;
         bp[0] = B.pos.x; bp[1] = B.pos.y; bp[2] = B.pos.z;
-        float *bv = C.ballVel + w * 3;
-        bv[0] = B.vel.x; bv[1] = B.vel.y; bv[2] = B.vel.z;
-        int32_t *ph = C.ballPhysics + w * 7;
-        ph[0] = B.inFlight; ph[1] = B.ltAgent; ph[2] = B.ltTeam; ph[3] = B.sbAgent;
-        ph[4] = B.sbTeam; ph[5] = B.spv; ph[6] = B.goingIn;
-        *reinterpret_cast<int2 *>(C.grabbed + w * 2) = make_int2(B.isGrabbed, B.holder);
+        if (dirty & kDirtyBall) {
+            float *bv = C.ballVel + w * 3;
+            bv[0] = B.vel.x; bv[1] = B.vel.y; bv[2] = B.vel.z;
+            int32_t *ph = C.ballPhysics + w * 7;
+            ph[0] = B.inFlight; ph[1] = B.ltAgent; ph[2] = B.ltTeam; ph[3] = B.sbAgent;
+            ph[4] = B.sbTeam; ph[5] = B.spv; ph[6] = B.goingIn;
+            *reinterpret_cast<int2 *>(C.grabbed + w * 2) = make_int2(B.isGrabbed, B.holder);
+        }
     } else {
         float2 *gp = reinterpret_cast<float2 *>(C.gameState + w * 14);
         const GameS &g = L.G;
-        gp[0] = make_float2(__int_as_float(g.inbInProgress), __int_as_float(g.liveBall));
-        gp[1] = make_float2(g.period, g.teamInPoss);
-        gp[2] = make_float2(__int_as_float(g.team0Hoop), g.team0Score);
-        gp[3] = make_float2(__int_as_float(g.team1Hoop), g.team1Score);
         gp[4] = make_float2(g.gameClock, g.shotClock);
-        gp[5] = make_float2(g.scoredBaskets, g.oobCount);
-        gp[6] = make_float2(g.inboundClock, __int_as_float(g.isOneOnOne));
-        C.worldClock[w] = L.resetNow;
-        C.rngCount[w] = L.rng;
+        if (dirty & kDirtyGame) {
+            gp[0] = make_float2(__int_as_float(g.inbInProgress), __int_as_float(g.liveBall));
+            gp[1] = make_float2(g.period, g.teamInPoss);
+            gp[2] = make_float2(__int_as_float(g.team0Hoop), g.team0Score);
+            gp[3] = make_float2(__int_as_float(g.team1Hoop), g.team1Score);
+            gp[5] = make_float2(g.scoredBaskets, g.oobCount);
+            gp[6] = make_float2(g.inboundClock, __int_as_float(g.isOneOnOne));
+        }
+        if (L.resetNow != L.resetNowOld) C.worldClock[w] = L.resetNow;
+        if (L.rng != L.rngOld) C.rngCount[w] = L.rng;
     }
 }
 
@@ -369,10 +381,13 @@ BBD void store_world(const World &W, const StepParams &p, int64_t w)
 {
     Lane L;
     L.B = W.b; L.G = W.g; L.resetNow = W.resetNow; L.rng = W.rng; L.idBase = W.idBase; L.didReset = false;
+    L.dirty = kDirtyAll; L.resetNowOld = ~W.resetNow; L.rngOld = ~W.rng; /* a fresh world: every row is written */
 #pragma unroll
     for (int i = 0; i < 2; i++) {
         L.A = W.a[i];
         L.me = i;
+        L.pointsWorthOld = ~W.a[i].pointsWorth;
+        L.cooldownOld = __int_as_float(~__float_as_int(W.a[i].cooldown)); L.curShotOld = __int_as_float(~__float_as_int(W.a[i].curShot));
         store_lane(L, p, p.io, w);
         store_reward(L, p, p.io, w);
         const Columns &C = p.col;
@@ -457,7 +472,7 @@ BBD void step_tile(const StepParams &p, const StepIo &io, float4 *warpImg, int64
     const bool tag = (p.sc.flags & BB_FLAG_TAG_MASK) != 0;
     const bool fast = __all_sync(kFullMask, tag && L.G.isOneOnOne == 1 && L.G.inbInProgress == 0);
     if (fast) pair_step_fast<kSync>(L, p.sc);                /* systems 1-17 */
-    else { Lane T = L; slow_step(&T, &p.sc, tag, kSync); L = T; finish_derived(L); } /* only the copy's address escapes */
+    else { Lane T = L; slow_step(&T, &p.sc, tag, kSync); L = T; finish_derived(L); L.dirty = kDirtyAll; } /* only the copy's address escapes */
     __syncwarp();
     const Vec3 opos = xorv(L.A.pos);
     const int32_t oInb = xori(L.A.imInb);

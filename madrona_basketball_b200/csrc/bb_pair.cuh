@@ -39,6 +39,24 @@ struct Lane {
     Vec3 facing;     /* q.rotateVec({0,1,0}) */
     float vel2, speed; /* length2 / length of the velocity */
     bool qDirty;     /* the orientation changed after `facing` was taken (shot, reset) */
+    /* Which state rows this step actually changed (store_lane skips the others: most rows are untouched on most steps,
+     * and an unchanged row costs neither a store slot nor HBM write-back).  A bit is set at every site that assigns the
+     * row; rows with a single cheap field are compared against the value loaded instead (the *Old copies). */
+    uint32_t dirty;
+    float cooldownOld, curShotOld;
+    int32_t pointsWorthOld, resetNowOld;
+    uint32_t rngOld;
+};
+enum : uint32_t {
+    kDirtyQ = 1u << 0,       /* Orientation */
+    kDirtyPoss = 1u << 1,    /* InPossession.hasBall / ballEntityID */
+    kDirtyInb = 1u << 2,     /* Inbounding */
+    kDirtyStats = 1u << 3,   /* Stats */
+    kDirtyTarget = 1u << 4,  /* Attributes.currentTargetPosition */
+    kDirtyBall = 1u << 5,    /* ball Velocity, BallPhysics, Grabbed */
+    kDirtyGame = 1u << 6,    /* GameState fields other than the two clocks */
+    kDirtyAttr = 1u << 7,    /* Attributes[0..4] (written by resetWorld only) */
+    kDirtyAll = 0xffu
 };
 
 BBD void finish_derived(Lane &L)
@@ -149,7 +167,7 @@ BBD void pair_shoot_turn(Lane &L, const SimConst &c, int k, Vec3 apos, Vec3 dpos
         going_in = closest_sq <= radius * radius;
     }
     Quat rot = rotation_between(v3(0.f, 1.f, 0.f), shot, c);
-    if (acting) { L.A.q = rot; L.qDirty = true; }
+    if (acting) { L.A.q = rot; L.qDirty = true; L.dirty |= kDirtyQ; }
     BallS &B = L.B;
     const int32_t aid = L.idBase + 3 + k;
     if (B.holder == aid) {
@@ -157,7 +175,8 @@ BBD void pair_shoot_turn(Lane &L, const SimConst &c, int k, Vec3 apos, Vec3 dpos
         if (going_in) { B.goingIn = 1; L.G.scoredBaskets += 1.f; }
         else if (acting) L.A.reward -= 1.f;
         B.isGrabbed = 0; B.holder = kPlaceholder;
-        if (acting) { L.A.hasBall = 0; L.A.ballId = kPlaceholder; L.A.imInb = 0; }
+        L.dirty |= kDirtyBall | kDirtyGame;
+        if (acting) { L.A.hasBall = 0; L.A.ballId = kPlaceholder; L.A.imInb = 0; L.dirty |= kDirtyPoss | kDirtyInb; }
         B.vel = shot * .1f;
         B.inFlight = 1;
         B.sbAgent = aid; B.sbTeam = k; B.spv = spv;
@@ -200,6 +219,7 @@ BBD void pair_reset_world(Lane &L, const SimConst &c)
     A.cooldown = 0.f; A.points = 0.f; A.fouls = 0.f;
     A.vel = v3(0.f, 0.f, 0.f);
     L.vel2 = 0.f; L.speed = 0.f; L.qDirty = true; /* sqrt(0) == 0 */
+    L.dirty = kDirtyAll;
     /* the three draws of helper.cpp:121,122,132, replicated */
     Vec3 base = v3(c.startX + (0.f * 2.f), c.startY, 0.f);
     float xd = pair_uniform(L, c, -kStartDev, kStartDev);
@@ -309,6 +329,7 @@ BBD void pair_defense(Lane &L, Vec3 opos, int32_t ohas, const SimConst &c)
     if (len2(hdv) > 1e-6f) guard = op + normalize(hdv) * kGuardDist;
     float f = D.reaction * kDt;
     D.target = D.target + (guard - D.target) * f;
+    L.dirty |= kDirtyTarget;
     Vec3 mv = D.target - D.pos;
     if (len2(mv) < 0.01f) { D.move = 0; return; }
     Vec3 dir = normalize(mv);
@@ -373,6 +394,7 @@ BBD void pair_step_fast(Lane &L, const SimConst &c)
     const int me = L.me;
     sys_tick(A);                       /* 1 */
     sys_action_mask<true>(A, g);       /* 2 */
+    if (A.rotate != 0) L.dirty |= kDirtyQ;
     sys_move_agent(A, c, L.facing);    /* 3 */
     L.qDirty = false;
     L.vel2 = len2(A.vel);
@@ -416,6 +438,7 @@ BBD void pair_step_fast(Lane &L, const SimConst &c)
             if (L.idBase + h == g.team0Hoop) g.team1Score += (float)points;
             else g.team0Score += (float)points;
             g.scoredBaskets += 1.f;
+            L.dirty |= kDirtyStats | kDirtyGame | kDirtyBall;
             B.inFlight = 0;
             B.vel = v3(0.f, 0.f, 0.f);
             B.sbAgent = kPlaceholder; B.sbTeam = kPlaceholder; B.spv = 2; B.goingIn = 0;
@@ -434,8 +457,10 @@ BBD void pair_step_fast(Lane &L, const SimConst &c)
         const int32_t touch = (len2(B.pos - A.pos) <= kLen2LeAgentSize) ? 1 : 0; /* length <= kAgentSize */
         const int32_t otouch = xori(touch);
         const int32_t t0 = me ? otouch : touch, t1 = me ? touch : otouch;
+        const int32_t ltA = B.ltAgent, ltT = B.ltTeam;
         if (t1) { B.ltAgent = L.idBase + 4; B.ltTeam = 1; }
         else if (t0) { B.ltAgent = L.idBase + 3; B.ltTeam = 0; }
+        if (B.ltAgent != ltA || B.ltTeam != ltT) L.dirty |= kDirtyBall;
     }
     {                                  /* 12 clock (game.cpp:992-1030) */
         bool live = (float)g.liveBall > 0.5f;
