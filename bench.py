@@ -521,8 +521,9 @@ def run_engine(args):
                 "traffic": ncu_traffic(f"bb_step_kernel@{n}"), "kernel": "bb_step_kernel", "worlds_per_launch": n,
                 "algorithmic_bytes_per_launch": n * BYTES_PER_WORLD_STEP, "peak_source": peak_src,
                 "traffic_note": "ncu --set full capture with ncu's default cache control (caches flushed before the launch, like the "
-                                "timed steps): DRAM reads = the state rows; the 11.7 MB of writes stay in the 126 MB L2 for the "
-                                "lifetime of the launch, so DRAM write bytes read 0",
+                                "timed launches): DRAM reads = the state + action rows; the 11.7 MB of stores stay in the L2 for the "
+                                "lifetime of the single profiled launch, so ncu's DRAM write bytes read 0 (in the timed cycle over the "
+                                "shards they are written back while later launches run)",
                 "note": "8192 worlds (15 MB) is latency/launch-bound by construction; see roofline_hbm_bound"}
 
     roofline_large = None
