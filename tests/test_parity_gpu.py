@@ -52,6 +52,21 @@ def test_ragged_world_counts(n):
     _run_lockstep(n, 40, check_every=13)
 
 
+@pytest.mark.parametrize("shape", [dict(BB_BLOCK_THREADS="128", BB_PHASE_SYNC="1", BB_OBS_ROUND="8"),
+                                   dict(BB_BLOCK_THREADS="128", BB_PHASE_SYNC="0", BB_OBS_ROUND="16"),
+                                   dict(BB_BLOCK_THREADS="64", BB_OBS_ROUND="8"),
+                                   dict(BB_BLOCK_THREADS="256", BB_PHASE_SYNC="1"),
+                                   dict(BB_PDL="0")])
+def test_every_launch_shape_is_bit_exact(monkeypatch, shape):
+    """The launch shapes the engine picks by world count (one-warp blocks / 64 threads / 128 threads with phase barriers and
+    two observation rounds / the 512-thread instantiation), forced here at a size the oracle checks every column of
+    (observations included): ragged count, dead-path flags off, 60 steps."""
+    for k, v in shape.items():
+        monkeypatch.setenv(k, v)
+    _run_lockstep(1000 + 37, 60, check_every=7)
+    _run_lockstep(333, 40, flags=0, check_every=5)
+
+
 def test_zero_actions_like_run_py():
     """scripts/run.py drives zero actions for agent 0 only; the hard-coded defender chases (a17)."""
     import torch
