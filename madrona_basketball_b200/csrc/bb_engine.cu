@@ -765,8 +765,9 @@ struct bb_engine {
     cudaStream_t serveStream;
     int32_t serveSeq;
     bool serving;
-    /* device aliases of the pinned buffers seen during this serve session (cudaPointerGetAttributes
-     * costs about a microsecond per pointer; the buffers must stay pinned while the server runs) */
+    /* device aliases of the pinned buffers seen during this serve session (cudaPointerGetAttributes costs about a
+     * microsecond per pointer, four pointers per 18 us step).  Contract (include/bb_engine.h): a buffer passed to
+     * bb_serve_step stays pinned until bb_serve_end; the cache is dropped by bb_serve_begin. */
     const void *aliasHost[64];
     void *aliasDev[64];
     int aliasCount;
@@ -1256,11 +1257,25 @@ static int serve_step_impl(bb_engine *e, const void *actions_host, bool u8, floa
     }
     /* spin on the completion word the last block writes into this page */
     uint64_t spins = 0;
+    int relaunches = 0;
     while (__atomic_load_n(&hc->complete, __ATOMIC_ACQUIRE) != seq) {
         __builtin_ia32_pause();
         if ((++spins & 0xfffff) == 0) { /* every ~1M spins: is the server still there? */
             if (!__atomic_load_n(&hc->alive, __ATOMIC_ACQUIRE) || cudaStreamQuery(e->serveStream) != cudaErrorNotReady) {
                 cudaError_t err = cudaStreamSynchronize(e->serveStream);
+                if (err == cudaSuccess && __atomic_load_n(&hc->complete, __ATOMIC_ACQUIRE) != seq && relaunches++ == 0) {
+                    /* the server idled out between the alive check above and the doorbell (it saw no step for
+                     * BB_SERVE_IDLE_MS): start it again for THIS sequence number and ring once more */
+                    e->serveSeq = seq - 1;
+                    const int rc = serve_launch(e);
+                    e->serveSeq = seq;
+                    if (rc != 0) return -1;
+                    for (int i = 0; i < 4; i++) {
+                        const unsigned long long flag = (i == 0 && u8 && act_dev) ? bb::kServeU8Bit : 0ull;
+                        __atomic_store_n(&hc->word[i], tag | flag | (unsigned long long)(uintptr_t)ptrs[i], __ATOMIC_RELEASE);
+                    }
+                    continue;
+                }
                 e->serving = false;
                 set_error(std::string("bb_serve_step: server kernel stopped: ") + cudaGetErrorString(err));
                 return -1;
