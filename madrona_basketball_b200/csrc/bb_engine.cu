@@ -904,7 +904,10 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
         if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_step_kernel<MAXT, SYNC, WPR>, blocks, threads, (size_t)smem, stream, true, p)); \
         else bb::bb_step_kernel<MAXT, SYNC, WPR><<<blocks, threads, smem, stream>>>(p);                          \
     } while (0)
-    if (threads == 32 && wpr == 16) { /* the latency-bound shape: one-warp blocks, no register cap worth having */
+#ifndef BB_NO_T32
+#define BB_NO_T32 0
+#endif
+    if (!BB_NO_T32 && threads == 32 && wpr == 16) { /* the latency-bound shape: one-warp blocks, no register cap worth having */
         BB_LAUNCH_STEP(32, false, 16);
     } else if (threads <= 128) {
         if (e->phaseSync) { if (wpr == 8) BB_LAUNCH_STEP(128, true, 8); else BB_LAUNCH_STEP(128, true, 16); }

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """A/B of two builds of libbball.so on the SAME box (box-to-box spread is ~3 %, more than most kernel changes):
-    python tools/ab_step.py libA.so libB.so [worlds ...]
+    python tools/ab_step.py libA.so[:ENV=VAL,ENV2=VAL2] libB.so[:...] [worlds ...]
 For each library (alternating, 3 rounds): K = 200 queued launches over rotating cold shards (bench.py's `value`
 measurement) with random actions, and bb_step_n graph replay; prints microseconds per step."""
 import json, os, subprocess, sys
@@ -26,11 +26,13 @@ def main():
     libs = sys.argv[1:3]
     worlds = sys.argv[3:] or ["8192", "65536", "1048576"]
     for rnd in range(3):
-        for lib in libs:
+        for spec in libs:
+            lib, _, extra = spec.partition(":")
             env = dict(os.environ, BB_LIB_PATH=os.path.abspath(lib))
+            env.update(kv.split("=", 1) for kv in extra.split(",") if kv)
             res = subprocess.run([sys.executable, "-c", CHILD] + worlds, env=env, capture_output=True, text=True)
             line = res.stdout.strip().splitlines()[-1] if res.stdout.strip() else res.stderr[-400:]
-            print(os.path.basename(lib), line, flush=True)
+            print(os.path.basename(spec), line, flush=True)
 
 if __name__ == "__main__":
     main()
