@@ -260,6 +260,18 @@ BBD void pair_collision(Lane &L, Vec3 opos)
     const Vec3 c = L.A.pos;
     const Vec3 f = L.facing;
     const Vec3 r = v3(f.y, -f.x, 0.f);
+    /* Far apart: nothing to test.  A rectangle's corners lie within R = sqrt(hw^2 + hd^2) * |f| of its centre (hwv and hdv
+     * are orthogonal and |r| <= |f|; |f| != 1 is covered, the orientation is never renormalised), so the two rectangles
+     * cannot touch when the centres are further apart than R_a + R_b.  The warp skips the SAT only when EVERY pair is beyond
+     * sqrt(2) (R_a + R_b) (tested without a root: d^2 > 4 (R_a^2 + R_b^2) >= 2 (R_a + R_b)^2): then one of the four axes
+     * separates the projections by more than 0.1 (R_a + R_b), five orders of magnitude above float rounding, so the
+     * reference's SAT finds `collision = false` too and writes nothing (game.cpp:598-617).  NaNs compare false -> SAT. */
+    {
+        const float R2 = (hw * hw + hd * hd) * len2(f);
+        const float oR2 = xorf(R2);
+        const bool apart = len2(opos - c) > 4.f * (R2 + oR2);
+        if (__all_sync(kFullMask, apart)) return;
+    }
     const Vec3 hwv = r * hw, hdv = f * hd;
     const Vec3 mv[4] = {c - hdv + hwv, c - hdv - hwv, c + hdv - hwv, c + hdv + hwv};
     const Vec3 ov[4] = {xorv(mv[0]), xorv(mv[1]), xorv(mv[2]), xorv(mv[3])};
