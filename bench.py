@@ -33,7 +33,18 @@ BYTES_PER_WORLD_STEP = 1872  # 56 in + 348 state read + 
 SEED = 1234
 LARGE_WORLDS = 1 << 20       # HBM-bound regime (working set 1.9 GB >> 126 MB L2)
 PREWARM_S = 0.5              # declared device pre-warm before the timed window (config.prewarm)
-SPACER_MEMSETS = 6           # 256 MiB memsets (~45 us each) queued ahead of the timed window while the host enqueues its K launches
+SPACER_US = 300              # a spin kernel of this length is queued ahead of the timed window while the host enqueues its K launches
+
+
+def enqueue_spacer(torch, flush):
+    """Keeps the stream busy for ~SPACER_US without touching memory (torch.cuda._sleep: one thread spinning on the clock), so
+    that the K launches enqueued behind it are all queued when the window opens and the kernel's code stays cached as in any
+    steady-state loop; the rows are cold by the shard rotation, not by a flush.  Falls back to 256 MiB memsets."""
+    try:
+        torch.cuda._sleep(int(SPACER_US * 1e-6 * 1.9e9))
+    except Exception:
+        for _ in range(6):
+            flush.zero_()
 
 
 def measured_peak_gbs():
@@ -237,9 +248,7 @@ def rotating_rate(n, total_worlds, n_gpus, rank, local_rank, K, Wm, prewarm_s, s
     if n_gpus > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    spacer = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    for _ in range(SPACER_MEMSETS):   # see run_engine: the K launches are queued behind these before the window opens
-        spacer.zero_()
+    enqueue_spacer(torch, torch.empty(256 << 20, dtype=torch.uint8, device=dev))   # see run_engine: the K launches queue up behind it
     e0.record()
     for s in range(K):
         calls[(first + s) % R][s % acts.shape[0]]()
@@ -367,11 +376,10 @@ def run_engine(args):
     barrier()
     with sampler:
         wall0 = time.perf_counter()
-        # The K launches are enqueued while the GPU is still busy with SPACER L2-flush memsets issued just before the first
-        # event, so the timed window holds K step kernels the stream already has in its queue: device time, not the host's
-        # enqueue pace or its scheduling jitter (5 us per launch from Python, more than a third of a step).
-        for _ in range(SPACER_MEMSETS):
-            flush.zero_()
+        # The K launches are enqueued while the GPU is still busy with a spacer (a ~300 us spin kernel) issued just before
+        # the first event, so the timed window holds K step kernels the stream already has in its queue: device time, not
+        # the host's enqueue pace or its scheduling jitter (5 us per launch from Python, half a step).
+        enqueue_spacer(torch, flush)
         e0.record()
         for call in timed:
             call()
@@ -609,7 +617,7 @@ def run_engine(args):
                        "l2": f"inputs larger than L2: every launch advances the next of {R} independent {n}-world shards on this GPU "
                              f"({R * n * BYTES_PER_WORLD_STEP / 1e6:.0f} MB of rows per cycle against a {l2_bytes / 1e6:.0f} MB L2), so each of the K timed "
                              "launches reads its rows from HBM; K launches back to back between one pair of CUDA events, enqueued "
-                             f"behind {SPACER_MEMSETS} x 256 MiB memsets (which also flush L2) so that the window is device time, not host enqueue pace",
+                             f"behind a {SPACER_US} us spin kernel so that the window is device time, not host enqueue pace",
                        "prewarm": f"{n_pw} untimed launches of the same cycle ({PREWARM_S} s) before the W warm-up steps, so that the timed "
                                   "window does not sit on the clock / launch-path ramp of an idle GPU",
                        "parallelism": f"world-sharded x{n_gpus}, no collective in the step"},
