@@ -77,6 +77,11 @@ typedef struct bb_rollout_buffers {
     double *ep_sums;    /* [3] sums over finished episodes: return, length, count */
 } bb_rollout_buffers;
 
+/* Test hook for the tcgen05 building blocks of bb_policy_forward's tensor-core path (csrc/bb_umma.cuh):
+ * D[128 x 32] = A[128 x K] . B[32 x K]^T as 3xTF32 through tcgen05.mma (kind::tf32, M = 128, N = 32, accumulator in tensor
+ * memory, read back with tcgen05.ld).  A, B, D: device pointers, f32, row-major; K a multiple of 8, 8..128. */
+int bb_umma_selftest(const float *a_dev, const float *b_dev, float *d_dev, int k, void *cuda_stream);
+
 /* ppo.py rollout() (ppo.py:60-141) on the engine's worlds for the trainee `agent_idx`:
  * env.reset() (env.py:178-185: Reset flags = 1, zero trainee action, one step, flags = 0), then T x
  * { Agent.forward on observations[:, agent_idx]; actions[:, agent_idx] = a; [frozen opponent:

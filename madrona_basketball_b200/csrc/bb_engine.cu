@@ -728,6 +728,7 @@ __global__ void bb_checksum_kernel(const __grid_constant__ ChecksumParams cp, in
 
 #include "bb_rollout.cuh"
 #include "bb_ppo.cuh"
+#include "bb_umma.cuh"
 
 /* ================================ host side ================================ */
 
@@ -1382,6 +1383,16 @@ int bb_checksum(bb_engine *e, uint64_t *out_dev, void *cuda_stream)
     }
     bb::bb_checksum_kernel<<<(int)((e->N + 127) / 128), 128, 0, (cudaStream_t)cuda_stream>>>(cp, e->N, out_dev);
     e->launches++;
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
+int bb_umma_selftest(const float *a_dev, const float *b_dev, float *d_dev, int k, void *cuda_stream)
+{
+    if (!a_dev || !b_dev || !d_dev || k < 8 || k > 128 || k % 8) { set_error("bb_umma_selftest: bad arguments"); return -1; }
+    const int smem = (128 + 128 + 32 + 32) * k * 4;
+    BB_CUDA_OK(cudaFuncSetAttribute(bb::bb_umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    bb::bb_umma_selftest_kernel<<<1, 128, smem, (cudaStream_t)cuda_stream>>>(a_dev, b_dev, d_dev, k);
     BB_CUDA_OK(cudaGetLastError());
     return 0;
 }

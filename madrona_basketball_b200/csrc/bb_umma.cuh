@@ -1,0 +1,184 @@
+/*
+ * bb_umma.cuh — 5th-generation tensor-core building blocks (tcgen05 / TMEM) for the policy contraction, sm_100a.
+ *
+ * The policy network (scripts/agent.py:108-154) is three small dense layers over a tile of observation rows:
+ * [rows x 128] . W1^T[128 x 32], [rows x 32] . W2^T, [rows x 32] . Wh^T.  With M = 128 rows per CTA each layer is one
+ * tcgen05.mma shape (M = 128, N = 32, kind::tf32, fp32 accumulator in tensor memory): a single thread issues the MMAs,
+ * the accumulator tile lives in TMEM with row i in TMEM lane i, and tcgen05.ld 32x32b hands every thread the 32 channels of
+ * ITS row -- so LayerNorm, ReLU, softmax and sampling are thread-local, with no quad shuffles.
+ *
+ * fp32-level accuracy (the parity bar against torch fp32) comes from 3xTF32: every operand is split x = hi + lo with
+ * hi = x & 0xffffe000 (what the tensor core reads) and lo = x - hi (exact), and each product is issued as
+ * hi.lo + lo.hi + hi.hi into the same accumulator.
+ *
+ * Shared-memory operand layout: the canonical K-major, no-swizzle UMMA layout (cute: "INTERLEAVE", ((8,n),2):((1,SBO),LBO) in
+ * 16-byte units): core matrices of 8 rows x 16 bytes (four tf32), 128 contiguous bytes each.  Element (row r, k) of an
+ * [R x K] operand sits at byte   (k / 4) * LBO + (r / 8) * 128 + (r % 8) * 16 + (k % 4) * 4,   LBO = (R / 8) * 128, SBO = 128.
+ * A thread that owns row r writes four consecutive k as one 16-byte store; the 32 lanes of a warp (32 consecutive rows)
+ * write 512 contiguous bytes: conflict-free.  One MMA instruction consumes K = 8 (two core matrices along K), so k-step s
+ * starts at byte 2 s LBO.
+ *
+ * Descriptor bit layouts follow cute/arch/mma_sm100_desc.hpp (SmemDescriptor, InstrDescriptor) of the CUTLASS tree vendored in
+ * this image; the PTX strings follow cute/arch/{mma_sm100_umma,copy_sm100,tmem_allocator_sm100}.hpp and cutlass/arch/barrier.h.
+ */
+#pragma once
+#include <cstdint>
+
+namespace bb {
+
+#define BBU __device__ __forceinline__
+
+BBU uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+/* 64-bit shared-memory matrix descriptor, SWIZZLE_NONE, version 1 (sm_100) */
+BBU uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes)
+{
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3fffu);          /* start address, 16-byte units, bits [0,14)  */
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16;    /* leading (K) byte offset, bits [16,30)      */
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32;    /* stride (M/N) byte offset, bits [32,46)     */
+    d |= (uint64_t)1 << 46;                               /* descriptor version = 1 (Blackwell)         */
+    return d;                                             /* base offset 0, layout type 0 = no swizzle  */
+}
+
+/* 32-bit instruction descriptor: D f32, A and B tf32, both K-major, dense */
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N)
+{
+    return (1u << 4)                      /* c_format = F32  */
+         | (2u << 7) | (2u << 10)         /* a_format = b_format = TF32 */
+         | ((uint32_t)(N >> 3) << 17)     /* n_dim */
+         | ((uint32_t)(M >> 4) << 24);    /* m_dim */
+}
+
+/* D[tmem] (+)= A[smem] . B[smem]^T, issued by ONE thread for the CTA */
+BBU void umma_tf32_ss(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n"
+                 :: "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+/* mbarrier arrive when every MMA issued so far by this thread has completed (implies tcgen05.fence::before_thread_sync) */
+BBU void umma_commit(uint64_t *mbar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(smem_u32(mbar)) : "memory");
+}
+BBU void mbar_init(uint64_t *mbar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(mbar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+/* bounded: a tensor-core operation that never completes (a malformed descriptor) must not hang the GPU; returns false after
+ * ~2^24 polls (tens of milliseconds), the callers then publish an error value instead of a result */
+BBU bool mbar_wait(uint64_t *mbar, uint32_t parity)
+{
+    const uint32_t a = smem_u32(mbar);
+    uint32_t done = 0;
+    for (uint32_t spins = 0; !done && spins < (1u << 24); spins++) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+                     : "=r"(done) : "r"(a), "r"(parity) : "memory");
+    }
+    return done != 0;
+}
+BBU void tc_fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+BBU void tc_fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+BBU void fence_smem_to_async_proxy() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+/* whole warp: allocate `cols` TMEM columns (power of two >= 32); the base address lands in *dst (shared memory) */
+BBU void tmem_alloc(uint32_t *dst, uint32_t cols)
+{
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(dst)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+BBU void tmem_free(uint32_t addr, uint32_t cols)
+{
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(addr), "r"(cols) : "memory");
+}
+/* whole warp w: lane i receives columns col .. col + 31 of TMEM lane 32 w + i (one accumulator row) */
+BBU void tmem_ld_row32(uint32_t tmem_base, int warp, int col, float (&v)[32])
+{
+    uint32_t r[32];
+    const uint32_t addr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)col;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+                   "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+                   "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                 : "r"(addr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+}
+
+/* ---- operand staging: 3xTF32 split of four consecutive k of one row, into the hi and lo copies of a K-major operand ---- */
+BBU void umma_split4(float4 x, uint4 &hi, uint4 &lo)
+{
+    hi.x = __float_as_uint(x.x) & 0xffffe000u; lo.x = __float_as_uint(x.x - __uint_as_float(hi.x));
+    hi.y = __float_as_uint(x.y) & 0xffffe000u; lo.y = __float_as_uint(x.y - __uint_as_float(hi.y));
+    hi.z = __float_as_uint(x.z) & 0xffffe000u; lo.z = __float_as_uint(x.z - __uint_as_float(hi.z));
+    hi.w = __float_as_uint(x.w) & 0xffffe000u; lo.w = __float_as_uint(x.w - __uint_as_float(hi.w));
+}
+/* byte offset of (row r, k-chunk kc) in an [R x K] operand (see the header comment) */
+BBU uint32_t umma_off(int r, int kc, int R) { return (uint32_t)(kc * (R / 8) * 128 + (r >> 3) * 128 + (r & 7) * 16); }
+
+/* One thread: D[128 x 32] (+)= A[128 x K] . B[32 x K]^T as 3xTF32: for every k-step hi.lo, lo.hi, hi.hi.
+ * aHi / aLo / bHi / bLo: shared addresses of the operand copies; `first` clears the accumulator on the very first MMA. */
+BBU void umma_issue_3xtf32(uint32_t tmem_d, uint32_t aHi, uint32_t aLo, uint32_t bHi, uint32_t bLo, int K, bool first)
+{
+    constexpr uint32_t idesc = umma_idesc_tf32(128, 32);
+    const uint32_t lboA = (128 / 8) * 128, lboB = (32 / 8) * 128;
+    uint32_t acc = first ? 0u : 1u;
+    for (int s = 0; s < K / 8; s++) {
+        const uint32_t oa = (uint32_t)(2 * s) * lboA, ob = (uint32_t)(2 * s) * lboB;
+        const uint64_t dAh = umma_smem_desc(aHi + oa, lboA, 128), dAl = umma_smem_desc(aLo + oa, lboA, 128);
+        const uint64_t dBh = umma_smem_desc(bHi + ob, lboB, 128), dBl = umma_smem_desc(bLo + ob, lboB, 128);
+        umma_tf32_ss(tmem_d, dAh, dBl, idesc, acc);
+        umma_tf32_ss(tmem_d, dAl, dBh, idesc, 1u);
+        umma_tf32_ss(tmem_d, dAh, dBh, idesc, 1u);
+        acc = 1u;
+    }
+}
+
+/* ---- self-test kernel (bb_umma_selftest): D[128 x 32] = A[128 x K] . B[32 x K]^T, one CTA of 128 threads ---- */
+__global__ void __launch_bounds__(128) bb_umma_selftest_kernel(const float *A, const float *B, float *D, int K)
+{
+    extern __shared__ __align__(128) unsigned char usm[];
+    __shared__ __align__(8) uint64_t mbar;
+    __shared__ uint32_t tmemBase;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    unsigned char *aHi = usm, *aLo = aHi + 128 * K * 4, *bHi = aLo + 128 * K * 4, *bLo = bHi + 32 * K * 4;
+    if (warp == 0) tmem_alloc(&tmemBase, 32);
+    if (tid == 0) mbar_init(&mbar, 1);
+    for (int kc = 0; kc < K / 4; kc++) {
+        uint4 hi, lo;
+        umma_split4(*reinterpret_cast<const float4 *>(A + (int64_t)tid * K + kc * 4), hi, lo);
+        *reinterpret_cast<uint4 *>(aHi + umma_off(tid, kc, 128)) = hi;
+        *reinterpret_cast<uint4 *>(aLo + umma_off(tid, kc, 128)) = lo;
+        if (tid < 32) {
+            umma_split4(*reinterpret_cast<const float4 *>(B + (int64_t)tid * K + kc * 4), hi, lo);
+            *reinterpret_cast<uint4 *>(bHi + umma_off(tid, kc, 32)) = hi;
+            *reinterpret_cast<uint4 *>(bLo + umma_off(tid, kc, 32)) = lo;
+        }
+    }
+    fence_smem_to_async_proxy();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem = tmemBase;
+    if (tid == 0) {
+        umma_issue_3xtf32(tmem, smem_u32(aHi), smem_u32(aLo), smem_u32(bHi), smem_u32(bLo), K, true);
+        umma_commit(&mbar);
+    }
+    const bool ok = mbar_wait(&mbar, 0);
+    tc_fence_after_sync();
+    float v[32];
+    if (ok) tmem_ld_row32(tmem, warp, 0, v);   /* warp-uniform */
+#pragma unroll
+    for (int i = 0; i < 32; i++) D[tid * 32 + i] = ok ? v[i] : -12345.f;
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_free(tmem, 32);
+}
+
+} // namespace bb

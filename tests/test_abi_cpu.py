@@ -34,7 +34,7 @@ def test_library_exports_every_declared_symbol(lib):
         assert hasattr(lib, sym), f"libbball.so lacks {sym}"
     assert sorted(_lib.SYMBOLS) == declared   # the ctypes table covers the whole header
     rollout = _declared_symbols("bb_rollout.h")
-    assert rollout == ["bb_gae", "bb_policy_forward", "bb_rollout"]
+    assert rollout == ["bb_gae", "bb_policy_forward", "bb_rollout", "bb_umma_selftest"]
     for sym in rollout:
         assert hasattr(lib, sym), f"libbball.so lacks {sym}"
     ppo = _declared_symbols("bb_ppo.h")

@@ -272,3 +272,36 @@ def test_ppo_iterations_train_end_to_end():
         x = agent.backbone(agent.obs_norm(obs))
         assert torch.allclose(logits, agent.actor(x), rtol=1e-5, atol=2e-5)
         assert torch.allclose(v_kernel, agent.critic(x).squeeze(-1), rtol=1e-5, atol=2e-5)
+
+
+@pytest.mark.parametrize("k", [8, 32, 128])
+def test_umma_selftest_matches_float64_matmul(k):
+    """csrc/bb_umma.cuh: tcgen05.mma kind::tf32 (M = 128, N = 32, accumulator in tensor memory) issued as 3xTF32 gives fp32-level
+    products: D = A . B^T against the float64 product, on random and on exactly representable inputs."""
+    import ctypes
+
+    import torch
+
+    from madrona_basketball_b200 import _lib
+
+    lib = _lib.load()
+    lib.bb_umma_selftest.restype = ctypes.c_int
+    lib.bb_umma_selftest.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    g = torch.Generator(device="cuda").manual_seed(5 + k)
+    for exact in (True, False):
+        if exact:   # small integers: every product and sum is exact in tf32 / fp32 -> bitwise equality expected
+            a = torch.randint(-8, 9, (128, k), device="cuda", generator=g).float()
+            b = torch.randint(-8, 9, (32, k), device="cuda", generator=g).float()
+        else:
+            a = torch.randn(128, k, device="cuda", generator=g)
+            b = torch.randn(32, k, device="cuda", generator=g)
+        d = torch.full((128, 32), float("nan"), device="cuda")
+        rc = lib.bb_umma_selftest(a.data_ptr(), b.data_ptr(), d.data_ptr(), k, torch.cuda.current_stream().cuda_stream)
+        assert rc == 0, _lib.last_error()
+        torch.cuda.synchronize()
+        want = a.double() @ b.double().t()
+        if exact:
+            assert torch.equal(d.double(), want)
+        else:
+            err = (d.double() - want).abs().max().item()
+            assert err < 2e-5 * max(1.0, want.abs().max().item()), err   # plain TF32 would be ~1e-2 here
