@@ -1424,6 +1424,24 @@ static int launch_policy(const bb_policy *pol, const bb::PolicyIo &io, cudaStrea
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    {   /* BB_POLICY_UMMA=1: the tcgen05 / TMEM kernel (csrc/bb_umma.cuh): 128 rows per CTA, one CTA per SM */
+        static int useUmma = -1;
+        if (useUmma < 0) { const char *s = getenv("BB_POLICY_UMMA"); useUmma = (s && atoi(s) != 0) ? 1 : 0; }
+        if (const char *s = getenv("BB_POLICY_UMMA_FORCE")) useUmma = atoi(s) != 0; /* tests switch per call */
+        if (useUmma) {
+            static bool attr = false;
+            if (!attr) {
+                BB_CUDA_OK(cudaFuncSetAttribute(bb::bb_policy_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::kUmSmemBytes));
+                attr = true;
+            }
+            int64_t tiles = (io.n + bb::kUmRows - 1) / bb::kUmRows;
+            if (tiles > sms) tiles = sms;
+            if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_policy_umma_kernel, (int)tiles, bb::kUmRows, (size_t)bb::kUmSmemBytes, stream, true, *pol, io));
+            else bb::bb_policy_umma_kernel<<<(int)tiles, bb::kUmRows, bb::kUmSmemBytes, stream>>>(*pol, io);
+            BB_CUDA_OK(cudaGetLastError());
+            return 0;
+        }
+    }
     int64_t blocks = (io.n + bb::kRowsPerBlock - 1) / bb::kRowsPerBlock;
     if (blocks > 4 * (int64_t)sms) blocks = 4 * (int64_t)sms; /* rows are strided over the resident blocks */
     if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_policy_kernel, (int)blocks, bb::kPolThreads, (size_t)0, stream, true, *pol, io));

@@ -181,4 +181,256 @@ __global__ void __launch_bounds__(128) bb_umma_selftest_kernel(const float *A, c
     if (warp == 0) tmem_free(tmem, 32);
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * bb_policy_umma_kernel — Agent.forward (scripts/agent.py:134-154, action.py:20-33) on the 5th-generation tensor cores.
+ *
+ * One CTA of 128 threads = one tile of 128 observation rows, one row per thread (grid-strided over the tiles).
+ *   stage    the thread reads its 512-byte row (32 x LDG.128), copies it to the rollout buffer, normalises it
+ *            (agent.py:27-39), splits it hi / lo and writes the two K-major operand copies (64 KB each);
+ *   layer 1  one thread issues 16 k-steps x 3 tcgen05.mma (M 128, N 32, K 8, kind::tf32) into TMEM columns 0..31,
+ *            commits to an mbarrier; every thread then reads ITS row's 32 channels with tcgen05.ld, adds the bias and does
+ *            LayerNorm + ReLU on registers, and writes the row as the next operand (16 KB per copy, over the old one);
+ *   layer 2  4 k-steps x 3 MMAs into columns 32..63, same epilogue;
+ *   heads    4 k-steps x 3 MMAs into columns 64..95 (19 logits + value, 12 zero columns);
+ *   tail     the six bucketed categoricals, the summed log-probability and the rollout bookkeeping, thread per row, with the
+ *            arithmetic of bb_policy_kernel's tail (same softmax / inverse-CDF expressions, same Threefry words).
+ * Weights are staged once per CTA as hi / lo K-major operands (W1 2 x 16 KB, W2 and heads 2 x 4 KB each) before
+ * griddepcontrol.wait (they do not depend on the preceding step kernel).  Shared memory: 178 KB -> one CTA per SM.
+ * ------------------------------------------------------------------------------------------------ */
+constexpr int kUmRows = 128;
+constexpr int kUmA = kUmRows * BB_OBS_DIM * 4;      /* 65536: one copy of the layer-1 A operand */
+constexpr int kUmW1 = kH * BB_OBS_DIM * 4;          /* 16384 */
+constexpr int kUmW2 = kH * kH * 4;                  /* 4096  */
+constexpr int kUmOffW1 = 2 * kUmA;
+constexpr int kUmOffW2 = kUmOffW1 + 2 * kUmW1;
+constexpr int kUmOffWh = kUmOffW2 + 2 * kUmW2;
+constexpr int kUmOffPar = kUmOffWh + 2 * kUmW2;
+constexpr int kUmParFloats = 2 * BB_OBS_DIM + 7 * kH;   /* mean, inv, b1 g1 e1 b2 g2 e2, bh(32) */
+constexpr int kUmSmemBytes = kUmOffPar + kUmParFloats * 4;
+
+/* nn.LayerNorm(H) + ReLU over one thread's 32 channels (channels >= H hold 0 and stay 0); biased variance, eps 1e-5 */
+BBU void um_layer_norm_relu(float (&v)[kH], int H, const float *g, const float *b)
+{
+    float s = 0.f;
+#pragma unroll
+    for (int c = 0; c < kH; c++) s += v[c];
+    const float inv = 1.f / (float)H;
+    const float mean = s * inv;
+    s = 0.f;
+#pragma unroll
+    for (int c = 0; c < kH; c++) {
+        v[c] = (c < H) ? v[c] - mean : 0.f;
+        s = fmaf(v[c], v[c], s);
+    }
+    const float rstd = rsqrtf(s * inv + 1e-5f);
+#pragma unroll
+    for (int c = 0; c < kH; c++) v[c] = (c < H) ? fmaxf(fmaf(v[c] * rstd, g[c], b[c]), 0.f) : 0.f;
+}
+
+/* the row's 32 activations -> hi / lo copies of a [128 x 32] K-major operand */
+BBU void um_store_row32(unsigned char *hiBase, unsigned char *loBase, int row, const float (&v)[kH])
+{
+#pragma unroll
+    for (int kc = 0; kc < kH / 4; kc++) {
+        uint4 hi, lo;
+        umma_split4(make_float4(v[4 * kc], v[4 * kc + 1], v[4 * kc + 2], v[4 * kc + 3]), hi, lo);
+        const uint32_t off = umma_off(row, kc, kUmRows);
+        *reinterpret_cast<uint4 *>(hiBase + off) = hi;
+        *reinterpret_cast<uint4 *>(loBase + off) = lo;
+    }
+}
+
+__global__ void __launch_bounds__(kUmRows, 1) bb_policy_umma_kernel(const bb_policy P, const PolicyIo io)
+{
+    extern __shared__ __align__(128) unsigned char usm[];
+    __shared__ __align__(8) uint64_t mbar;
+    __shared__ uint32_t tmemBase;
+    const int H = P.hidden;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    unsigned char *aHi = usm, *aLo = usm + kUmA;
+    unsigned char *w1Hi = usm + kUmOffW1, *w1Lo = w1Hi + kUmW1;
+    unsigned char *w2Hi = usm + kUmOffW2, *w2Lo = w2Hi + kUmW2;
+    unsigned char *whHi = usm + kUmOffWh, *whLo = whHi + kUmW2;
+    float *par = reinterpret_cast<float *>(usm + kUmOffPar);
+    float *sMean = par, *sInv = par + BB_OBS_DIM, *sB1 = sInv + BB_OBS_DIM, *sG1 = sB1 + kH, *sE1 = sG1 + kH;
+    float *sB2 = sE1 + kH, *sG2 = sB2 + kH, *sE2 = sG2 + kH, *sBh = sE2 + kH;
+
+    if (warp == 0) tmem_alloc(&tmemBase, 128);
+    if (tid == 0) mbar_init(&mbar, 1);
+    /* ---- weights -> hi / lo K-major operands (consecutive threads = consecutive output rows: 512 contiguous bytes per chunk) ---- */
+    for (int i = tid; i < kH * (BB_OBS_DIM / 4); i += kUmRows) {
+        const int kc = i / kH, j = i % kH;
+        const float4 w = j < H ? *reinterpret_cast<const float4 *>(P.w1 + j * BB_OBS_DIM + kc * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        uint4 hi, lo;
+        umma_split4(w, hi, lo);
+        *reinterpret_cast<uint4 *>(w1Hi + umma_off(j, kc, kH)) = hi;
+        *reinterpret_cast<uint4 *>(w1Lo + umma_off(j, kc, kH)) = lo;
+    }
+    for (int i = tid; i < kH * (kH / 4); i += kUmRows) {
+        const int kc = i / kH, j = i % kH;
+        float w2v[4], whv[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const int k = kc * 4 + e;
+            w2v[e] = (j < H && k < H) ? P.w2[j * H + k] : 0.f;
+            whv[e] = (k < H && j < kHeads) ? (j < BB_NUM_LOGITS ? P.wa[j * H + k] : P.wc[k]) : 0.f;
+        }
+        uint4 hi, lo;
+        umma_split4(make_float4(w2v[0], w2v[1], w2v[2], w2v[3]), hi, lo);
+        *reinterpret_cast<uint4 *>(w2Hi + umma_off(j, kc, kH)) = hi;
+        *reinterpret_cast<uint4 *>(w2Lo + umma_off(j, kc, kH)) = lo;
+        umma_split4(make_float4(whv[0], whv[1], whv[2], whv[3]), hi, lo);
+        *reinterpret_cast<uint4 *>(whHi + umma_off(j, kc, kH)) = hi;
+        *reinterpret_cast<uint4 *>(whLo + umma_off(j, kc, kH)) = lo;
+    }
+    if (tid < BB_OBS_DIM) { sMean[tid] = P.obs_mean[tid]; sInv[tid] = P.obs_inv_std[tid]; }
+    if (tid < kH) {
+        const bool a = tid < H;
+        sB1[tid] = a ? P.b1[tid] : 0.f; sG1[tid] = a ? P.ln1_g[tid] : 0.f; sE1[tid] = a ? P.ln1_b[tid] : 0.f;
+        sB2[tid] = a ? P.b2[tid] : 0.f; sG2[tid] = a ? P.ln2_g[tid] : 0.f; sE2[tid] = a ? P.ln2_b[tid] : 0.f;
+        sBh[tid] = tid < BB_NUM_LOGITS ? P.ba[tid] : (tid == BB_NUM_LOGITS ? P.bc[0] : 0.f);
+    }
+    /* programmatic dependent launch (bb_rollout): everything below depends on the step kernel that precedes this launch */
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem = tmemBase;
+    const uint32_t aHiS = smem_u32(aHi), aLoS = smem_u32(aLo);
+    uint32_t phase = 0;
+    bool ok = true;
+
+    for (int64_t row0 = (int64_t)blockIdx.x * kUmRows; row0 < io.n; row0 += (int64_t)gridDim.x * kUmRows) {
+        const int64_t rr = row0 + tid;
+        const bool valid = rr < io.n;
+        const int64_t r = valid ? rr : io.n - 1; /* tail threads shadow the last row and never store */
+        /* ---- stage the row: buffer copy, normaliser, hi / lo operands ---- */
+        {
+            const float4 *orow = reinterpret_cast<const float4 *>(io.obs + r * io.obsStride);
+            float4 *brow = (io.bufObs && valid) ? reinterpret_cast<float4 *>(io.bufObs + r * BB_OBS_DIM) : nullptr;
+#pragma unroll 4
+            for (int kc = 0; kc < BB_OBS_DIM / 4; kc++) {
+                const float4 x = orow[kc];
+                if (brow) brow[kc] = x;   /* buffer.obs[step] = obs (ppo.py:128) */
+                const float4 mu = *reinterpret_cast<const float4 *>(sMean + kc * 4);
+                const float4 is = *reinterpret_cast<const float4 *>(sInv + kc * 4);
+                float4 xn = make_float4((x.x - mu.x) * is.x, (x.y - mu.y) * is.y, (x.z - mu.z) * is.z, (x.w - mu.w) * is.w);
+                if (P.obs_clamp > 0.f) {
+                    xn.x = fminf(fmaxf(xn.x, -P.obs_clamp), P.obs_clamp); xn.y = fminf(fmaxf(xn.y, -P.obs_clamp), P.obs_clamp);
+                    xn.z = fminf(fmaxf(xn.z, -P.obs_clamp), P.obs_clamp); xn.w = fminf(fmaxf(xn.w, -P.obs_clamp), P.obs_clamp);
+                }
+                uint4 hi, lo;
+                umma_split4(xn, hi, lo);
+                const uint32_t off = umma_off(tid, kc, kUmRows);
+                *reinterpret_cast<uint4 *>(aHi + off) = hi;
+                *reinterpret_cast<uint4 *>(aLo + off) = lo;
+            }
+        }
+        float v[kH];
+        /* ---- the three layers: operands visible to the async proxy -> one thread issues -> everyone reads its row ---- */
+#pragma unroll 1
+        for (int layer = 0; layer < 3; layer++) {
+            fence_smem_to_async_proxy();
+            tc_fence_before_sync();
+            __syncthreads();
+            tc_fence_after_sync();
+            if (tid == 0) {
+                const uint32_t bHi = smem_u32(layer == 0 ? w1Hi : layer == 1 ? w2Hi : whHi);
+                const uint32_t bLo = smem_u32(layer == 0 ? w1Lo : layer == 1 ? w2Lo : whLo);
+                umma_issue_3xtf32(tmem + 32u * (uint32_t)layer, aHiS, aLoS, bHi, bLo, layer == 0 ? BB_OBS_DIM : kH, true);
+                umma_commit(&mbar);
+            }
+            ok = mbar_wait(&mbar, phase) && ok;
+            phase ^= 1u;
+            tc_fence_after_sync();
+            tmem_ld_row32(tmem, warp, 32 * layer, v);
+            if (layer < 2) {
+                const float *bb = layer == 0 ? sB1 : sB2;
+#pragma unroll
+                for (int c = 0; c < kH; c++) v[c] += bb[c];
+                um_layer_norm_relu(v, H, layer == 0 ? sG1 : sG2, layer == 0 ? sE1 : sE2);
+                um_store_row32(aHi, aLo, tid, v);   /* the previous operand has been consumed: the MMAs completed */
+            }
+        }
+        /* ---- heads: v[0..18] actor logits, v[19] critic ---- */
+#pragma unroll
+        for (int c = 0; c < kHeads; c++) v[c] += sBh[c];
+        if (!ok) {   /* a tensor-core batch never completed: make the failure visible instead of publishing garbage */
+#pragma unroll
+            for (int c = 0; c < kHeads; c++) v[c] = __int_as_float(0x7fc00000);
+        }
+        if (valid) {
+            if (io.logitsOut) {
+#pragma unroll
+                for (int c = 0; c < BB_NUM_LOGITS; c++) io.logitsOut[r * BB_NUM_LOGITS + c] = v[c];
+            }
+            if (io.evaluateOnly) { if (io.nextValue) io.nextValue[r] = v[BB_NUM_LOGITS]; }
+            else if (io.valueOut) io.valueOut[r] = v[BB_NUM_LOGITS];
+        }
+        if (!io.evaluateOnly) {
+            /* ---- bucketed categoricals (action.py:5-33), the expressions of bb_policy_kernel's tail, bucket by bucket ---- */
+            float tot = 0.f;
+            uint32_t x0 = 0, x1 = 0;
+#pragma unroll
+            for (int b = 0; b < BB_NUM_ACTION_DIMS; b++) {
+                constexpr int kOff[BB_NUM_ACTION_DIMS] = {0, 2, 10, 13, 15, 17};
+                constexpr int kCnt[BB_NUM_ACTION_DIMS] = {2, 8, 3, 2, 2, 2};
+                const int off = kOff[b], cnt = kCnt[b];
+                float m = v[off];
+#pragma unroll
+                for (int i = 1; i < cnt; i++) m = fmaxf(m, v[off + i]);
+                float e[8];
+                float s = 0.f;
+#pragma unroll
+                for (int i = 0; i < cnt; i++) { e[i] = expf(v[off + i] - m); s += e[i]; }
+                const float lse = m + logf(s);
+                int a = 0;
+                float la = v[off];
+                if (io.stochastic) { /* inverse CDF: smallest a with u * s < e_0 + .. + e_a; word (b & 1) of Threefry call b >> 1 */
+                    if ((b & 1) == 0) threefry2x32(io.seed, (uint32_t)(io.rowOffset + r), io.draw, (uint32_t)(b >> 1), x0, x1);
+                    const float us = ((float)(((b & 1) ? x1 : x0) >> 8) * 0x1p-24f) * s;
+                    float c = 0.f;
+                    a = cnt - 1;
+                    la = v[off + cnt - 1];
+                    bool found = false;
+#pragma unroll
+                    for (int i = 0; i < cnt; i++) {
+                        c += e[i];
+                        if (!found && us < c) { a = i; la = v[off + i]; found = true; }
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 1; i < cnt; i++) if (v[off + i] > la) { a = i; la = v[off + i]; }
+                }
+                tot += la - lse;
+                if (valid) {
+                    if (io.actionsOut) io.actionsOut[r * io.actionStride + b] = a;
+                    if (io.bufActions) io.bufActions[r * BB_NUM_ACTION_DIMS + b] = (float)a;
+                }
+            }
+            if (valid && io.logpOut) io.logpOut[r] = tot;
+        }
+        /* ---- bookkeeping of the previous step (ppo.py:84-85,128-134; ppo_stats.py:21-36) ---- */
+        if (valid && io.bufRewPrev) {
+            const float rw = io.rew[r * io.rdStride], dn = io.done[r * io.rdStride];
+            io.bufRewPrev[r] = rw;
+            io.bufNotDonePrev[r] = 1.0f - dn;
+            if (io.curReward) {
+                const float cr = io.curReward[r] + rw, el = io.epLength[r] + 1.f;
+                if (dn != 0.f) {
+                    atomicAdd(&io.epSums[0], (double)cr);
+                    atomicAdd(&io.epSums[1], (double)el);
+                    atomicAdd(&io.epSums[2], 1.0);
+                }
+                io.curReward[r] = cr * (1.f - dn);
+                io.epLength[r] = el * (1.f - dn);
+            }
+        }
+        if (valid && io.resetCol) *reinterpret_cast<int2 *>(io.resetCol + r * 2) = make_int2(0, 0);
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_free(tmem, 128);
+}
+
 } // namespace bb

@@ -25,7 +25,8 @@ def _agent(g, prefix="sd0::"):
     return a.cuda()
 
 
-def test_policy_kernel_matches_reference_agent_forward():
+@pytest.mark.parametrize("flavour", ["mma_sync", "tcgen05"])
+def test_policy_kernel_matches_reference_agent_forward(flavour, monkeypatch):
     """bb_policy_forward vs Agent.norm_obs_backbone + actor / critic (agent.py:134-154) and
     DiscreteActionDistributions.best / action_stats (action.py:20-45): logits / value rtol 1e-5 + atol 2e-5
     (3xTF32 products), argmax actions equal wherever the top two logits of a bucket differ by more than 1e-4."""
@@ -33,6 +34,7 @@ def test_policy_kernel_matches_reference_agent_forward():
 
     from madrona_basketball_b200.rollout import PolicyWeights, policy_forward
 
+    monkeypatch.setenv("BB_POLICY_UMMA_FORCE", "1" if flavour == "tcgen05" else "0")   # csrc/bb_umma.cuh vs the mma.sync kernel
     g = np.load(GOLD)
     agent = _agent(g)
     w = PolicyWeights.from_module(agent)

@@ -37,8 +37,16 @@ def _obs_batch(n, seed=0):
     return sim, sim.observations_tensor().to_torch()
 
 
+@pytest.fixture(params=["mma_sync", "tcgen05"])
+def policy_flavour(request, monkeypatch):
+    """bb_policy_forward's two kernels: the default warp-level one (mma.sync 3xTF32) and the tcgen05 / TMEM one
+    (BB_POLICY_UMMA, csrc/bb_umma.cuh); both are held to the same torch fp32 reference."""
+    monkeypatch.setenv("BB_POLICY_UMMA_FORCE", "1" if request.param == "tcgen05" else "0")
+    return request.param
+
+
 @pytest.mark.parametrize("hidden", [32, 16])
-def test_policy_forward_matches_torch(hidden):
+def test_policy_forward_matches_torch(hidden, policy_flavour):
     import torch
 
     from madrona_basketball_b200.rollout import PolicyWeights, policy_forward
@@ -81,7 +89,7 @@ def test_policy_forward_matches_torch(hidden):
             assert np.array_equal(ad[clear, b], sl.argmax(dim=1).cpu().numpy()[clear])
 
 
-def test_sampler_follows_the_categorical_distribution():
+def test_sampler_follows_the_categorical_distribution(policy_flavour):
     """Many draws for a handful of rows: empirical frequencies vs softmax probabilities (chi-square)."""
     import torch
 
