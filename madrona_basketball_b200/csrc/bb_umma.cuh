@@ -195,10 +195,15 @@ __global__ void __launch_bounds__(128) bb_umma_selftest_kernel(const float *A, c
  *   tail     the six bucketed categoricals, the summed log-probability and the rollout bookkeeping, thread per row, with the
  *            arithmetic of bb_policy_kernel's tail (same softmax / inverse-CDF expressions, same Threefry words).
  * Weights are staged once per CTA as hi / lo K-major operands (W1 2 x 16 KB, W2 and heads 2 x 4 KB each) before
- * griddepcontrol.wait (they do not depend on the preceding step kernel).  Shared memory: 178 KB -> one CTA per SM.
+ * griddepcontrol.wait (they do not depend on the preceding step kernel).  Layer 1 is issued as two K = 64 passes through one
+ * 2 x 32 KB operand buffer (the row waits in registers), which keeps the CTA at 114 KB of shared memory: in the rollout chain
+ * its blocks must become resident NEXT TO the step kernel's (programmatic dependent launch overlaps this kernel's weight
+ * staging with the step's tail and the next step's launch with this kernel's tail); at 178 KB they could not, and the rollout
+ * lost 7 us per step.
  * ------------------------------------------------------------------------------------------------ */
 constexpr int kUmRows = 128;
-constexpr int kUmA = kUmRows * BB_OBS_DIM * 4;      /* 65536: one copy of the layer-1 A operand */
+constexpr int kUmKHalf = BB_OBS_DIM / 2;           /* layer 1 runs as two K = 64 passes over one 32 KB operand buffer per copy */
+constexpr int kUmA = kUmRows * kUmKHalf * 4;       /* 32768: one copy of (half of) the layer-1 A operand */
 constexpr int kUmW1 = kH * BB_OBS_DIM * 4;          /* 16384 */
 constexpr int kUmW2 = kH * kH * 4;                  /* 4096  */
 constexpr int kUmOffW1 = 2 * kUmA;
@@ -304,13 +309,18 @@ __global__ void __launch_bounds__(kUmRows, 1) bb_policy_umma_kernel(const bb_pol
         const int64_t rr = row0 + tid;
         const bool valid = rr < io.n;
         const int64_t r = valid ? rr : io.n - 1; /* tail threads shadow the last row and never store */
-        /* ---- stage the row: buffer copy, normaliser, hi / lo operands ---- */
+        /* ---- the row: requested up front (32 independent 16-byte loads per thread in flight: with one thread per row the
+         * loads of a warp are strided by the row pitch, so their latency is paid once, not per chunk), copied to the rollout
+         * buffer and normalised in registers (agent.py:27-39) ---- */
+        float4 xr[BB_OBS_DIM / 4];
         {
             const float4 *orow = reinterpret_cast<const float4 *>(io.obs + r * io.obsStride);
             float4 *brow = (io.bufObs && valid) ? reinterpret_cast<float4 *>(io.bufObs + r * BB_OBS_DIM) : nullptr;
-#pragma unroll 4
+#pragma unroll
+            for (int kc = 0; kc < BB_OBS_DIM / 4; kc++) xr[kc] = orow[kc];
+#pragma unroll
             for (int kc = 0; kc < BB_OBS_DIM / 4; kc++) {
-                const float4 x = orow[kc];
+                const float4 x = xr[kc];
                 if (brow) brow[kc] = x;   /* buffer.obs[step] = obs (ppo.py:128) */
                 const float4 mu = *reinterpret_cast<const float4 *>(sMean + kc * 4);
                 const float4 is = *reinterpret_cast<const float4 *>(sInv + kc * 4);
@@ -319,37 +329,52 @@ __global__ void __launch_bounds__(kUmRows, 1) bb_policy_umma_kernel(const bb_pol
                     xn.x = fminf(fmaxf(xn.x, -P.obs_clamp), P.obs_clamp); xn.y = fminf(fmaxf(xn.y, -P.obs_clamp), P.obs_clamp);
                     xn.z = fminf(fmaxf(xn.z, -P.obs_clamp), P.obs_clamp); xn.w = fminf(fmaxf(xn.w, -P.obs_clamp), P.obs_clamp);
                 }
-                uint4 hi, lo;
-                umma_split4(xn, hi, lo);
-                const uint32_t off = umma_off(tid, kc, kUmRows);
-                *reinterpret_cast<uint4 *>(aHi + off) = hi;
-                *reinterpret_cast<uint4 *>(aLo + off) = lo;
+                xr[kc] = xn;
             }
         }
         float v[kH];
-        /* ---- the three layers: operands visible to the async proxy -> one thread issues -> everyone reads its row ---- */
+        /* ---- four tensor-core passes: layer 1 (k 0..63), layer 1 (k 64..127, accumulating), layer 2, heads.  Each pass: the
+         * threads write their row's operand chunks, make them visible to the async proxy, one thread issues, everyone waits on
+         * the mbarrier (so the operand buffer is free again) ---- */
 #pragma unroll 1
-        for (int layer = 0; layer < 3; layer++) {
+        for (int pass = 0; pass < 4; pass++) {
+            if (pass < 2) {
+#pragma unroll
+                for (int kc = 0; kc < kUmKHalf / 4; kc++) {
+                    uint4 hi, lo;
+                    const float4 x = pass == 0 ? xr[kc] : xr[kc + kUmKHalf / 4];
+                    umma_split4(x, hi, lo);
+                    const uint32_t off = umma_off(tid, kc, kUmRows);
+                    *reinterpret_cast<uint4 *>(aHi + off) = hi;
+                    *reinterpret_cast<uint4 *>(aLo + off) = lo;
+                }
+            }
             fence_smem_to_async_proxy();
             tc_fence_before_sync();
             __syncthreads();
             tc_fence_after_sync();
+            const int layer = pass == 0 ? 0 : pass - 1;
             if (tid == 0) {
-                const uint32_t bHi = smem_u32(layer == 0 ? w1Hi : layer == 1 ? w2Hi : whHi);
-                const uint32_t bLo = smem_u32(layer == 0 ? w1Lo : layer == 1 ? w2Lo : whLo);
-                umma_issue_3xtf32(tmem + 32u * (uint32_t)layer, aHiS, aLoS, bHi, bLo, layer == 0 ? BB_OBS_DIM : kH, true);
+                if (pass < 2) {   /* W1's k-chunks 16 p .. 16 p + 15: chunk kc of the [32 x 128] operand starts at kc * LBO_B */
+                    const uint32_t wOff = (uint32_t)pass * (uint32_t)(kUmKHalf / 4) * (uint32_t)((kH / 8) * 128);
+                    umma_issue_3xtf32(tmem, aHiS, aLoS, smem_u32(w1Hi) + wOff, smem_u32(w1Lo) + wOff, kUmKHalf, pass == 0);
+                } else {
+                    umma_issue_3xtf32(tmem + 32u * (uint32_t)layer, aHiS, aLoS, smem_u32(layer == 1 ? w2Hi : whHi),
+                                      smem_u32(layer == 1 ? w2Lo : whLo), kH, true);
+                }
                 umma_commit(&mbar);
             }
             ok = mbar_wait(&mbar, phase) && ok;
             phase ^= 1u;
             tc_fence_after_sync();
+            if (pass == 0) continue;
             tmem_ld_row32(tmem, warp, 32 * layer, v);
             if (layer < 2) {
                 const float *bb = layer == 0 ? sB1 : sB2;
 #pragma unroll
                 for (int c = 0; c < kH; c++) v[c] += bb[c];
                 um_layer_norm_relu(v, H, layer == 0 ? sG1 : sG2, layer == 0 ? sE1 : sE2);
-                um_store_row32(aHi, aLo, tid, v);   /* the previous operand has been consumed: the MMAs completed */
+                um_store_row32(aHi, aLo, tid, v);   /* the operand buffer is free: the MMAs that read it have completed */
             }
         }
         /* ---- heads: v[0..18] actor logits, v[19] critic ---- */
