@@ -13,6 +13,7 @@ DEPS = SOURCES + [
     os.path.join(_HERE, "csrc", "bb_pair.cuh"),
     os.path.join(_HERE, "csrc", "bb_rollout.cuh"),
     os.path.join(_HERE, "csrc", "bb_ppo.cuh"),
+    os.path.join(_HERE, "csrc", "bb_umma.cuh"),
     os.path.join(_HERE, "..", "include", "bb_ppo.h"),
     os.path.join(_HERE, "..", "include", "bb_rollout.h"),
     os.path.join(_HERE, "..", "include", "bb_math.h"),
