@@ -91,6 +91,23 @@ int64_t bb_ppo_moments_workspace_bytes(void);
 int bb_ppo_moments(const float *obs, const float *values_unnorm, const float *returns, const float *advantages, int64_t rows,
                    void *workspace, double *sums_out, void *cuda_stream);
 
+/* bb_ppo_moments without a workspace argument, for callers that cannot allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The per-block partial sums go to a static device array inside the library
+ * (BB_PPO_MOMENTS_STATIC_MAX_BLOCKS x 2 x 131 doubles = 1 073 152 bytes, held by every GPU that loads libbball.so until
+ * the process exits); the call itself performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ * Same kernels, same grid and therefore the same bits in sums_out as bb_ppo_moments.
+ * Limits: rows <= BB_PPO_MOMENTS_STATIC_MAX_ROWS and a device whose grid (2 blocks per SM) fits
+ * BB_PPO_MOMENTS_STATIC_MAX_BLOCKS, i.e. up to 256 SMs; beyond either the call fails with a message in bb_last_error().
+ * ALL calls on a device share the one array (it keeps the previous call's partials; nothing needs clearing because
+ * every block overwrites its whole partial and only those are read): calls that overlap on the GPU -- different
+ * streams, or different threads / processes' graphs replayed concurrently on one context -- race.  Serialise them on
+ * one stream, or use bb_ppo_moments with a workspace per stream. */
+#define BB_PPO_MOMENTS_STATIC_MAX_BLOCKS 512
+#define BB_PPO_MOMENTS_STATIC_MAX_ROWS (1 << 24)
+int bb_ppo_moments_static(const float *obs, const float *values_unnorm, const float *returns, const float *advantages,
+                          int64_t rows, double *sums_out, void *cuda_stream);
+
 /* RunningMeanStd state (agent.py:24-26): float64 mean[dim], var[dim], count[1] on the device, updated in place. */
 typedef struct bb_running_norm { double *mean, *var, *count; } bb_running_norm;
 

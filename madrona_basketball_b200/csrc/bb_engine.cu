@@ -1701,6 +1701,73 @@ int bb_ppo_moments(const float *obs, const float *values_unnorm, const float *re
     return 0;
 }
 
+/* ---- bb_ppo_moments for callers that may not allocate (graph capture, serving loops): the per-block partial sums live in
+ * a file-scope device array instead of a caller-provided workspace.  The array belongs to the library image: every GPU
+ * that loads libbball.so holds these bytes until the process exits.  Its NAME is only a host-side stand-in here -- the
+ * device address is looked up once per device with cudaGetSymbolAddress (that device current) and handed to the kernels. */
+} // extern "C" (device storage and its address table have C++ linkage)
+
+namespace bb {
+constexpr int kMomStaticDoubles = BB_PPO_MOMENTS_STATIC_MAX_BLOCKS * 2 * kMomCols;
+static __device__ __align__(256) double g_momentsScratch[kMomStaticDoubles];
+} // namespace bb
+
+static constexpr int kMomStaticMaxDevices = 64;
+static double *g_momentsScratchAddr[kMomStaticMaxDevices]; /* per device, nullptr until resolved */
+
+static double *moments_static_scratch()
+{
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMomStaticMaxDevices) {
+        set_error("bb_ppo_moments_static: no current CUDA device (or device ordinal beyond " + std::to_string(kMomStaticMaxDevices - 1) + ")");
+        return nullptr;
+    }
+    double *p = __atomic_load_n(&g_momentsScratchAddr[dev], __ATOMIC_ACQUIRE);
+    if (p) return p;
+    void *sym = nullptr;
+    const cudaError_t err = cudaGetSymbolAddress(&sym, bb::g_momentsScratch);
+    if (err != cudaSuccess || !sym) {
+        set_error(std::string("bb_ppo_moments_static: cudaGetSymbolAddress(g_momentsScratch) failed: ") + cudaGetErrorString(err));
+        return nullptr;
+    }
+    if (((uintptr_t)sym & 255) != 0) { set_error("bb_ppo_moments_static: scratch array is not 256-byte aligned"); return nullptr; }
+    __atomic_store_n(&g_momentsScratchAddr[dev], (double *)sym, __ATOMIC_RELEASE); /* racing threads resolve the same address */
+    return (double *)sym;
+}
+
+extern "C" {
+
+int bb_ppo_moments_static(const float *obs, const float *values_unnorm, const float *returns, const float *advantages, int64_t rows,
+                          double *sums_out, void *cuda_stream)
+{
+    if (!obs || !values_unnorm || !returns || !advantages || rows <= 0 || !sums_out) { set_error("bb_ppo_moments_static: bad arguments"); return -1; }
+    if (((uintptr_t)obs & 15) != 0) { set_error("bb_ppo_moments_static: obs must be 16-byte aligned"); return -1; }
+    if (rows > (int64_t)BB_PPO_MOMENTS_STATIC_MAX_ROWS) {
+        set_error("bb_ppo_moments_static: " + std::to_string(rows) + " rows exceed the static limit of " +
+                  std::to_string((int64_t)BB_PPO_MOMENTS_STATIC_MAX_ROWS) + " (BB_PPO_MOMENTS_STATIC_MAX_ROWS); use bb_ppo_moments with a workspace");
+        return -1;
+    }
+    int maxBlocks = 0;
+    if (ppo_grid(&maxBlocks) != 0) return -1;
+    const int64_t want = (rows + 7) / 8;
+    const int blocks = (int)(want < maxBlocks ? want : maxBlocks); /* the grid bb_ppo_moments uses: same partials, same bits */
+    if (blocks > BB_PPO_MOMENTS_STATIC_MAX_BLOCKS) {
+        set_error("bb_ppo_moments_static: this device's grid of " + std::to_string(blocks) + " blocks exceeds the static scratch of " +
+                  std::to_string(BB_PPO_MOMENTS_STATIC_MAX_BLOCKS) + " block partials (BB_PPO_MOMENTS_STATIC_MAX_BLOCKS); use bb_ppo_moments");
+        return -1;
+    }
+    double *scratch = moments_static_scratch();
+    if (!scratch) return -1;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    /* nothing has to start at zero: blocks 0 .. blocks-1 overwrite every entry of their partial, and the reduction reads
+     * exactly those; whatever an earlier (larger) call left beyond them is never read */
+    bb::bb_ppo_moments_kernel<<<blocks, bb::kMomThreads, 0, st>>>(obs, values_unnorm, returns, advantages, rows, scratch);
+    BB_CUDA_OK(cudaGetLastError());
+    bb::bb_ppo_moments_reduce_kernel<<<(2 * bb::kMomCols + 63) / 64, 64, 0, st>>>((const double *)scratch, blocks, sums_out);
+    BB_CUDA_OK(cudaGetLastError());
+    return 0;
+}
+
 int bb_ppo_finish_advantages(const double *sums, double global_rows, const bb_running_norm *obs_norm, const bb_running_norm *value_norm,
                              float *obs_mean_f32, float *obs_inv_std_f32, float value_clamp, float *values_unnorm, float *returns,
                              float *advantages, int64_t rows, float *scratch, void *cuda_stream)

@@ -39,7 +39,7 @@ def test_library_exports_every_declared_symbol(lib):
         assert hasattr(lib, sym), f"libbball.so lacks {sym}"
     ppo = _declared_symbols("bb_ppo.h")
     assert ppo == ["bb_p2p_connect", "bb_p2p_create", "bb_p2p_destroy", "bb_ppo_adam", "bb_ppo_adam_p2p", "bb_ppo_finish_advantages",
-                   "bb_ppo_grad", "bb_ppo_moments", "bb_ppo_moments_workspace_bytes", "bb_ppo_workspace_bytes", "bb_randperm",
+                   "bb_ppo_grad", "bb_ppo_moments", "bb_ppo_moments_static", "bb_ppo_moments_workspace_bytes", "bb_ppo_workspace_bytes", "bb_randperm",
                    "bb_randperm_workspace_bytes"]
     for sym in ppo:
         assert hasattr(lib, sym), f"libbball.so lacks {sym}"
