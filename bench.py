@@ -33,6 +33,7 @@ BYTES_PER_WORLD_STEP = 1872  # 56 in + 348 state read + 
 SEED = 1234
 LARGE_WORLDS = 1 << 20       # HBM-bound regime (working set 1.9 GB >> 126 MB L2)
 PREWARM_S = 0.5              # declared device pre-warm before the timed window (config.prewarm)
+DEPHASE_SPAN = 150           # steps: the shards of a rank are spread over this much of the episode cycle before anything is timed
 SPACER_US = 300              # a spin kernel of this length is queued ahead of the timed window while the host enqueues its K launches
 
 
@@ -43,8 +44,19 @@ def enqueue_spacer(torch, flush):
     try:
         torch.cuda._sleep(int(SPACER_US * 1e-6 * 1.9e9))
     except Exception:
+        if flush is None:
+            flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
         for _ in range(6):
             flush.zero_()
+
+
+def dephase_steps(R: int) -> int:
+    """Extra untimed steps per shard index.  Every world of every shard starts from the same spawn and the game's clocks run
+    in lock step, so shots, rebounds and resets come in waves (a step costs 1.0x on a quiet step, 1.6x in a wave, waves
+    48-96 steps apart: profiles/r02b_step_times_1m_200_steps.txt).  With all shards at the same phase a 20-launch window
+    lands on ONE phase of that cycle and reads 8.1 or 10.3 us per step by chance; with shard i advanced i x dephase_steps(R)
+    steps the window's launches sample the whole cycle -- the long-run mean, run after run."""
+    return max(7, -(-DEPHASE_SPAN // R))
 
 
 def measured_peak_gbs():
@@ -235,6 +247,10 @@ def rotating_rate(n, total_worlds, n_gpus, rank, local_rank, K, Wm, prewarm_s, s
     for s in range(acts.shape[0]):
         shards[s % R].fill_actions(SEED, seed_base + s, out=acts[s])
     calls = [[sh.sim.bind_step_with_actions(acts[b]) for b in range(acts.shape[0])] for sh in shards]
+    for j in range(R):                       # shards at different phases of the episode cycle (dephase_steps)
+        for s in range(j * dephase_steps(R)):
+            calls[j][s % acts.shape[0]]()
+        torch.cuda.synchronize()
     t0, i = time.perf_counter(), 0
     while i < 2 * R or time.perf_counter() - t0 < prewarm_s:
         calls[i % R][i % acts.shape[0]]()
@@ -248,7 +264,7 @@ def rotating_rate(n, total_worlds, n_gpus, rank, local_rank, K, Wm, prewarm_s, s
     if n_gpus > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    enqueue_spacer(torch, torch.empty(256 << 20, dtype=torch.uint8, device=dev))   # see run_engine: the K launches queue up behind it
+    enqueue_spacer(torch, None)   # see run_engine: the K launches queue up behind it
     e0.record()
     for s in range(K):
         calls[(first + s) % R][s % acts.shape[0]]()
@@ -257,10 +273,35 @@ def rotating_rate(n, total_worlds, n_gpus, rank, local_rank, K, Wm, prewarm_s, s
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if n_gpus > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    stream_ms = float(t.item())
+    # the same K steps as one CUDA-graph replay (run_engine's `value`): capture, one untimed replay, complete the shard cycle
+    first = (first + K) % R
+    g, side = torch.cuda.CUDAGraph(), torch.cuda.Stream(dev)
+    with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+        for s in range(K):
+            shards[(first + s) % R].sim.bind_step_with_actions(acts[s % acts.shape[0]])()
+    g.replay()
+    n_fill = (R - K % R) % R
+    while n_fill < Wm:
+        n_fill += R
+    for s in range(n_fill):
+        calls[(first + K + s) % R][s % acts.shape[0]]()
+    if n_gpus > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    enqueue_spacer(torch, None)
+    e0.record()
+    g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if n_gpus > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    del calls, shards
+    del calls, shards, g
     return {"value": total_worlds * K / (ms * 1e-3), "unit": UNIT, "worlds_per_gpu": n, "us_per_step": ms / K * 1e3, "shards_per_gpu": R,
-            "hbm_frac": n * BYTES_PER_WORLD_STEP / (ms / K * 1e-3) / 1e9 / measured_peak_gbs()[0]}
+            "hbm_frac": n * BYTES_PER_WORLD_STEP / (ms / K * 1e-3) / 1e9 / measured_peak_gbs()[0],
+            "stream_launches": {"value": total_worlds * K / (stream_ms * 1e-3), "us_per_step": stream_ms / K * 1e3}}
 
 
 def stress_rate(total_worlds, n_gpus, rank, local_rank, steps=100, warm=20):
@@ -360,6 +401,11 @@ def run_engine(args):
             bound[key] = shards[shard_idx].sim.bind_step_with_actions(actions[batch])
         bound[key]()
 
+    dephase = dephase_steps(R)
+    for i in range(R):                       # untimed: shard i sits i x dephase steps further into the episode cycle
+        for s in range(i * dephase):
+            launch(i, s % (K + Wm))
+        torch.cuda.synchronize()
     t_pw, n_pw = time.perf_counter(), 0
     while n_pw < 4 * R or time.perf_counter() - t_pw < PREWARM_S:
         launch(n_pw % R, n_pw % (K + Wm))
@@ -386,7 +432,43 @@ def run_engine(args):
         e1.record()
         barrier()
         wall = time.perf_counter() - wall0
-    gpu_launches = sum(sh.sim.launch_count() for sh in shards) - launches0
+    stream_launches = sum(sh.sim.launch_count() for sh in shards) - launches0
+    stream_dev_ms = float(e0.elapsed_time(e1))
+    t = torch.tensor([stream_dev_ms], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    stream_value = total_worlds * K / (float(t.item()) * 1e-3)
+
+    # ---------------------------------------------------------------- value: the same K cold-row steps as ONE CUDA graph launch
+    # A step kernel lasts ~8 us, so a loop of ordinary launches is bound by the stream's per-launch front-end cost
+    # (stream_launches above); a launch-bound inner loop belongs in a CUDA graph.  The K steps over the rotating shards are
+    # captured once (the engine's launches carry their programmatic-dependent-launch attribute into the graph's edges) and the
+    # timed window is ONE replay: K step kernels, each on the next shard's rows, which are as cold as above -- between two
+    # touches of a shard the other R - 1 shards (2.4 x L2) pass through the cache, in the warm-up below and across replays.
+    first = (first + K) % R
+    side = torch.cuda.Stream(dev)
+    gK = torch.cuda.CUDAGraph()
+    launches0 = sum(sh.sim.launch_count() for sh in shards)
+    with torch.cuda.graph(gK, stream=side, capture_error_mode="thread_local"):
+        for s in range(K):     # bound inside the capture: the closure keeps the capturing stream
+            shards[(first + s) % R].sim.bind_step_with_actions(actions[Wm + s])()
+    gpu_launches = sum(sh.sim.launch_count() for sh in shards) - launches0     # kernel nodes in the graph = launches per replay
+    assert gpu_launches == K, (gpu_launches, K)
+    gK.replay()                # untimed: instantiation / upload of the graph, and K more warm-up steps
+    n_fill = (R - K % R) % R   # ordinary launches over the shards the graph leaves out of this cycle, then whole cycles up to >= W
+    while n_fill < Wm:
+        n_fill += R
+    for s in range(n_fill):
+        launch((first + K + s) % R, s % (K + Wm))
+    barrier()
+    with sampler:
+        wall0 = time.perf_counter()
+        enqueue_spacer(torch, flush)
+        e0.record()
+        gK.replay()
+        e1.record()
+        barrier()
+        wall = time.perf_counter() - wall0
     dev_ms = float(e0.elapsed_time(e1))
     t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
     if world_size > 1:
@@ -616,10 +698,17 @@ def run_engine(args):
             "config": {"workload": workload_string(args.worlds_per_gpu, n_gpus),
                        "l2": f"inputs larger than L2: every launch advances the next of {R} independent {n}-world shards on this GPU "
                              f"({R * n * BYTES_PER_WORLD_STEP / 1e6:.0f} MB of rows per cycle against a {l2_bytes / 1e6:.0f} MB L2), so each of the K timed "
-                             "launches reads its rows from HBM; K launches back to back between one pair of CUDA events, enqueued "
-                             f"behind a {SPACER_US} us spin kernel so that the window is device time, not host enqueue pace",
-                       "prewarm": f"{n_pw} untimed launches of the same cycle ({PREWARM_S} s) before the W warm-up steps, so that the timed "
-                                  "window does not sit on the clock / launch-path ramp of an idle GPU",
+                             "launches reads its rows from HBM; the K step kernels are one CUDA-graph replay between one pair of CUDA "
+                             f"events, enqueued behind a {SPACER_US} us spin kernel so that the window is device time",
+                       "launch": f"one CUDA graph of the K = {K} step kernels (captured from the engine's ordinary bb_step_with_actions calls, "
+                                 "programmatic dependent launch edges), replayed once in the timed window; stream_launches = the same K "
+                                 "steps as K ordinary stream launches",
+                       "dephase": f"before anything is timed shard i is advanced i x {dephase} extra steps: the worlds' game clocks run in lock "
+                                  "step, so shots / resets come in waves (a step costs 1.0x to 1.6x depending on the phase); with the "
+                                  "shards spread over the cycle the K timed launches sample all of it instead of one phase by chance",
+                       "prewarm": f"{n_pw} untimed launches of the same cycle ({PREWARM_S} s), one untimed replay of the graph and "
+                                  f"{n_fill} ordinary launches (>= W, completing the shard cycle) before the timed window, so that it does "
+                                  "not sit on the clock / launch-path ramp of an idle GPU",
                        "parallelism": f"world-sharded x{n_gpus}, no collective in the step"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "path": e2e_path,
                     "what": "per step: action rows read from pinned host memory over PCIe, fused step, reward + done written back "
@@ -647,6 +736,9 @@ def run_engine(args):
                                      "what": "round 1's `value`: ONE isolated launch after a 256 MiB L2-flush memset, one event pair per step "
                                              "(max over ranks of the mean); null_floor_us = a 1-element torch kernel timed the same way on "
                                              "this box, i.e. the launch + event floor that number contains (informational)"},
+            "stream_launches": {"value": stream_value, "unit": UNIT, "us_per_step": stream_dev_ms / K * 1e3, "gpu_launches": int(stream_launches),
+                                "what": "the same K cold-row steps as K ordinary launches queued on the stream (round 2's earlier `value`): "
+                                        "carries the stream's per-launch cost that the graph replay avoids (informational)"},
             "l2_warm_graph": {"value": warm_value, "unit": UNIT,
                               "what": "same K steps replayed as one CUDA graph, no L2 flush (informational)"},
             "graph_step_n": {"value": step_n_value, "unit": UNIT,

@@ -78,6 +78,9 @@ struct StepParams {
     StepIo io;
     int64_t numWorlds;
     int prefetchBlocks;       /* > 0: block b pulls the state rows of block b + prefetchBlocks into L2 */
+    int prefetchSelf;         /* ahead of griddepcontrol.wait, pull this warp's own rows into L2: bit 0 state rows, bit 1 action rows */
+    int earlyTrigger;         /* 1: release the stream's next programmatic launch as soon as this grid has started (step chains
+                               * of one-warp blocks: the next grid's blocks sit resident at their griddepcontrol.wait) */
 };
 
 /* ------------------------------ obs image --------------------------------- *
@@ -405,8 +408,9 @@ BBD void store_world(const World &W, const StepParams &p, int64_t w)
  * lane c of the calling warp issues one cp.async.bulk.prefetch.L2 for column c.  By the time the
  * block that owns those worlds starts, its up-front loads would hit L2 instead of DRAM.  Tuning knob
  * only (BB_PREFETCH_BLOCKS): on B200 it costs more than it hides, see bb_create. */
-BBD void prefetch_state_rows(const StepParams &p, int64_t world0, int worlds, int lane)
+BBD void prefetch_state_rows(const StepParams &p, int64_t world0, int worlds, int lane, bool withActions = true)
 {
+    if (lane == 0 && !withActions) return;
     const Columns &C = p.col;
     const void *base = nullptr;
     int bpw = 0; /* bytes per world */
@@ -509,9 +513,17 @@ template <int kMaxT, bool kSync, int kWPR>
 __global__ void __launch_bounds__(kMaxT, kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_kernel(const __grid_constant__ StepParams p)
 {
     extern __shared__ float4 smem4[];
+    if (kMaxT == 32 && p.prefetchSelf) {
+        /* A block released early by its predecessor (earlyTrigger) sits here until that grid has drained.  L2 prefetches of
+         * the rows it is about to load cost nothing meanwhile and are safe before the wait: the L2 is the point of coherence,
+         * so a line the predecessor still writes is simply written in place; nothing is read into registers or L1. */
+        const int64_t w0 = ((int64_t)blockIdx.x * 32) >> 1;
+        if (w0 + kWorldsPerWarp <= p.numWorlds) prefetch_state_rows(p, w0, kWorldsPerWarp, threadIdx.x, (p.prefetchSelf & 2) != 0);
+    }
     /* programmatic dependent launch (bb_rollout): let the next kernel of the chain be scheduled early, and wait here for
      * the previous one to complete; both are no-ops for an ordinary launch */
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (kMaxT == 32 && p.earlyTrigger) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float4 *warpImg = smem4 + warp * kWPR * kImgWorld4;
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -754,7 +766,7 @@ struct bb_engine {
     void *colPtr[26];
     bb::StepParams params;
     cudaStream_t hostStream; /* bb_step_host / setters */
-    int blockThreads, phaseSync, prefetchBlocks, obsRound, pdlDefault;
+    int blockThreads, phaseSync, prefetchBlocks, obsRound, pdlDefault, pdlEarly, prefetchSelf;
     int64_t launches;
     /* bb_step_n: graph of stepGraphN step kernels */
     cudaGraphExec_t stepGraphExec;
@@ -885,7 +897,7 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), int blocks, int threads, size_t
 }
 
 int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, float *reward_out = nullptr,
-                float *done_out = nullptr, bool host_mapped = false, bool pdl = false, bool actions_u8 = false)
+                float *done_out = nullptr, bool host_mapped = false, bool pdl = false, bool actions_u8 = false, bool early = false)
 {
     bb::StepParams p = e->params;
     p.io.actionSrc = actions_dev;
@@ -900,6 +912,10 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
     const int wpr = e->obsRound;
     const int smem = bb::smem_bytes_for(threads, wpr);
     pdl = pdl && threads <= 128 && !e->phaseSync;
+    p.earlyTrigger = (pdl && early && threads == 32) ? 1 : 0;
+    p.prefetchSelf = 0;
+    if (pdl && threads == 32 && e->prefetchSelf && !host_mapped)
+        p.prefetchSelf = 1 | ((!actions_dev || ((uintptr_t)actions_dev & 15u) == 0) ? 2 : 0);
 #define BB_LAUNCH_STEP(MAXT, SYNC, WPR)                                                                          \
     do {                                                                                                         \
         if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_step_kernel<MAXT, SYNC, WPR>, blocks, threads, (size_t)smem, stream, true, p)); \
@@ -1009,6 +1025,21 @@ bb_engine *bb_create(const bb_config *cfg)
     pick_launch_shape(e->N, &e->blockThreads, &e->phaseSync, &e->obsRound);
     e->pdlDefault = 1;
     if (const char *s = getenv("BB_PDL")) e->pdlDefault = atoi(s) != 0;
+    {   /* Early release of the next programmatic launch (griddepcontrol.launch_dependents at the kernel's top): pays when this
+         * grid and the next one fit on the GPU together -- one-warp blocks, at most half of the 8 block slots per SM -- so the
+         * next step's blocks are resident at their griddepcontrol.wait when this one drains.  Same-box A/B (profiles r02i):
+         * 2048 worlds 9.4 -> 6.6 us per queued launch, 8192 worlds 10.0 -> 8.9 us in a graph; 16 384 worlds (1024 blocks,
+         * they no longer fit twice) 10.7 -> 11.1 us, hence the bound.  BB_PDL_EARLY=0/1 overrides. */
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.gpu_id);
+        const int64_t blocks = (e->N * 2 + e->blockThreads - 1) / e->blockThreads;
+        e->pdlEarly = (e->blockThreads == 32 && blocks <= 4 * (int64_t)sms) ? 1 : 0;
+        if (const char *s = getenv("BB_PDL_EARLY")) e->pdlEarly = atoi(s) != 0;
+        /* one-warp blocks prefetch their own rows into L2 ahead of griddepcontrol.wait (bb_step_kernel): 8192 cold-row worlds
+         * 9.43 -> 9.11 us per step in a graph, 9.74 -> 9.34 us as queued launches (same-box A/B, profiles r02i) */
+        e->prefetchSelf = 1;
+        if (const char *s = getenv("BB_PREFETCH_SELF")) e->prefetchSelf = atoi(s) != 0;
+    }
     if (!check_sqrt_thresholds()) {
         set_error("bb_create: the squared-length thresholds of bb_world.cuh do not match this host's sqrtf");
         cudaFree(e->slab);
@@ -1068,19 +1099,26 @@ void bb_destroy(bb_engine *e)
 /* Ordinary (uncaptured) step launches carry the programmatic-stream-serialization attribute: the kernel's blocks may be
  * scheduled while the previous kernel of the stream drains, and wait at their first instruction (griddepcontrol.wait)
  * until that kernel has completed and flushed -- whatever kernel it is -- so only launch latency overlaps, never data.
- * Not inside a foreign stream capture (a captured first node has no predecessor to hang the edge on); BB_PDL=0 disables. */
+ * Inside a caller's stream capture the edge needs a kernel node to hang on: taken only when the capture's single pending
+ * dependency is a kernel node (a captured first node, or one behind a memcpy / event node, gets a plain edge).  BB_PDL=0 disables. */
 static bool pdl_for(bb_engine *e, cudaStream_t s)
 {
     if (!e->pdlDefault) return false;
     cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(s, &st) != cudaSuccess) { cudaGetLastError(); return false; }
-    return st == cudaStreamCaptureStatusNone;
+    const cudaGraphNode_t *deps = nullptr;
+    size_t numDeps = 0;
+    if (cudaStreamGetCaptureInfo(s, &st, nullptr, nullptr, &deps, &numDeps) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (st == cudaStreamCaptureStatusNone) return true;
+    if (st != cudaStreamCaptureStatusActive || numDeps != 1 || !deps) return false;
+    cudaGraphNodeType ty;
+    if (cudaGraphNodeGetType(deps[0], &ty) != cudaSuccess) { cudaGetLastError(); return false; }
+    return ty == cudaGraphNodeTypeKernel;
 }
 
 int bb_step(bb_engine *e, void *cuda_stream)
 {
     if (e->serving) { set_error("bb_step: the persistent server is running (bb_serve_end first)"); return -1; }
-    return launch_step(e, nullptr, (cudaStream_t)cuda_stream, nullptr, nullptr, false, pdl_for(e, (cudaStream_t)cuda_stream));
+    return launch_step(e, nullptr, (cudaStream_t)cuda_stream, nullptr, nullptr, false, pdl_for(e, (cudaStream_t)cuda_stream), false, e->pdlEarly != 0);
 }
 
 int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream)
@@ -1096,7 +1134,7 @@ int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream)
             const bool pdl = attempt == 0; /* second attempt: plain edges, should a driver refuse programmatic ones in capture */
             BB_CUDA_OK(cudaStreamBeginCapture(e->captureStream, cudaStreamCaptureModeThreadLocal));
             int rc = 0;
-            for (int32_t i = 0; i < n && rc == 0; i++) rc = launch_step(e, nullptr, e->captureStream, nullptr, nullptr, false, pdl && i > 0);
+            for (int32_t i = 0; i < n && rc == 0; i++) rc = launch_step(e, nullptr, e->captureStream, nullptr, nullptr, false, pdl && i > 0, false, e->pdlEarly != 0);
             cudaError_t err = cudaStreamEndCapture(e->captureStream, &graph);
             if (rc == 0 && err == cudaSuccess && cudaGraphInstantiate(&e->stepGraphExec, graph, 0) != cudaSuccess) e->stepGraphExec = nullptr;
             if (graph) { cudaGraphDestroy(graph); graph = nullptr; }
@@ -1114,7 +1152,7 @@ int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream)
 int bb_step_with_actions(bb_engine *e, const int32_t *actions_dev, void *cuda_stream)
 {
     if (e->serving) { set_error("bb_step_with_actions: the persistent server is running (bb_serve_end first)"); return -1; }
-    return launch_step(e, actions_dev, (cudaStream_t)cuda_stream, nullptr, nullptr, false, pdl_for(e, (cudaStream_t)cuda_stream));
+    return launch_step(e, actions_dev, (cudaStream_t)cuda_stream, nullptr, nullptr, false, pdl_for(e, (cudaStream_t)cuda_stream), false, e->pdlEarly != 0);
 }
 
 /* Device alias of a pinned (page-locked, mapped) host buffer, or NULL for pageable memory.
@@ -1479,6 +1517,9 @@ int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, 
     e->launches++;
     BB_CUDA_OK(cudaGetLastError());
     static const bool pdl = [] { const char *s = getenv("BB_ROLLOUT_PDL"); return !(s && atoi(s) == 0); }();
+    /* bit 0: the step kernel releases the policy kernel early (its blocks stage the weights while the step runs: rollout
+     * 0.715 -> 0.689 ms); bit 1: the policy kernel releases the step kernel early (measured slower, 0.746 ms: off) */
+    static const int early = [] { const char *s = getenv("BB_ROLLOUT_EARLY"); return s ? atoi(s) : 1; }();
     if (launch_step(e, nullptr, st) != 0) return -1;
     for (int t = 0; t <= T; t++) {
         bb::PolicyIo io{};
@@ -1502,6 +1543,7 @@ int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, 
         } else {
             io.resetCol = C.reset; /* env.py:182 resets.fill_(0) */
         }
+        io.earlyTrigger = (pdl && (early & 2) && !frozen) ? 1 : 0;
         if (launch_policy(trainee, io, st, pdl) != 0) return -1;
         e->launches++;
         if (t == T) break;
@@ -1511,10 +1553,11 @@ int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, 
             fo.obs = C.obs + other * BB_OBS_DIM; fo.obsStride = 2 * BB_OBS_DIM; fo.n = n; fo.rowOffset = world_offset;
             fo.stochastic = 1; fo.seed = seed; fo.draw = 0x80000000u + draw_base + (uint32_t)t;
             fo.actionsOut = C.action + other * 6; fo.actionStride = 12;
+            fo.earlyTrigger = (pdl && (early & 2)) ? 1 : 0;
             if (launch_policy(frozen, fo, st, pdl) != 0) return -1;
             e->launches++;
         }
-        if (launch_step(e, nullptr, st, nullptr, nullptr, false, pdl) != 0) return -1;
+        if (launch_step(e, nullptr, st, nullptr, nullptr, false, pdl, false, (early & 1) != 0) != 0) return -1;
     }
     return 0;
 }

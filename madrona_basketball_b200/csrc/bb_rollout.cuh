@@ -26,6 +26,7 @@ struct PolicyIo {
     const float *obs;
     int64_t obsStride, n, rowOffset;
     int stochastic, evaluateOnly;
+    int earlyTrigger;         /* 1: griddepcontrol.launch_dependents once this grid runs (the following step kernel sits resident) */
     uint32_t seed, draw;
     int32_t *actionsOut;
     int64_t actionStride;
@@ -197,6 +198,7 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
     /* programmatic dependent launch (bb_rollout): the weights above do not depend on the step kernel that precedes this
      * launch in the stream; everything below does.  No-ops for an ordinary launch. */
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (io.earlyTrigger) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     __syncthreads();
 
     const int64_t rowStride = (int64_t)gridDim.x * kRowsPerBlock;

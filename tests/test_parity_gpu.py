@@ -425,3 +425,33 @@ def test_step_n_graph_replay_equals_separate_steps(n):
         torch.cuda.synchronize()
         assert_states_equal(engine_state(b), engine_state(a), f"step_n N={n} k={k}")
     assert a.launch_count() == b.launch_count()
+
+
+@pytest.mark.parametrize("n", [300, 8192])
+def test_caller_captured_graph_of_steps_equals_separate_steps(n):
+    """A caller's own stream capture around ordinary step calls (what bench.py's `value` replays): step_with_actions of two
+    engines interleaved inside torch.cuda.graph -- the second and later kernel nodes take programmatic-dependent-launch
+    edges, the first a plain one -- replayed twice == the same steps launched one by one, bit for bit."""
+    import torch
+
+    k = 6
+    eng = [make_engine(n) for _ in range(4)]      # 0, 1: stepped by the graph; 2, 3: their twins, ordinary launches
+    acts = torch.empty((k, n, 2, 6), dtype=torch.int32, device="cuda")
+    for s in range(k):
+        eng[0].fill_actions(SEED, s, out=acts[s])
+    for sim in eng:
+        for s in range(3):
+            sim.step_with_actions(acts[s])
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):
+        for s in range(k):
+            eng[s % 2].bind_step_with_actions(acts[s])()
+    for _ in range(2):
+        graph.replay()
+        for s in range(k):
+            eng[2 + s % 2].step_with_actions(acts[s])
+    torch.cuda.synchronize()
+    for i in (0, 1):
+        assert_states_equal(engine_state(eng[i]), engine_state(eng[2 + i]), f"captured steps N={n} engine {i}")

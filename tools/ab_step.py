@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """A/B of two builds of libbball.so on the SAME box (box-to-box spread is ~3 %, more than most kernel changes):
     python tools/ab_step.py libA.so[:ENV=VAL,ENV2=VAL2] libB.so[:...] [worlds ...]
-For each library (alternating, 3 rounds): K = 200 queued launches over rotating cold shards (bench.py's `value`
-measurement) with random actions, and bb_step_n graph replay; prints microseconds per step."""
+For each library (alternating, 3 rounds): K = 200 steps over rotating cold shards with random actions (bench.py's `value`:
+one CUDA-graph replay; and the same as queued stream launches), and bb_step_n graph replay; prints microseconds per step."""
 import json, os, subprocess, sys
 
 CHILD = r'''
@@ -18,7 +18,8 @@ for n in [int(a) for a in sys.argv[1:]]:
     sh.sim.step_n(50); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(); sh.sim.step_n(200); e1.record(); torch.cuda.synchronize()
-    out[n] = {"cold_us": round(r["us_per_step"], 3), "graph_us": round(e0.elapsed_time(e1) / 200 * 1e3, 3)}
+    out[n] = {"cold_graph_us": round(r["us_per_step"], 3), "cold_stream_us": round(r["stream_launches"]["us_per_step"], 3),
+              "step_n_us": round(e0.elapsed_time(e1) / 200 * 1e3, 3)}
 print(json.dumps(out))
 '''
 
