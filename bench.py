@@ -540,6 +540,22 @@ def run_engine(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     step_n_value = total_worlds * K / (float(t.item()) * 1e-3)
 
+    # ---------------------------------------------------------------- fused K steps with K action batches (informational)
+    # bb_step_n_with_actions: the same K random-action batches as `value`, but taken by ONE launch of the looping kernel
+    # on one 8192-world shard (BASELINE.md section 3's "fused-K-steps kernel"); the shard's rows stay in L1 / L2 between steps.
+    fused_acts = actions[Wm:Wm + K].contiguous()
+    sim.step_n_with_actions(fused_acts)
+    barrier()
+    with sampler:
+        e0.record()
+        sim.step_n_with_actions(fused_acts)
+        e1.record()
+        barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world_size > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    fused_k_value = total_worlds * K / (float(t.item()) * 1e-3)
+
     # ---------------------------------------------------------------- e2e: host buffers through the C ABI
     # Every step takes its own action batch from pinned host memory (a ring of pre-filled pinned
     # buffers: the producer is not what is measured) and returns reward + done into pinned host memory.
@@ -664,6 +680,12 @@ def run_engine(args):
             # configs[2] as STRONG scaling: 65 536 worlds / N per GPU (the weak headline above matches it only at N = 8)
             extras["strong_65536"] = rotating_rate(65536 // n_gpus, 65536, n_gpus, rank, local_rank, K, Wm, 0.2, seed_base=1000)
             extras["strong_65536"]["what"] = "BASELINE configs[2]: 65 536 worlds sharded over the N GPUs, same measurement as `value`"
+        if n_gpus == 1:
+            # the metric's second size ("at 8192/64K worlds") on ONE GPU, measured exactly like `value`: 65 536 worlds per launch,
+            # K launches as one graph replay over rotating shards (rows cold), with its HBM fraction
+            extras["worlds_65536"] = rotating_rate(65536, 65536, 1, rank, local_rank, K, Wm, 0.2, seed_base=1000)
+            extras["worlds_65536"]["what"] = ("65 536 worlds on one GPU, same kernel and same measurement as `value` (K launches over "
+                                              "rotating shards larger than L2); hbm_frac = 1872 B x 65 536 / time per launch / measured peak")
         if n_gpus == 8:
             extras["stress_2p20"] = stress_rate(1 << 20, n_gpus, rank, local_rank)
         # configs[3]: data-parallel PPO (scripts/ppo.py:226-376 one process per GPU), gradient all-reduce with NCCL (default) and
@@ -742,8 +764,12 @@ def run_engine(args):
             "l2_warm_graph": {"value": warm_value, "unit": UNIT,
                               "what": "same K steps replayed as one CUDA graph, no L2 flush (informational)"},
             "graph_step_n": {"value": step_n_value, "unit": UNIT,
-                             "what": "K steps through bb_step_n: one CUDA-graph launch, programmatic dependent launch between the step "
-                                     "kernels, device-resident actions (scripts/run.py loop), no L2 flush (informational)"},
+                             "what": "K steps through bb_step_n: ONE launch of the looping kernel (every warp takes its 16 worlds through "
+                                     "the K steps in a row; round 1 / BB_STEP_N_GRAPH=1: a CUDA graph of K step kernels), device-resident "
+                                     "actions (scripts/run.py loop), no L2 flush (informational)"},
+            "fused_k_steps": {"value": fused_k_value, "unit": UNIT,
+                              "what": "K steps with K random-action batches through bb_step_n_with_actions: one launch of the looping "
+                                      "kernel on one shard, rows L1 / L2 resident between steps (informational)"},
             "wall_s_timed_region": wall,
         }
         line.update(extras)

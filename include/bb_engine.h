@@ -92,11 +92,18 @@ void bb_destroy(bb_engine *e);
 int bb_step(bb_engine *e, void *cuda_stream);
 
 /* n consecutive Manager::step() calls with no host work in between (the loop of scripts/run.py:16-20, or the
- * reference's own `for _ in range(n): sim.step()`), as ONE CUDA-graph launch: the n step kernels are captured once per
- * n (programmatic-dependent-launch edges between consecutive steps: blocks of step k+1 start as blocks of step k
- * retire and wait for its completion before touching state) and the instantiated graph is replayed on `cuda_stream`.
- * The Action column is whatever the caller and hardCodeDefenseSystem left in it, exactly as with n bb_step calls. */
+ * reference's own `for _ in range(n): sim.step()`), as ONE kernel launch on `cuda_stream`: worlds never interact, so each
+ * warp takes its 16 worlds through all n steps in a row (bb_step_loop_kernel: no launch, drain or grid dependency between
+ * steps; every step still writes its full state, observation rows, reward and done).  Results are bit-identical to n bb_step
+ * calls.  The Action column is whatever the caller and hardCodeDefenseSystem left in it, exactly as with n bb_step calls.
+ * BB_STEP_N_GRAPH=1 (or a tuning launch shape without a looping instantiation) selects round 1's form instead: the n step
+ * kernels captured once per n into a CUDA graph with programmatic-dependent-launch edges, replayed with one graph launch. */
 int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream);
+
+/* bb_step_n with a recorded action stream: step s takes its Action rows from actions_dev + s * N*2*6 (device, i32
+ * [n,N,2,6]) -- n x (`action_tensor.copy_(actions[s]); step()`, scripts/env.py:143,155) as one launch of the looping
+ * kernel.  Extension; bit-identical to n bb_step_with_actions calls. */
+int bb_step_n_with_actions(bb_engine *e, int32_t n, const int32_t *actions_dev, void *cuda_stream);
 
 /* bb_step, but Action is first taken from `actions_dev` (device, i32 [N,2,6]) —
  * the fused equivalent of `action_tensor.copy_(actions); step()`

@@ -13,7 +13,7 @@ SYMBOLS = [
     "bb_create", "bb_destroy", "bb_step", "bb_step_n", "bb_step_with_actions", "bb_step_host", "bb_export",
     "bb_set_action", "bb_trigger_reset", "bb_fill_actions", "bb_checksum", "bb_launch_count",
     "bb_num_worlds", "bb_last_error", "bb_math_eval", "bb_serve_begin", "bb_serve_step", "bb_serve_end",
-    "bb_serve_last_gpu_ns", "bb_step_host_u8", "bb_serve_step_u8", "bb_serve_last_marks",
+    "bb_serve_last_gpu_ns", "bb_step_host_u8", "bb_serve_step_u8", "bb_serve_last_marks", "bb_step_n_with_actions",
 ]
 
 
@@ -52,6 +52,8 @@ def load() -> ctypes.CDLL:
     lib.bb_step.argtypes = [vp, vp]
     lib.bb_step_n.restype = ctypes.c_int
     lib.bb_step_n.argtypes = [vp, i32, vp]
+    lib.bb_step_n_with_actions.restype = ctypes.c_int
+    lib.bb_step_n_with_actions.argtypes = [vp, i32, vp, vp]
     lib.bb_step_with_actions.restype = ctypes.c_int
     lib.bb_step_with_actions.argtypes = [vp, vp, vp]
     lib.bb_step_host.restype = ctypes.c_int

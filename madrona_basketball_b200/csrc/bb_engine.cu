@@ -537,6 +537,32 @@ __global__ void __launch_bounds__(kMaxT, kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 1
     step_tile<kSync, kWPR>(p, p.io, warpImg, warpWorld0, lane);
 }
 
+/* n x Manager::step() in ONE launch (bb_step_n, bb_step_n_with_actions): worlds never interact and a tile's rows are read and
+ * written by its own warp only, so the warp simply takes n steps in a row -- no grid-wide dependency, no launch, no drain and
+ * no cold instruction fetch between steps, and the tile's rows stay in this SM's L1 / the L2 from one step to the next (every
+ * step still stores its full state, observation rows, reward and done, exactly like n launches: the columns ARE the exported
+ * tensors).  Between two steps the warp's stores are ordered before its partner lanes' loads by __syncwarp() (with phase
+ * barriers: the block's).  actionStride != 0: step s reads its Action rows from io.actionSrc + s * actionStride (int32
+ * elements), a recorded action stream [n,N,2,6]; otherwise every step reads the Action column the previous one left, like
+ * scripts/run.py:16-20. */
+template <int kMaxT, bool kSync, int kWPR>
+__global__ void __launch_bounds__(kMaxT, kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_loop_kernel(const __grid_constant__ StepParams p, int32_t n, int64_t actionStride)
+{
+    extern __shared__ float4 smem4[];
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float4 *warpImg = smem4 + warp * kWPR * kImgWorld4;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t warpWorld0 = (t - lane) >> 1;
+    if (!kSync && warpWorld0 >= p.numWorlds) return;
+    StepIo io = p.io;
+    for (int32_t s = 0; s < n; s++) {
+        step_tile<kSync, kWPR>(p, io, warpImg, warpWorld0, lane);
+        __syncwarp(); /* this step's stores (state rows, and the image the observation rows were emitted from) before the next step's loads */
+        if (io.actionSrc) io.actionSrc += actionStride;
+    }
+}
+
 /* ------------------------------ persistent server -------------------------- *
  * Host-driven stepping without a kernel launch or a stream wait per step (bb_serve_*): the kernel
  * stays resident, block 0 polls a doorbell in mapped pinned host memory, every block then runs
@@ -552,6 +578,8 @@ struct ServeHostCtl { /* mapped pinned host memory */
      * wanted tag, so one poll (one PCIe round trip) fetches doorbell and buffers together.
      * word[0] == kServeExitWord: leave. */
     unsigned long long word[4];
+    unsigned long long pad0[4]; /* the doorbell (host writes, device polls) and the completion word (device writes, host
+                                 * spins) sit on different 64-byte lines */
     int32_t complete;        /* device -> host: last completed sequence number */
     int32_t alive;           /* device -> host: 1 while the server runs */
     unsigned long long tSeen, tDone; /* %globaltimer when block 0 saw the doorbell / the last block finished (tuning) */
@@ -611,7 +639,13 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
                 }
                 tSeen = global_timer_ns();
                 if (marks) { hc->mark[0] = tSeen; hc->tSeen = tSeen; }
-                asm volatile("fence.acq_rel.sys;" ::: "memory"); /* acquire: the host's action rows precede its doorbell */
+                /* acquire: the host's action rows precede its doorbell.  A relaxed load followed by an ACQUIRE fence is the
+                 * acquire pattern of the PTX memory model; it compiles to CCTL.IVALL (drop this SM's L1 lines).  The acq_rel
+                 * fence used before (flag bit 3 brings it back for A/B runs) adds MEMBAR.ALL.SYS -- the release half, which waits
+                 * for a PCIe round trip although this thread has written nothing the host is waiting for: 17.8 -> 16.4 us per
+                 * served step with packed rows, 23.4 -> 22.0 with int32 rows (profiles/r02j_ab_serve_fences.txt). */
+                if (flags & 8) asm volatile("fence.acq_rel.sys;" ::: "memory");
+                else asm volatile("fence.acquire.sys;" ::: "memory");
                 if (marks) hc->mark[1] = global_timer_ns();
                 if (got != kServeExit) {
                     dc->io.actionSrc = (const int32_t *)(w0 & kServePtrMask); dc->io.rewardOut = (float *)(w1 & kServePtrMask);
@@ -645,8 +679,10 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
         if (threadIdx.x == 0) {
             const uint64_t tTile = marks ? global_timer_ns() : 0;
             if (marks && blockIdx.x == 0) hc->mark[4] = tTile;
-            __threadfence(); /* release (gpu scope): this block's writes before the count; the last block's
-                              * system-scope release below is cumulative over everything it has observed */
+            /* release (gpu scope): this block's writes before the count; the last block's system-scope release below is
+             * cumulative over everything it has observed.  (A system-scope fence in every block, so that the last block's
+             * release finds the host writes already performed, was measured: 16.5 -> 22.8 us per step.) */
+            __threadfence();
             const unsigned old = atomicAdd(&dc->doneCount, 1u);
             if (old == gridDim.x - 1) { /* last block of this step */
                 dc->doneCount = 0;      /* nobody touches it again before the host rings the next doorbell */
@@ -766,7 +802,7 @@ struct bb_engine {
     void *colPtr[26];
     bb::StepParams params;
     cudaStream_t hostStream; /* bb_step_host / setters */
-    int blockThreads, phaseSync, prefetchBlocks, obsRound, pdlDefault, pdlEarly, prefetchSelf;
+    int blockThreads, phaseSync, prefetchBlocks, obsRound, pdlDefault, pdlEarly, prefetchSelf, stepLoop;
     int64_t launches;
     /* bb_step_n: graph of stepGraphN step kernels */
     cudaGraphExec_t stepGraphExec;
@@ -896,8 +932,11 @@ cudaError_t launch_pdl(void (*kernel)(KArgs...), int blocks, int threads, size_t
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
 }
 
+/* loop_n > 0: ONE launch of bb_step_loop_kernel taking loop_n steps (action rows of step s at actions_dev + s * action_stride);
+ * returns 1 without launching when the engine's launch shape has no looping instantiation (tuning overrides) */
 int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, float *reward_out = nullptr,
-                float *done_out = nullptr, bool host_mapped = false, bool pdl = false, bool actions_u8 = false, bool early = false)
+                float *done_out = nullptr, bool host_mapped = false, bool pdl = false, bool actions_u8 = false, bool early = false,
+                int32_t loop_n = 0, int64_t action_stride = 0)
 {
     bb::StepParams p = e->params;
     p.io.actionSrc = actions_dev;
@@ -924,6 +963,22 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
 #ifndef BB_NO_T32
 #define BB_NO_T32 0
 #endif
+    if (loop_n > 0) {
+        p.earlyTrigger = 0; p.prefetchSelf = 0; p.prefetchBlocks = 0;
+#define BB_LAUNCH_LOOP(MAXT, SYNC, WPR)                                                                          \
+    do {                                                                                                         \
+        if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_step_loop_kernel<MAXT, SYNC, WPR>, blocks, threads, (size_t)smem, stream, true, p, loop_n, action_stride)); \
+        else bb::bb_step_loop_kernel<MAXT, SYNC, WPR><<<blocks, threads, smem, stream>>>(p, loop_n, action_stride); \
+    } while (0)
+        if (!BB_NO_T32 && threads == 32 && wpr == 16) BB_LAUNCH_LOOP(32, false, 16);
+        else if (threads <= 128 && !e->phaseSync && wpr == 16) BB_LAUNCH_LOOP(128, false, 16);
+        else if (threads <= 128 && e->phaseSync && wpr == 8) BB_LAUNCH_LOOP(128, true, 8);
+        else return 1;
+#undef BB_LAUNCH_LOOP
+        e->launches += loop_n; /* passes of the step code over every world */
+        BB_CUDA_OK(cudaGetLastError());
+        return 0;
+    }
     if (!BB_NO_T32 && threads == 32 && wpr == 16) { /* the latency-bound shape: one-warp blocks, no register cap worth having */
         BB_LAUNCH_STEP(32, false, 16);
     } else if (threads <= 128) {
@@ -1058,7 +1113,11 @@ bb_engine *bb_create(const bb_config *cfg)
         cudaFuncSetAttribute(bb::bb_step_kernel<128, false, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
         cudaFuncSetAttribute(bb::bb_step_kernel<512, true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
         cudaFuncSetAttribute(bb::bb_step_kernel<512, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_step_loop_kernel<128, true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_step_loop_kernel<128, false, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
     }
+    e->stepLoop = 1; /* bb_step_n = one launch of the looping kernel */
+    if (const char *s = getenv("BB_STEP_N_GRAPH")) e->stepLoop = atoi(s) != 0 ? 0 : 1;
     if (cudaStreamCreateWithFlags(&e->hostStream, cudaStreamNonBlocking) != cudaSuccess) {
         set_error("bb_create: cudaStreamCreate failed");
         cudaFree(e->slab);
@@ -1125,6 +1184,10 @@ int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream)
 {
     if (n <= 0) return 0;
     if (e->serving) { set_error("bb_step_n: the persistent server is running (bb_serve_end first)"); return -1; }
+    if (e->stepLoop) { /* one launch of the looping kernel; BB_STEP_N_GRAPH=1 keeps the graph of n launches below */
+        const int rc = launch_step(e, nullptr, (cudaStream_t)cuda_stream, nullptr, nullptr, false, pdl_for(e, (cudaStream_t)cuda_stream), false, false, n, 0);
+        if (rc <= 0) return rc;
+    }
     if (!e->stepGraphExec || e->stepGraphN != n) {
         if (e->stepGraphExec) { cudaGraphExecDestroy(e->stepGraphExec); e->stepGraphExec = nullptr; }
         if (!e->captureStream) BB_CUDA_OK(cudaStreamCreateWithFlags(&e->captureStream, cudaStreamNonBlocking));
@@ -1146,6 +1209,22 @@ int bb_step_n(bb_engine *e, int32_t n, void *cuda_stream)
     }
     BB_CUDA_OK(cudaGraphLaunch(e->stepGraphExec, (cudaStream_t)cuda_stream));
     e->launches += n;
+    return 0;
+}
+
+int bb_step_n_with_actions(bb_engine *e, int32_t n, const int32_t *actions_dev, void *cuda_stream)
+{
+    if (n <= 0) return 0;
+    if (e->serving) { set_error("bb_step_n_with_actions: the persistent server is running (bb_serve_end first)"); return -1; }
+    if (!actions_dev) { set_error("bb_step_n_with_actions: actions_dev is NULL"); return -1; }
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    const int64_t stride = e->N * 12; /* int32 elements per step */
+    if (e->stepLoop) {
+        const int rc = launch_step(e, actions_dev, s, nullptr, nullptr, false, pdl_for(e, s), false, false, n, stride);
+        if (rc <= 0) return rc;
+    }
+    for (int32_t i = 0; i < n; i++) /* launch shapes without a looping instantiation: n ordinary launches */
+        if (launch_step(e, actions_dev + (int64_t)i * stride, s, nullptr, nullptr, false, pdl_for(e, s), false, e->pdlEarly != 0) != 0) return -1;
     return 0;
 }
 
@@ -1456,6 +1535,15 @@ static int policy_ok(const bb_policy *p, const char *who)
     return 0;
 }
 
+/* BB_POLICY_UMMA=1 (read once) selects the tcgen05 policy kernel; BB_POLICY_UMMA_FORCE=0/1 overrides it for as long as it is
+ * set (read per call: the tests run both kernels in one process) */
+static bool policy_uses_umma()
+{
+    static const int dflt = [] { const char *s = getenv("BB_POLICY_UMMA"); return (s && atoi(s) != 0) ? 1 : 0; }();
+    if (const char *s = getenv("BB_POLICY_UMMA_FORCE")) return atoi(s) != 0;
+    return dflt != 0;
+}
+
 static int launch_policy(const bb_policy *pol, const bb::PolicyIo &io, cudaStream_t stream, bool pdl = false)
 {
     if (io.n <= 0) return 0;
@@ -1463,10 +1551,7 @@ static int launch_policy(const bb_policy *pol, const bb::PolicyIo &io, cudaStrea
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     {   /* BB_POLICY_UMMA=1: the tcgen05 / TMEM kernel (csrc/bb_umma.cuh): 128 rows per CTA, one CTA per SM */
-        static int useUmma = -1;
-        if (useUmma < 0) { const char *s = getenv("BB_POLICY_UMMA"); useUmma = (s && atoi(s) != 0) ? 1 : 0; }
-        if (const char *s = getenv("BB_POLICY_UMMA_FORCE")) useUmma = atoi(s) != 0; /* tests switch per call */
-        if (useUmma) {
+        if (policy_uses_umma()) {
             static bool attr = false;
             if (!attr) {
                 BB_CUDA_OK(cudaFuncSetAttribute(bb::bb_policy_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bb::kUmSmemBytes));
@@ -1512,6 +1597,35 @@ int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, 
     const bb::Columns &C = e->params.col;
     const int64_t n = e->N;
     const int T = buf->horizon;
+    /* Default: the whole rollout as ONE launch of bb_rollout_loop_kernel (every warp takes its 16 worlds through env.reset() and
+     * the T x { policy rows; step } in a row).  BB_ROLLOUT_LOOP=0: round 2's chain of 2-3 kernels per step below. */
+    const char *loopEnv = getenv("BB_ROLLOUT_LOOP"); /* read per call: the tests run both forms in one process */
+    bool loop = !(loopEnv && atoi(loopEnv) == 0) && !policy_uses_umma(); /* the looping kernel carries the mma.sync policy rows */
+    const int64_t tiles = (n + bb::kWorldsPerWarp - 1) / bb::kWorldsPerWarp;
+    const size_t loopSmem = bb::rollout_loop_smem_bytes(frozen != nullptr);
+    if (loop) { /* only when every block of the looping kernel is resident at once (see the kernel) */
+        static bool attr = false;
+        if (!attr) {
+            BB_CUDA_OK(cudaFuncSetAttribute(bb::bb_rollout_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bb::rollout_loop_smem_bytes(true)));
+            attr = true;
+        }
+        int perSm = 0, sms = 148;
+        BB_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, bb::bb_rollout_loop_kernel, bb::kLoopWarps * 32, loopSmem));
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.gpu_id);
+        if (tiles > (int64_t)perSm * sms && !(loopEnv && atoi(loopEnv) == 2)) loop = false; /* BB_ROLLOUT_LOOP=2 forces it (tests, A/B) */
+    }
+    if (loop) {
+        bb::RolloutLoop rl{};
+        rl.buf = *buf; rl.agentIdx = agent_idx; rl.hasFrozen = frozen ? 1 : 0;
+        rl.seed = seed; rl.drawBase = draw_base; rl.worldOffset = world_offset;
+        bb::StepParams p = e->params;
+        p.io = bb::StepIo{nullptr, nullptr, nullptr, nullptr, 0, 0};
+        p.prefetchBlocks = 0; p.prefetchSelf = 0; p.earlyTrigger = 0;
+        BB_CUDA_OK(launch_pdl(bb::bb_rollout_loop_kernel, (int)tiles, bb::kLoopWarps * 32, loopSmem, st, pdl_for(e, st), p, *trainee, frozen ? *frozen : *trainee, rl));
+        e->launches += T + 1; /* passes of the step code over every world */
+        BB_CUDA_OK(cudaGetLastError());
+        return 0;
+    }
     /* env.reset(), env.py:178-185 */
     bb::bb_reset_prologue_kernel<<<(int)((n + 255) / 256), 256, 0, st>>>(C.reset, C.action, n, agent_idx);
     e->launches++;

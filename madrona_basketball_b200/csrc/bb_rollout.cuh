@@ -59,15 +59,17 @@ constexpr int kW1Stride = BB_OBS_DIM + 4;   /* 132: rows q, q+1, .. land 4 banks
 constexpr int kW2Stride = kH + 4;           /* 36 */
 constexpr int kHeadPerThread = kHeads / 4;  /* 5 */
 
-struct __align__(16) PolicySmem {
+template <int kRows>
+struct __align__(16) PolicySmemT {
     float w1[kH][kW1Stride];
     float w2[kH][kW2Stride];
     float wh[kHeads][kW2Stride];            /* rows 0..18 actor, row 19 critic */
-    float hid[kRowsPerBlock][kW2Stride];    /* a row's hidden vector (private to its quad) */
-    float out[kRowsPerBlock][kHeads + 4];   /* a row's 19 logits + value */
+    float hid[kRows][kW2Stride];            /* a row's hidden vector (private to its quad) */
+    float out[kRows][kHeads + 4];           /* a row's 19 logits + value */
     float mean[BB_OBS_DIM], inv[BB_OBS_DIM];
     float b1[kH], g1[kH], e1[kH], b2[kH], g2[kH], e2[kH], bh[kHeads];
 };
+using PolicySmem = PolicySmemT<kRowsPerBlock>;
 
 BBD float quad_sum(float v)
 {
@@ -166,6 +168,191 @@ __device__ __constant__ int kBucketOff[BB_NUM_ACTION_DIMS] = {0, 2, 10, 13, 15, 
 __device__ __constant__ int kBucketCnt[BB_NUM_ACTION_DIMS] = {2, 8, 3, 2, 2, 2};
 __device__ __constant__ int kQuadBuckets[4][2] = {{0, 2}, {1, -1}, {3, 4}, {5, -1}};
 
+/* Agent.forward + sampling + rollout bookkeeping for the 8 rows rw0 .. rw0 + 7 on the calling warp (quad (rb & 7) takes row
+ * rw0 + (rb & 7); rb = the quad's row slot in S.hid / S.out; all 32 lanes must call it).  The body of bb_policy_kernel's row
+ * loop, shared with bb_rollout_loop_kernel: the same instructions in the same order, hence the same bits. */
+template <class Smem>
+BBD void policy_rows8(const bb_policy &P, Smem &S, const PolicyIo &io, int64_t rw0, int rb, int q, int lane)
+{
+    const int H = P.hidden;
+    const int64_t rr = rw0 + (rb & 7);
+    const bool valid = rr < io.n;
+    const int64_t r = valid ? rr : io.n - 1; /* tail quads shadow the last row and never store */
+    /* ---- backbone.0: observation normaliser (agent.py:27-39) fused into Linear(128,H) ---- */
+    const float4 *orow = reinterpret_cast<const float4 *>(io.obs + r * io.obsStride);
+    float4 *brow = (io.bufObs && valid) ? reinterpret_cast<float4 *>(io.bufObs + r * BB_OBS_DIM) : nullptr;
+    float acc[kCh];
+#pragma unroll
+    for (int c = 0; c < kCh; c++) acc[c] = S.b1[4 * c + q];
+#if BB_POL_MMA
+    if (brow) { /* buffer.obs[step] = obs (ppo.py:128): this thread's 8 of the row's 32 chunks */
+#pragma unroll
+        for (int i = 0; i < 8; i++) brow[4 * i + q] = orow[4 * i + q];
+    }
+    {   /* 3xTF32 tensor-core product (see quad_mma_tf32x3): the A fragment comes straight from global memory, normalised on the fly */
+        const float *xr = io.obs + r * io.obsStride;
+        const int g = lane >> 2;
+        const float *wbase = &S.w1[0][0] + (4 * (g & 1) + (g >> 1)) * kW1Stride + q;
+        float acc2[kCh];   /* odd k-steps accumulate separately: two independent MMA chains per tile (this kernel is latency bound) */
+#pragma unroll
+        for (int c = 0; c < kCh; c++) acc2[c] = 0.f;
+#pragma unroll 4
+        for (int k0 = 0; k0 < BB_OBS_DIM; k0 += 16) {
+            float xv[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int k = k0 + q + 4 * i;
+                xv[i] = (xr[k] - S.mean[k]) * S.inv[k];
+                if (P.obs_clamp > 0.f) xv[i] = fminf(fmaxf(xv[i], -P.obs_clamp), P.obs_clamp);
+            }
+            quad_mma_step<kW1Stride, kCh / 2>(xv[0], xv[1], wbase + k0, acc);
+            quad_mma_step<kW1Stride, kCh / 2>(xv[2], xv[3], wbase + k0 + 8, acc2);
+        }
+#pragma unroll
+        for (int c = 0; c < kCh; c++) acc[c] += acc2[c];
+    }
+#else
+    float4 xq = orow[0];
+#pragma unroll 2
+    for (int k4 = 0; k4 < BB_OBS_DIM / 4; k4++) {
+        const float4 x = xq;
+        if (k4 + 1 < BB_OBS_DIM / 4) xq = orow[k4 + 1]; /* next quad of inputs in flight while this one is used */
+        if (brow && (k4 & 3) == q) brow[k4] = x;         /* buffer.obs[step] = obs (ppo.py:128), one store per chunk */
+        const float4 mu = *reinterpret_cast<const float4 *>(&S.mean[k4 * 4]);
+        const float4 is = *reinterpret_cast<const float4 *>(&S.inv[k4 * 4]);
+        float x0 = (x.x - mu.x) * is.x, x1 = (x.y - mu.y) * is.y, x2 = (x.z - mu.z) * is.z, x3 = (x.w - mu.w) * is.w;
+        if (P.obs_clamp > 0.f) {
+            x0 = fminf(fmaxf(x0, -P.obs_clamp), P.obs_clamp); x1 = fminf(fmaxf(x1, -P.obs_clamp), P.obs_clamp);
+            x2 = fminf(fmaxf(x2, -P.obs_clamp), P.obs_clamp); x3 = fminf(fmaxf(x3, -P.obs_clamp), P.obs_clamp);
+        }
+#pragma unroll
+        for (int c = 0; c < kCh; c++) {
+            const float4 w = *reinterpret_cast<const float4 *>(&S.w1[4 * c + q][k4 * 4]);
+            acc[c] = fmaf(w.w, x3, fmaf(w.z, x2, fmaf(w.y, x1, fmaf(w.x, x0, acc[c]))));
+        }
+    }
+#endif
+    layer_norm_relu(acc, q, H, S.g1, S.e1);              /* backbone.1-2 */
+#pragma unroll
+    for (int c = 0; c < kCh; c++) S.hid[rb][4 * c + q] = acc[c];
+    __syncwarp();
+    /* ---- backbone.3-5: Linear(H,H) + LayerNorm + ReLU ---- */
+#pragma unroll
+    for (int c = 0; c < kCh; c++) acc[c] = S.b2[4 * c + q];
+#if BB_POL_MMA
+    quad_mma_tf32x3<kH, kW2Stride, kCh / 2>(&S.hid[rb][0], &S.w2[0][0], lane, acc);
+#else
+#pragma unroll
+    for (int k4 = 0; k4 < kH / 4; k4++) {
+        const float4 h = *reinterpret_cast<const float4 *>(&S.hid[rb][k4 * 4]);
+#pragma unroll
+        for (int c = 0; c < kCh; c++) {
+            const float4 w = *reinterpret_cast<const float4 *>(&S.w2[4 * c + q][k4 * 4]);
+            acc[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, acc[c]))));
+        }
+    }
+#endif
+    layer_norm_relu(acc, q, H, S.g2, S.e2);
+    __syncwarp(); /* every read of the first hidden vector is done */
+#pragma unroll
+    for (int c = 0; c < kCh; c++) S.hid[rb][4 * c + q] = acc[c];
+    __syncwarp();
+    /* ---- heads: outputs q, q+4, .., q+16 of (19 actor logits | critic) ---- */
+#if BB_POL_MMA
+    float o[kHeadPerThread + 1];   /* o[5]: "output" 20 + q, rows of the next shared array: computed and dropped */
+#pragma unroll
+    for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
+    o[kHeadPerThread] = 0.f;
+    quad_mma_tf32x3<kH, kW2Stride, 3>(&S.hid[rb][0], &S.wh[0][0], lane, o);
+#else
+    float o[kHeadPerThread];
+#pragma unroll
+    for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
+#pragma unroll
+    for (int k4 = 0; k4 < kH / 4; k4++) {
+        const float4 h = *reinterpret_cast<const float4 *>(&S.hid[rb][k4 * 4]);
+#pragma unroll
+        for (int c = 0; c < kHeadPerThread; c++) {
+            const float4 w = *reinterpret_cast<const float4 *>(&S.wh[4 * c + q][k4 * 4]);
+            o[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, o[c]))));
+        }
+    }
+#endif
+#pragma unroll
+    for (int c = 0; c < kHeadPerThread; c++) {
+        const int j = 4 * c + q;
+        S.out[rb][j] = o[c];
+        if (io.logitsOut && valid && j < BB_NUM_LOGITS) io.logitsOut[r * BB_NUM_LOGITS + j] = o[c];
+    }
+    if (q == 3 && valid) { /* output 19 = critic */
+        if (io.evaluateOnly) { if (io.nextValue) io.nextValue[r] = o[kHeadPerThread - 1]; }
+        else if (io.valueOut) io.valueOut[r] = o[kHeadPerThread - 1];
+    }
+    __syncwarp();
+    if (!io.evaluateOnly) {
+        /* ---- bucketed categoricals (action.py:5-33): this thread's one or two buckets ---- */
+        float lp[2] = {0.f, 0.f};
+#pragma unroll
+        for (int s2 = 0; s2 < 2; s2++) {
+            const int b = kQuadBuckets[q][s2];
+            if (b < 0) continue;
+            const int off = kBucketOff[b], cnt = kBucketCnt[b];
+            const float *l = &S.out[rb][off];
+            float m = l[0];
+            for (int i = 1; i < cnt; i++) m = fmaxf(m, l[i]);
+            float s = 0.f;
+            for (int i = 0; i < cnt; i++) s += expf(l[i] - m);
+            const float lse = m + logf(s);
+            int a = 0;
+            if (io.stochastic) { /* inverse CDF: smallest a with u * s < e_0 + .. + e_a; word (b & 1) of Threefry call b >> 1 */
+                uint32_t x0, x1;
+                threefry2x32(io.seed, (uint32_t)(io.rowOffset + r), io.draw, (uint32_t)(b >> 1), x0, x1);
+                const float us = ((float)(((b & 1) ? x1 : x0) >> 8) * 0x1p-24f) * s;
+                float c = 0.f;
+                a = cnt - 1;
+                for (int i = 0; i < cnt; i++) {
+                    c += expf(l[i] - m);
+                    if (us < c) { a = i; break; }
+                }
+            } else {
+                for (int i = 1; i < cnt; i++) if (l[i] > l[a]) a = i;
+            }
+            lp[s2] = l[a] - lse;
+            if (valid) {
+                if (io.actionsOut) io.actionsOut[r * io.actionStride + b] = a;
+                if (io.bufActions) io.bufActions[r * BB_NUM_ACTION_DIMS + b] = (float)a;
+            }
+        }
+        /* log_probs.sum(dim=-1), agent.py:152, in bucket order 0..5: owners q0.a, q1.a, q0.b, q2.a, q2.b, q3.a */
+        const int qb = lane & ~3;
+        float tot = __shfl_sync(0xffffffffu, lp[0], qb);
+        tot += __shfl_sync(0xffffffffu, lp[0], qb + 1);
+        tot += __shfl_sync(0xffffffffu, lp[1], qb);
+        tot += __shfl_sync(0xffffffffu, lp[0], qb + 2);
+        tot += __shfl_sync(0xffffffffu, lp[1], qb + 2);
+        tot += __shfl_sync(0xffffffffu, lp[0], qb + 3);
+        if (q == 0 && valid && io.logpOut) io.logpOut[r] = tot;
+    }
+    /* ---- bookkeeping of the previous step (ppo.py:84-85,128-134; ppo_stats.py:21-36) ---- */
+    if (q == 1 && valid && io.bufRewPrev) {
+        const float rw = io.rew[r * io.rdStride], dn = io.done[r * io.rdStride];
+        io.bufRewPrev[r] = rw;
+        io.bufNotDonePrev[r] = 1.0f - dn;
+        if (io.curReward) {
+            const float cr = io.curReward[r] + rw, el = io.epLength[r] + 1.f;
+            if (dn != 0.f) {
+                atomicAdd(&io.epSums[0], (double)cr);
+                atomicAdd(&io.epSums[1], (double)el);
+                atomicAdd(&io.epSums[2], 1.0);
+            }
+            io.curReward[r] = cr * (1.f - dn);
+            io.epLength[r] = el * (1.f - dn);
+        }
+    }
+    if (q == 2 && valid && io.resetCol) *reinterpret_cast<int2 *>(io.resetCol + r * 2) = make_int2(0, 0);
+    __syncwarp(); /* S.hid / S.out of this quad are rewritten by the next row */
+}
+
 __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy P, const PolicyIo io)
 {
     __shared__ PolicySmem S;
@@ -203,182 +390,7 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
 
     const int64_t rowStride = (int64_t)gridDim.x * kRowsPerBlock;
     for (int64_t rw0 = (int64_t)blockIdx.x * kRowsPerBlock + (rb & ~7); rw0 < io.n; rw0 += rowStride) { /* warp-uniform trip count */
-        const int64_t rr = rw0 + (rb & 7);
-        const bool valid = rr < io.n;
-        const int64_t r = valid ? rr : io.n - 1; /* tail quads shadow the last row and never store */
-        /* ---- backbone.0: observation normaliser (agent.py:27-39) fused into Linear(128,H) ---- */
-        const float4 *orow = reinterpret_cast<const float4 *>(io.obs + r * io.obsStride);
-        float4 *brow = (io.bufObs && valid) ? reinterpret_cast<float4 *>(io.bufObs + r * BB_OBS_DIM) : nullptr;
-        float acc[kCh];
-#pragma unroll
-        for (int c = 0; c < kCh; c++) acc[c] = S.b1[4 * c + q];
-#if BB_POL_MMA
-        if (brow) { /* buffer.obs[step] = obs (ppo.py:128): this thread's 8 of the row's 32 chunks */
-#pragma unroll
-            for (int i = 0; i < 8; i++) brow[4 * i + q] = orow[4 * i + q];
-        }
-        {   /* 3xTF32 tensor-core product (see quad_mma_tf32x3): the A fragment comes straight from global memory, normalised on the fly */
-            const float *xr = io.obs + r * io.obsStride;
-            const int g = lane >> 2;
-            const float *wbase = &S.w1[0][0] + (4 * (g & 1) + (g >> 1)) * kW1Stride + q;
-            float acc2[kCh];   /* odd k-steps accumulate separately: two independent MMA chains per tile (this kernel is latency bound) */
-#pragma unroll
-            for (int c = 0; c < kCh; c++) acc2[c] = 0.f;
-#pragma unroll 4
-            for (int k0 = 0; k0 < BB_OBS_DIM; k0 += 16) {
-                float xv[4];
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const int k = k0 + q + 4 * i;
-                    xv[i] = (xr[k] - S.mean[k]) * S.inv[k];
-                    if (P.obs_clamp > 0.f) xv[i] = fminf(fmaxf(xv[i], -P.obs_clamp), P.obs_clamp);
-                }
-                quad_mma_step<kW1Stride, kCh / 2>(xv[0], xv[1], wbase + k0, acc);
-                quad_mma_step<kW1Stride, kCh / 2>(xv[2], xv[3], wbase + k0 + 8, acc2);
-            }
-#pragma unroll
-            for (int c = 0; c < kCh; c++) acc[c] += acc2[c];
-        }
-#else
-        float4 xq = orow[0];
-#pragma unroll 2
-        for (int k4 = 0; k4 < BB_OBS_DIM / 4; k4++) {
-            const float4 x = xq;
-            if (k4 + 1 < BB_OBS_DIM / 4) xq = orow[k4 + 1]; /* next quad of inputs in flight while this one is used */
-            if (brow && (k4 & 3) == q) brow[k4] = x;         /* buffer.obs[step] = obs (ppo.py:128), one store per chunk */
-            const float4 mu = *reinterpret_cast<const float4 *>(&S.mean[k4 * 4]);
-            const float4 is = *reinterpret_cast<const float4 *>(&S.inv[k4 * 4]);
-            float x0 = (x.x - mu.x) * is.x, x1 = (x.y - mu.y) * is.y, x2 = (x.z - mu.z) * is.z, x3 = (x.w - mu.w) * is.w;
-            if (P.obs_clamp > 0.f) {
-                x0 = fminf(fmaxf(x0, -P.obs_clamp), P.obs_clamp); x1 = fminf(fmaxf(x1, -P.obs_clamp), P.obs_clamp);
-                x2 = fminf(fmaxf(x2, -P.obs_clamp), P.obs_clamp); x3 = fminf(fmaxf(x3, -P.obs_clamp), P.obs_clamp);
-            }
-#pragma unroll
-            for (int c = 0; c < kCh; c++) {
-                const float4 w = *reinterpret_cast<const float4 *>(&S.w1[4 * c + q][k4 * 4]);
-                acc[c] = fmaf(w.w, x3, fmaf(w.z, x2, fmaf(w.y, x1, fmaf(w.x, x0, acc[c]))));
-            }
-        }
-#endif
-        layer_norm_relu(acc, q, H, S.g1, S.e1);              /* backbone.1-2 */
-#pragma unroll
-        for (int c = 0; c < kCh; c++) S.hid[rb][4 * c + q] = acc[c];
-        __syncwarp();
-        /* ---- backbone.3-5: Linear(H,H) + LayerNorm + ReLU ---- */
-#pragma unroll
-        for (int c = 0; c < kCh; c++) acc[c] = S.b2[4 * c + q];
-#if BB_POL_MMA
-        quad_mma_tf32x3<kH, kW2Stride, kCh / 2>(&S.hid[rb][0], &S.w2[0][0], lane, acc);
-#else
-#pragma unroll
-        for (int k4 = 0; k4 < kH / 4; k4++) {
-            const float4 h = *reinterpret_cast<const float4 *>(&S.hid[rb][k4 * 4]);
-#pragma unroll
-            for (int c = 0; c < kCh; c++) {
-                const float4 w = *reinterpret_cast<const float4 *>(&S.w2[4 * c + q][k4 * 4]);
-                acc[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, acc[c]))));
-            }
-        }
-#endif
-        layer_norm_relu(acc, q, H, S.g2, S.e2);
-        __syncwarp(); /* every read of the first hidden vector is done */
-#pragma unroll
-        for (int c = 0; c < kCh; c++) S.hid[rb][4 * c + q] = acc[c];
-        __syncwarp();
-        /* ---- heads: outputs q, q+4, .., q+16 of (19 actor logits | critic) ---- */
-#if BB_POL_MMA
-        float o[kHeadPerThread + 1];   /* o[5]: "output" 20 + q, rows of the next shared array: computed and dropped */
-#pragma unroll
-        for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
-        o[kHeadPerThread] = 0.f;
-        quad_mma_tf32x3<kH, kW2Stride, 3>(&S.hid[rb][0], &S.wh[0][0], lane, o);
-#else
-        float o[kHeadPerThread];
-#pragma unroll
-        for (int c = 0; c < kHeadPerThread; c++) o[c] = S.bh[4 * c + q];
-#pragma unroll
-        for (int k4 = 0; k4 < kH / 4; k4++) {
-            const float4 h = *reinterpret_cast<const float4 *>(&S.hid[rb][k4 * 4]);
-#pragma unroll
-            for (int c = 0; c < kHeadPerThread; c++) {
-                const float4 w = *reinterpret_cast<const float4 *>(&S.wh[4 * c + q][k4 * 4]);
-                o[c] = fmaf(w.w, h.w, fmaf(w.z, h.z, fmaf(w.y, h.y, fmaf(w.x, h.x, o[c]))));
-            }
-        }
-#endif
-#pragma unroll
-        for (int c = 0; c < kHeadPerThread; c++) {
-            const int j = 4 * c + q;
-            S.out[rb][j] = o[c];
-            if (io.logitsOut && valid && j < BB_NUM_LOGITS) io.logitsOut[r * BB_NUM_LOGITS + j] = o[c];
-        }
-        if (q == 3 && valid) { /* output 19 = critic */
-            if (io.evaluateOnly) { if (io.nextValue) io.nextValue[r] = o[kHeadPerThread - 1]; }
-            else if (io.valueOut) io.valueOut[r] = o[kHeadPerThread - 1];
-        }
-        __syncwarp();
-        if (!io.evaluateOnly) {
-            /* ---- bucketed categoricals (action.py:5-33): this thread's one or two buckets ---- */
-            float lp[2] = {0.f, 0.f};
-#pragma unroll
-            for (int s2 = 0; s2 < 2; s2++) {
-                const int b = kQuadBuckets[q][s2];
-                if (b < 0) continue;
-                const int off = kBucketOff[b], cnt = kBucketCnt[b];
-                const float *l = &S.out[rb][off];
-                float m = l[0];
-                for (int i = 1; i < cnt; i++) m = fmaxf(m, l[i]);
-                float s = 0.f;
-                for (int i = 0; i < cnt; i++) s += expf(l[i] - m);
-                const float lse = m + logf(s);
-                int a = 0;
-                if (io.stochastic) { /* inverse CDF: smallest a with u * s < e_0 + .. + e_a; word (b & 1) of Threefry call b >> 1 */
-                    uint32_t x0, x1;
-                    threefry2x32(io.seed, (uint32_t)(io.rowOffset + r), io.draw, (uint32_t)(b >> 1), x0, x1);
-                    const float us = ((float)(((b & 1) ? x1 : x0) >> 8) * 0x1p-24f) * s;
-                    float c = 0.f;
-                    a = cnt - 1;
-                    for (int i = 0; i < cnt; i++) {
-                        c += expf(l[i] - m);
-                        if (us < c) { a = i; break; }
-                    }
-                } else {
-                    for (int i = 1; i < cnt; i++) if (l[i] > l[a]) a = i;
-                }
-                lp[s2] = l[a] - lse;
-                if (valid) {
-                    if (io.actionsOut) io.actionsOut[r * io.actionStride + b] = a;
-                    if (io.bufActions) io.bufActions[r * BB_NUM_ACTION_DIMS + b] = (float)a;
-                }
-            }
-            /* log_probs.sum(dim=-1), agent.py:152, in bucket order 0..5: owners q0.a, q1.a, q0.b, q2.a, q2.b, q3.a */
-            const int qb = lane & ~3;
-            float tot = __shfl_sync(0xffffffffu, lp[0], qb);
-            tot += __shfl_sync(0xffffffffu, lp[0], qb + 1);
-            tot += __shfl_sync(0xffffffffu, lp[1], qb);
-            tot += __shfl_sync(0xffffffffu, lp[0], qb + 2);
-            tot += __shfl_sync(0xffffffffu, lp[1], qb + 2);
-            tot += __shfl_sync(0xffffffffu, lp[0], qb + 3);
-            if (q == 0 && valid && io.logpOut) io.logpOut[r] = tot;
-        }
-        /* ---- bookkeeping of the previous step (ppo.py:84-85,128-134; ppo_stats.py:21-36) ---- */
-        if (q == 1 && valid && io.bufRewPrev) {
-            const float rw = io.rew[r * io.rdStride], dn = io.done[r * io.rdStride];
-            io.bufRewPrev[r] = rw;
-            io.bufNotDonePrev[r] = 1.0f - dn;
-            if (io.curReward) {
-                const float cr = io.curReward[r] + rw, el = io.epLength[r] + 1.f;
-                if (dn != 0.f) {
-                    atomicAdd(&io.epSums[0], (double)cr);
-                    atomicAdd(&io.epSums[1], (double)el);
-                    atomicAdd(&io.epSums[2], 1.0);
-                }
-                io.curReward[r] = cr * (1.f - dn);
-                io.epLength[r] = el * (1.f - dn);
-            }
-        }
-        if (q == 2 && valid && io.resetCol) *reinterpret_cast<int2 *>(io.resetCol + r * 2) = make_int2(0, 0);
-        __syncwarp(); /* S.hid / S.out of this quad are rewritten by the next row */
+        policy_rows8(P, S, io, rw0, rb, q, lane);
     }
 }
 
@@ -391,6 +403,134 @@ __global__ void bb_reset_prologue_kernel(int32_t *resetCol, int32_t *actionCol, 
     resetCol[w * 2 + 1] = 1;
     int2 *a = reinterpret_cast<int2 *>(actionCol + (w * 2 + agentIdx) * 6);
     a[0] = make_int2(0, 0); a[1] = make_int2(0, 0); a[2] = make_int2(0, 0);
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * bb_rollout_loop_kernel: ppo.py rollout() (ppo.py:60-141) as ONE launch.
+ *
+ * Worlds never interact, and a world's trainee / opponent rows are that world's own observation rows: the warp that steps
+ * worlds [w0, w0 + 16) can also run Agent.forward for their rows.  So each warp takes its 16 worlds through env.reset() and
+ * all T x { policy rows (two groups of 8) [+ the frozen opponent's rows]; step_tile } of the rollout, then the closing
+ * critic evaluation, without a launch, a grid dependency or a weight re-staging between steps: the policy weights are
+ * staged once per block (once per rollout instead of once per step), and the observation rows / actions / reward / done
+ * a step hands to the next policy call are this SM's own stores (L1 / L2 hits).  Arithmetic per row = policy_rows8, per tile =
+ * step_tile: bit-identical to the chain of bb_policy_kernel / bb_step_kernel launches bb_rollout enqueues otherwise
+ * (tests/test_rollout_gpu.py runs both against the stepwise loop).  Between a tile's step and its rows' policy call the
+ * warp's stores are ordered before its other lanes' loads by __syncwarp().
+ * Block = ONE tile of 16 worlds and TWO warps: Agent.forward for 8 rows is a ~3000-instruction dependent chain (twice the
+ * step's), so the tile's 16 rows go to the two warps in parallel (8 each, policy_rows8), the block meets at a barrier, warp 0
+ * steps the tile, and the block meets again.  (One warp doing both row groups in turn was measured first: 0.85 ms per rollout
+ * against 0.74 ms for the kernel chain -- the chain runs the row groups on 1024 warps, that form on 512.)
+ * Dynamic shared memory = PolicySmemT<16> (trainee) [+ one for the frozen opponent] + one observation image.  Meant for
+ * grids that are resident at once (bb_rollout falls back to the kernel chain otherwise: with more blocks than slots every
+ * wave of blocks would run the whole rollout one after the other). */
+struct RolloutLoop {
+    bb_rollout_buffers buf;
+    int32_t agentIdx, hasFrozen;
+    uint32_t seed, drawBase;
+    int64_t worldOffset;
+};
+
+template <class Smem>
+BBD void stage_policy(const bb_policy &P, Smem &S, int tid, int nthreads)
+{
+    const int H = P.hidden;
+    for (int i = tid; i < kH * (BB_OBS_DIM / 4); i += nthreads) {
+        const int j = i / (BB_OBS_DIM / 4), k4 = i % (BB_OBS_DIM / 4);
+        const float4 v = j < H ? *reinterpret_cast<const float4 *>(P.w1 + j * BB_OBS_DIM + k4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4 *>(&S.w1[j][k4 * 4]) = v;
+    }
+    for (int i = tid; i < kH * kH; i += nthreads) {
+        const int j = i / kH, k = i % kH;
+        S.w2[j][k] = (j < H && k < H) ? P.w2[j * H + k] : 0.f;
+    }
+    for (int i = tid; i < kHeads * kH; i += nthreads) {
+        const int j = i / kH, k = i % kH;
+        S.wh[j][k] = k < H ? (j < BB_NUM_LOGITS ? P.wa[j * H + k] : P.wc[k]) : 0.f;
+    }
+    for (int i = tid; i < BB_OBS_DIM; i += nthreads) { S.mean[i] = P.obs_mean[i]; S.inv[i] = P.obs_inv_std[i]; }
+    for (int j = tid; j < kH; j += nthreads) {
+        const bool a = j < H;
+        S.b1[j] = a ? P.b1[j] : 0.f; S.g1[j] = a ? P.ln1_g[j] : 0.f; S.e1[j] = a ? P.ln1_b[j] : 0.f;
+        S.b2[j] = a ? P.b2[j] : 0.f; S.g2[j] = a ? P.ln2_g[j] : 0.f; S.e2[j] = a ? P.ln2_b[j] : 0.f;
+    }
+    for (int j = tid; j < kHeads; j += nthreads) S.bh[j] = j < BB_NUM_LOGITS ? P.ba[j] : P.bc[0];
+}
+
+constexpr int kLoopWarps = 2;
+using LoopSmem = PolicySmemT<8 * kLoopWarps>;
+__host__ __device__ constexpr size_t rollout_loop_smem_bytes(bool frozen)
+{
+    return sizeof(LoopSmem) * (frozen ? 2 : 1) + (size_t)kWorldsPerWarp * kImgWorld4 * 16;
+}
+
+__global__ void __launch_bounds__(kLoopWarps * 32) bb_rollout_loop_kernel(const __grid_constant__ StepParams p, const bb_policy trainee,
+                                                                          const bb_policy frozen, const RolloutLoop rl)
+{
+    extern __shared__ float4 smem4[];
+    LoopSmem &St = *reinterpret_cast<LoopSmem *>(smem4);
+    LoopSmem &Sf = *(reinterpret_cast<LoopSmem *>(smem4) + 1);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, q = tid & 3, rb = tid >> 2;
+    float4 *tileImg = reinterpret_cast<float4 *>(reinterpret_cast<LoopSmem *>(smem4) + (rl.hasFrozen ? 2 : 1));
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    stage_policy(trainee, St, tid, kLoopWarps * 32);
+    if (rl.hasFrozen) stage_policy(frozen, Sf, tid, kLoopWarps * 32);
+    const Columns &C = p.col;
+    const int64_t n = p.numWorlds;
+    const int64_t tileWorld0 = (int64_t)blockIdx.x * kWorldsPerWarp;
+    if (tileWorld0 >= n) return; /* block-uniform */
+    const int agent = rl.agentIdx, T = rl.buf.horizon;
+    if (warp == 0) { /* env.reset(), env.py:178-185: Reset flags = 1, trainee action = 0, one step (the flags are cleared by the first policy call) */
+        const int64_t w = tileWorld0 + (lane >> 1);
+        const int me = lane & 1;
+        if (w < n) {
+            C.reset[w * 2 + me] = 1;
+            if (me == agent) {
+                int2 *a = reinterpret_cast<int2 *>(C.action + (w * 2 + me) * 6);
+                a[0] = make_int2(0, 0); a[1] = make_int2(0, 0); a[2] = make_int2(0, 0);
+            }
+        }
+        __syncwarp();
+        step_tile<false, kWorldsPerWarp>(p, p.io, tileImg, tileWorld0, lane);
+    }
+    __syncthreads(); /* the staged weights; the reset step's observation rows before the first policy call's loads */
+    const int64_t rw0 = tileWorld0 + 8 * warp; /* this warp's 8 rows */
+    for (int t = 0; t <= T; t++) {
+        PolicyIo io{};
+        io.obs = C.obs + agent * BB_OBS_DIM; io.obsStride = 2 * BB_OBS_DIM; io.n = n; io.rowOffset = rl.worldOffset;
+        io.stochastic = 1; io.seed = rl.seed; io.draw = rl.drawBase + (uint32_t)t;
+        io.evaluateOnly = (t == T);
+        if (t < T) {
+            io.actionsOut = C.action + agent * 6; io.actionStride = 12;
+            io.logpOut = rl.buf.log_probs + (int64_t)t * n;
+            io.valueOut = rl.buf.values + (int64_t)t * n;
+            io.bufObs = rl.buf.obs + (int64_t)t * n * BB_OBS_DIM;
+            io.bufActions = rl.buf.actions + (int64_t)t * n * BB_NUM_ACTION_DIMS;
+        } else {
+            io.nextValue = rl.buf.next_value;
+        }
+        if (t > 0) {
+            io.rew = C.reward + agent; io.done = C.done + agent; io.rdStride = 2;
+            io.bufRewPrev = rl.buf.rewards + (int64_t)(t - 1) * n;
+            io.bufNotDonePrev = rl.buf.not_dones + (int64_t)(t - 1) * n;
+            io.curReward = rl.buf.cur_reward; io.epLength = rl.buf.ep_length; io.epSums = rl.buf.ep_sums;
+        } else {
+            io.resetCol = C.reset;
+        }
+        if (rw0 < n) policy_rows8(trainee, St, io, rw0, rb, q, lane);
+        if (t == T) break;
+        if (rl.hasFrozen && rw0 < n) { /* env.py:126-143: the frozen policy drives the other agent from its own observation row */
+            PolicyIo fo{};
+            const int other = 1 - agent;
+            fo.obs = C.obs + other * BB_OBS_DIM; fo.obsStride = 2 * BB_OBS_DIM; fo.n = n; fo.rowOffset = rl.worldOffset;
+            fo.stochastic = 1; fo.seed = rl.seed; fo.draw = 0x80000000u + rl.drawBase + (uint32_t)t;
+            fo.actionsOut = C.action + other * 6; fo.actionStride = 12;
+            policy_rows8(frozen, Sf, fo, rw0, rb, q, lane);
+        }
+        __syncthreads(); /* both warps' sampled actions (and cleared Reset flags) before the step's loads */
+        if (warp == 0) step_tile<false, kWorldsPerWarp>(p, p.io, tileImg, tileWorld0, lane);
+        __syncthreads(); /* the step's observation rows, reward and done before the next policy call's loads */
+    }
 }
 
 /* compute_advantages (ppo.py:144-166): thread per environment, reverse scan over the horizon */

@@ -121,8 +121,19 @@ class SimpleGridworldSimulator:
         self._check(self._lib.bb_step(self._h, self._stream()), "bb_step")
 
     def step_n(self, n: int) -> None:
-        """Extension: n consecutive step() calls as one CUDA-graph launch (bb_step_n)."""
+        """Extension: n consecutive step() calls as ONE kernel launch (bb_step_n: every warp takes its worlds through the n
+        steps in a row; BB_STEP_N_GRAPH=1: a CUDA graph of n step kernels)."""
         self._check(self._lib.bb_step_n(self._h, int(n), self._stream()), "bb_step_n")
+
+    def step_n_with_actions(self, actions) -> None:
+        """Extension: `for a in actions: action_tensor.copy_(a); step()` as one kernel launch (bb_step_n_with_actions);
+        actions: int32 [n, N, 2, 6] on the device."""
+        import torch
+
+        assert actions.is_cuda and actions.is_contiguous() and actions.dtype == torch.int32
+        assert actions.dim() == 4 and actions[0].numel() == self.num_worlds * 12
+        self._check(self._lib.bb_step_n_with_actions(self._h, int(actions.shape[0]), actions.data_ptr(), self._stream()),
+                    "bb_step_n_with_actions")
 
     def step_with_actions(self, actions) -> None:
         """Extension: `action_tensor.copy_(actions); step()` fused into the kernel's loads."""

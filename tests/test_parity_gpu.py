@@ -408,9 +408,8 @@ def test_config2_8192_worlds_10000_steps_checksums():
 
 @pytest.mark.parametrize("n", [300, 8192, 200000])
 def test_step_n_graph_replay_equals_separate_steps(n):
-    """bb_step_n: k steps as one CUDA-graph launch (programmatic dependent launch edges between the step kernels at
-    rollout sizes, plain edges with the large-batch kernel) == k separate step() calls, bit for bit; replay and
-    re-capture with another k included."""
+    """bb_step_n: k steps as ONE launch of the looping kernel (one-warp blocks, 64-thread blocks and the large-batch shape
+    with phase barriers) == k separate step() calls, bit for bit; another k included."""
     import torch
 
     a, b = make_engine(n), make_engine(n)
@@ -425,6 +424,49 @@ def test_step_n_graph_replay_equals_separate_steps(n):
         torch.cuda.synchronize()
         assert_states_equal(engine_state(b), engine_state(a), f"step_n N={n} k={k}")
     assert a.launch_count() == b.launch_count()
+
+
+@pytest.mark.parametrize("n", [300, 8192, 200000])
+def test_step_n_with_actions_equals_separate_steps(n):
+    """bb_step_n_with_actions: k steps, each with its own action rows, as ONE launch of the looping kernel (every warp takes
+    its 16 worlds through the k steps in a row) == k step_with_actions launches, bit for bit on every column; a second call
+    continues from the state the first one left."""
+    import torch
+
+    k = 24
+    a, b = make_engine(n), make_engine(n)
+    acts = torch.empty((2 * k, n, 2, 6), dtype=torch.int32, device="cuda")
+    for s in range(2 * k):
+        a.fill_actions(SEED, s, out=acts[s])
+    for half in range(2):
+        for s in range(half * k, (half + 1) * k):
+            a.step_with_actions(acts[s])
+        b.step_n_with_actions(acts[half * k:(half + 1) * k])
+        torch.cuda.synchronize()
+        assert_states_equal(engine_state(b), engine_state(a), f"step_n_with_actions N={n} half={half}")
+    assert b.launch_count() == 1 + 2 * k          # world generation + one pass of the step code per step
+
+
+def test_step_n_graph_form_still_matches(monkeypatch):
+    """BB_STEP_N_GRAPH=1: bb_step_n as round 1's CUDA graph of n step kernels == the looping kernel == separate steps."""
+    import torch
+
+    n = 8192
+    a, b = make_engine(n), make_engine(n)
+    monkeypatch.setenv("BB_STEP_N_GRAPH", "1")
+    c = make_engine(n)
+    monkeypatch.delenv("BB_STEP_N_GRAPH")
+    for s in range(5):
+        for sim in (a, b, c):
+            sim.fill_actions(SEED, s)
+            sim.step()
+    for _ in range(33):
+        a.step()
+    b.step_n(33)
+    c.step_n(33)
+    torch.cuda.synchronize()
+    assert_states_equal(engine_state(b), engine_state(a), "looping kernel")
+    assert_states_equal(engine_state(c), engine_state(a), "graph of step kernels")
 
 
 @pytest.mark.parametrize("n", [300, 8192])
