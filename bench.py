@@ -583,10 +583,13 @@ def run_engine(args):
             calls[s % ring]()
         if world_size > 1:
             dist.barrier()
-        t0 = time.perf_counter()
-        for s in range(Ke):
-            calls[(Wm + s) % ring]()  # returns when reward + done (+ obs) are in host memory
-        dt = time.perf_counter() - t0
+        windows = []              # five windows of Ke steps, the MEDIAN window counts: one host scheduler hiccup does not decide the number
+        for _ in range(5):
+            t0 = time.perf_counter()
+            for s in range(Ke):
+                calls[(Wm + s) % ring]()  # returns when reward + done (+ obs) are in host memory
+            windows.append(time.perf_counter() - t0)
+        dt = sorted(windows)[len(windows) // 2]
         tt = torch.tensor([dt], dtype=torch.float64, device=dev)
         if world_size > 1:
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -734,7 +737,10 @@ def run_engine(args):
                        "parallelism": f"world-sharded x{n_gpus}, no collective in the step"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "path": e2e_path,
                     "what": "per step: action rows read from pinned host memory over PCIe, fused step, reward + done written back "
-                            "to pinned host memory, the call returns when they are there; synchronous, one step in flight.  value = "
+                            "to pinned host memory, the call returns when they are there; synchronous, one step in flight; wall clock, median of "
+                            "five 200-step windows.  The call is SimpleGridworldSimulator.bind_serve_step(...)() / step_host(...): the "
+                            "C-ABI entry point with its pointers looked up once per buffer (the served paths go through the bound-call "
+                            "glue csrc/bb_fastcall.c instead of ctypes, which costs ~1.5 us per call).  value = "
                             "the fastest of the four host paths below (named in `path`); the *_u8 paths take the rows PACKED, u8 "
                             "[N,2,6] (12 B/world, a declared extension of the C ABI: every field the policy emits is < 8), the "
                             "others the reference's int32 rows (48 B/world; int32_rows.value).  The 1024 B/world observation rows "

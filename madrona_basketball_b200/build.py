@@ -75,5 +75,43 @@ def build_engine(force: bool = False, verbose: bool = False, extra=(), out: str 
     return out
 
 
+# ---- binding glue: a CPython callable bound to one C-ABI entry point (csrc/bb_fastcall.c; gcc, no CUDA) ----
+FASTCALL_SRC = os.path.join(_HERE, "csrc", "bb_fastcall.c")
+
+
+def fastcall_path() -> str:
+    import sysconfig
+
+    return os.path.join(_HERE, "_fastcall" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def build_fastcall(force: bool = False) -> str:
+    """gcc -O2 -shared -fPIC bb_fastcall.c -> madrona_basketball_b200/_fastcall.<abi>.so (rebuilt when older than its source)."""
+    import sysconfig
+
+    out = fastcall_path()
+    if not force and os.path.exists(out) and os.path.getsize(out) > 0:
+        with open(FASTCALL_SRC, "rb") as f, open(out + ".hash", "a+") as h:
+            import hashlib
+
+            want = hashlib.sha256(f.read()).hexdigest()
+            h.seek(0)
+            if h.read().strip() == want:
+                return out
+    gcc = shutil.which("gcc") or shutil.which("cc")
+    if not gcc:
+        raise RuntimeError("gcc not found; cannot build _fastcall")
+    cmd = [gcc, "-O2", "-shared", "-fPIC", "-I", sysconfig.get_paths()["include"], FASTCALL_SRC, "-o", out]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("gcc failed:\n" + res.stdout + res.stderr)
+    import hashlib
+
+    with open(FASTCALL_SRC, "rb") as f, open(out + ".hash", "w") as h:
+        h.write(hashlib.sha256(f.read()).hexdigest() + "\n")
+    return out
+
+
 if __name__ == "__main__":
     print(build_engine(force=True, verbose=True))
+    print(build_fastcall(force=True))

@@ -509,21 +509,26 @@ BBD void step_tile(const StepParams &p, const StepIo &io, float4 *warpImg, int64
 
 /* One Manager::step(): thread t = (world t/2, agent t%2).  blockDim.x is any multiple of 32 up to kMaxT; dynamic shared
  * memory = smem_bytes_for(blockDim.x, kWPR).  kSync: see phase_sync; kWPR: worlds per observation round (16 or 8). */
-template <int kMaxT, bool kSync, int kWPR>
-__global__ void __launch_bounds__(kMaxT, kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_kernel(const __grid_constant__ StepParams p)
+/* kMinB: resident blocks per SM the register budget is cut for.  kMinB == 1 with kMaxT == 128 is the "lone warps" shape of the
+ * latency-bound regime (at most 4 x SMs warps): four warps per block, ONE block per SM, so that every warp has a scheduler
+ * (SMSP) to itself and no register cap -- one-warp blocks are spread by the block scheduler unevenly (ncu of 512 one-warp blocks:
+ * some SMSPs hold two warps for the whole kernel while others hold none, SM active time 1.6x apart). */
+template <int kMaxT, bool kSync, int kWPR, int kMinB = (kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 128 / kMaxT)>
+__global__ void __launch_bounds__(kMaxT, kMinB) bb_step_kernel(const __grid_constant__ StepParams p)
 {
     extern __shared__ float4 smem4[];
-    if (kMaxT == 32 && p.prefetchSelf) {
+    constexpr bool kLat = kMaxT == 32 || kMinB == 1; /* a latency-bound shape: every warp alone on its scheduler */
+    if (kLat && p.prefetchSelf) {
         /* A block released early by its predecessor (earlyTrigger) sits here until that grid has drained.  L2 prefetches of
          * the rows it is about to load cost nothing meanwhile and are safe before the wait: the L2 is the point of coherence,
          * so a line the predecessor still writes is simply written in place; nothing is read into registers or L1. */
-        const int64_t w0 = ((int64_t)blockIdx.x * 32) >> 1;
-        if (w0 + kWorldsPerWarp <= p.numWorlds) prefetch_state_rows(p, w0, kWorldsPerWarp, threadIdx.x, (p.prefetchSelf & 2) != 0);
+        const int64_t w0 = ((int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31)) >> 1;
+        if (w0 + kWorldsPerWarp <= p.numWorlds) prefetch_state_rows(p, w0, kWorldsPerWarp, threadIdx.x & 31, (p.prefetchSelf & 2) != 0);
     }
     /* programmatic dependent launch (bb_rollout): let the next kernel of the chain be scheduled early, and wait here for
      * the previous one to complete; both are no-ops for an ordinary launch */
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (kMaxT == 32 && p.earlyTrigger) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (kLat && p.earlyTrigger) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float4 *warpImg = smem4 + warp * kWPR * kImgWorld4;
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -545,8 +550,8 @@ __global__ void __launch_bounds__(kMaxT, kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 1
  * barriers: the block's).  actionStride != 0: step s reads its Action rows from io.actionSrc + s * actionStride (int32
  * elements), a recorded action stream [n,N,2,6]; otherwise every step reads the Action column the previous one left, like
  * scripts/run.py:16-20. */
-template <int kMaxT, bool kSync, int kWPR>
-__global__ void __launch_bounds__(kMaxT, kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 128 / kMaxT) bb_step_loop_kernel(const __grid_constant__ StepParams p, int32_t n, int64_t actionStride)
+template <int kMaxT, bool kSync, int kWPR, int kMinB = (kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 128 / kMaxT)>
+__global__ void __launch_bounds__(kMaxT, kMinB) bb_step_loop_kernel(const __grid_constant__ StepParams p, int32_t n, int64_t actionStride)
 {
     extern __shared__ float4 smem4[];
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -572,15 +577,14 @@ __global__ void __launch_bounds__(kMaxT, kMaxT == 32 ? 8 : BB_MIN_BLOCKS_128 * 1
  * The server exits by itself after idleTimeoutNs without a doorbell, so a vanished host cannot wedge
  * the GPU. */
 struct ServeHostCtl { /* mapped pinned host memory */
-    /* host -> device doorbell: four 64-bit words {actions, reward, done, obs}, each the buffer's device
-     * alias (< 2^48) tagged in its top 16 bits with the low 16 bits of the sequence number to run.
-     * Each word is written and read atomically, and the step starts only when all four carry the
-     * wanted tag, so one poll (one PCIe round trip) fetches doorbell and buffers together.
-     * word[0] == kServeExitWord: leave. */
-    unsigned long long word[4];
-    unsigned long long pad0[4]; /* the doorbell (host writes, device polls) and the completion word (device writes, host
-                                 * spins) sit on different 64-byte lines */
-    int32_t complete;        /* device -> host: last completed sequence number */
+    /* host -> device doorbell.  word[0] is the ONLY word block 0 polls (one 8-byte PCIe read per sample): the low 16 bits of
+     * the sequence number to run in its top 16 bits, kServeU8Bit, kServeLongBit and, in its low 6 bits, the slot of the
+     * device-side table that holds the step's buffer combination {actions, reward, done, obs} (device aliases).
+     * Long form (first use of a combination, or a re-used slot): word[2..5] carry the four aliases; the host writes them
+     * BEFORE word[0], block 0 reads them once AFTER it has acquired word[0] and stores them in the table slot.  Short form:
+     * the slot is already filled.  word[0] == kServeExitWord: leave. */
+    unsigned long long word[8];
+    int32_t complete;        /* device -> host: last completed sequence number (its own 64-byte line: the host spins on it) */
     int32_t alive;           /* device -> host: 1 while the server runs */
     unsigned long long tSeen, tDone; /* %globaltimer when block 0 saw the doorbell / the last block finished (tuning) */
     /* tuning marks (%globaltimer, ns) of the last step: [0] doorbell seen by block 0, [1] after its acquire fence,
@@ -590,12 +594,18 @@ struct ServeHostCtl { /* mapped pinned host memory */
 };
 constexpr unsigned long long kServeExitWord = ~0ull;
 constexpr unsigned long long kServePtrMask = (1ull << 47) - 1;
-constexpr unsigned long long kServeU8Bit = 1ull << 47; /* word[0]: the action rows are packed bytes */
-struct ServeDevCtl { /* device memory */
-    int32_t seq;
-    int32_t stepDone;        /* last sequence number whose completion word has been sent */
+constexpr unsigned long long kServeU8Bit = 1ull << 47;   /* word[0]: the action rows are packed bytes */
+constexpr unsigned long long kServeLongBit = 1ull << 46; /* word[0]: word[2..5] carry the buffer combination of the slot */
+constexpr int kServeSlots = 64;
+struct ServeDevCtl { /* device memory; the polled word, the counter and the flag on different 128-byte lines: blocks that are
+                      * done poll `bell` for the next step while the last blocks still count themselves done */
+    unsigned long long bell;  /* block 0 -> other blocks: the doorbell word of the step to run (tag | flags | slot) */
+    unsigned long long pad0[15];
     unsigned int doneCount;
-    StepIo io;
+    unsigned int pad1[31];
+    int32_t stepDone;         /* last sequence number whose completion word has been sent */
+    int32_t pad2[31];
+    unsigned long long combo[kServeSlots][4]; /* buffer combinations: device aliases of {actions, reward, done, obs} */
 };
 constexpr int32_t kServeExit = -1;
 
@@ -605,8 +615,8 @@ BBD void st_release_gpu(int32_t *p, int32_t v) { asm volatile("st.release.gpu.gl
 BBD void st_release_sys(int32_t *p, int32_t v) { asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 BBD uint64_t global_timer_ns() { uint64_t t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 
-constexpr int kServeThreads = 32;
-__global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_constant__ StepParams p, ServeHostCtl *hc, ServeDevCtl *dc,
+constexpr int kServeThreads = 128; /* upper bound; launched with 32 (one tile per block) or 128 (four tiles, one block per SM) */
+__global__ void __launch_bounds__(kServeThreads, 1) bb_serve_kernel(const __grid_constant__ StepParams p, ServeHostCtl *hc, ServeDevCtl *dc,
                                                                   int32_t startSeq, uint64_t idleTimeoutNs, int flags)
 {
     extern __shared__ float4 smem4[];
@@ -623,50 +633,54 @@ __global__ void __launch_bounds__(kServeThreads) bb_serve_kernel(const __grid_co
         const int32_t want = seq + 1;
         if (threadIdx.x == 0) {
             int32_t got;
+            const unsigned long long tag = (unsigned long long)((unsigned)want & 0xffffu);
+            unsigned long long w0;
             if (blockIdx.x == 0) {
                 const uint64_t t0 = global_timer_ns();
                 unsigned polls = 0;
-                const unsigned long long tag = (unsigned long long)((unsigned)want & 0xffffu);
-                unsigned long long w0, w1, w2, w3;
-                /* one sample (two 16-byte reads) in flight at a time: several outstanding reads of the same host line
-                 * serialise on PCIe and delay everything else on the link (measured: 4 in flight cost 5 us per step) */
+                /* one 8-byte read in flight at a time: several outstanding reads of the same host line serialise on PCIe and
+                 * delay everything else on the link (measured: 4 in flight cost 5 us per step) */
                 for (;;) {
-                    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w0), "=l"(w1) : "l"(&hc->word[0]) : "memory");
-                    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w2), "=l"(w3) : "l"(&hc->word[2]) : "memory");
+                    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w0) : "l"(&hc->word[0]) : "memory");
                     if (w0 == kServeExitWord) { got = kServeExit; break; }
-                    if ((w0 >> 48) == tag && (w1 >> 48) == tag && (w2 >> 48) == tag && (w3 >> 48) == tag) { got = want; break; }
-                    if ((++polls & 31u) == 0 && global_timer_ns() - t0 > idleTimeoutNs) { got = kServeExit; break; }
+                    if ((w0 >> 48) == tag) { got = want; break; }
+                    if ((++polls & 31u) == 0 && global_timer_ns() - t0 > idleTimeoutNs) { got = kServeExit; w0 = kServeExitWord; break; }
                 }
                 tSeen = global_timer_ns();
                 if (marks) { hc->mark[0] = tSeen; hc->tSeen = tSeen; }
-                /* acquire: the host's action rows precede its doorbell.  A relaxed load followed by an ACQUIRE fence is the
-                 * acquire pattern of the PTX memory model; it compiles to CCTL.IVALL (drop this SM's L1 lines).  The acq_rel
-                 * fence used before (flag bit 3 brings it back for A/B runs) adds MEMBAR.ALL.SYS -- the release half, which waits
-                 * for a PCIe round trip although this thread has written nothing the host is waiting for: 17.8 -> 16.4 us per
-                 * served step with packed rows, 23.4 -> 22.0 with int32 rows (profiles/r02j_ab_serve_fences.txt). */
+                /* acquire: the host's action rows (and word[2..5]) precede its doorbell.  A relaxed load followed by an ACQUIRE
+                 * fence is the acquire pattern of the PTX memory model; it compiles to CCTL.IVALL (drop this SM's L1 lines).
+                 * The acq_rel fence used before (flag bit 3 brings it back for A/B runs) adds MEMBAR.ALL.SYS -- the release
+                 * half, which waits for a PCIe round trip although this thread has written nothing the host is waiting for:
+                 * 17.8 -> 16.4 us per served step with packed rows, 23.4 -> 22.0 with int32 rows
+                 * (profiles/r02j_ab_serve_fences.txt). */
                 if (flags & 8) asm volatile("fence.acq_rel.sys;" ::: "memory");
                 else asm volatile("fence.acquire.sys;" ::: "memory");
                 if (marks) hc->mark[1] = global_timer_ns();
-                if (got != kServeExit) {
-                    dc->io.actionSrc = (const int32_t *)(w0 & kServePtrMask); dc->io.rewardOut = (float *)(w1 & kServePtrMask);
-                    dc->io.doneOut = (float *)(w2 & kServePtrMask); dc->io.obsOut = (float *)(w3 & kServePtrMask);
-                    dc->io.actionsU8 = (w0 & kServeU8Bit) ? 1 : 0;
-                    dc->io.actionsHost = ((w0 & kServePtrMask) != 0 && ((w0 & kServePtrMask) & 15ull) == 0) ? 1 : 0;
+                if (got != kServeExit && (w0 & kServeLongBit)) { /* a new buffer combination: into its table slot */
+                    unsigned long long p0, p1, p2, p3;
+                    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(p0), "=l"(p1) : "l"(&hc->word[2]) : "memory");
+                    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(p2), "=l"(p3) : "l"(&hc->word[4]) : "memory");
+                    unsigned long long *c = dc->combo[w0 & (kServeSlots - 1)];
+                    c[0] = p0 & kServePtrMask; c[1] = p1 & kServePtrMask; c[2] = p2 & kServePtrMask; c[3] = p3 & kServePtrMask;
                 }
-                st_release_gpu(&dc->seq, got);
+                asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(&dc->bell), "l"(w0) : "memory");
                 if (marks) hc->mark[2] = global_timer_ns();
             } else {
                 for (;;) {
-                    got = ld_acquire_gpu(&dc->seq);
-                    if (got == want || got == kServeExit) break;
+                    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(w0) : "l"(&dc->bell) : "memory");
+                    if (w0 == kServeExitWord) { got = kServeExit; break; }
+                    if ((w0 >> 48) == tag) { got = want; break; }
                     __nanosleep(20);
                 }
             }
             sSeq = got;
             if (got != kServeExit) {
-                const volatile StepIo *src = &dc->io;
-                sIo.actionSrc = src->actionSrc; sIo.rewardOut = src->rewardOut; sIo.doneOut = src->doneOut;
-                sIo.obsOut = src->obsOut; sIo.actionsHost = src->actionsHost; sIo.actionsU8 = src->actionsU8;
+                const volatile unsigned long long *c = dc->combo[w0 & (kServeSlots - 1)];
+                const unsigned long long a0 = c[0];
+                sIo.actionSrc = (const int32_t *)a0; sIo.rewardOut = (float *)c[1]; sIo.doneOut = (float *)c[2]; sIo.obsOut = (float *)c[3];
+                sIo.actionsU8 = (w0 & kServeU8Bit) ? 1 : 0;
+                sIo.actionsHost = (a0 != 0 && (a0 & 15ull) == 0) ? 1 : 0;
             }
         }
         __syncthreads();
@@ -803,6 +817,8 @@ struct bb_engine {
     bb::StepParams params;
     cudaStream_t hostStream; /* bb_step_host / setters */
     int blockThreads, phaseSync, prefetchBlocks, obsRound, pdlDefault, pdlEarly, prefetchSelf, stepLoop;
+    int lone;         /* the "lone warps" launch shape (bb_step_kernel): 128-thread blocks, one per SM, no register cap */
+    int serveThreads; /* block size of the persistent server: 32 or 128 */
     int64_t launches;
     /* bb_step_n: graph of stepGraphN step kernels */
     cudaGraphExec_t stepGraphExec;
@@ -820,6 +836,9 @@ struct bb_engine {
     const void *aliasHost[64];
     void *aliasDev[64];
     int aliasCount;
+    /* buffer combinations {actions, reward, done, obs} the server's device table holds (host pointers; slot = index) */
+    const void *comboHost[bb::kServeSlots][4];
+    int comboCount, comboNext;
 };
 
 namespace {
@@ -951,9 +970,10 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
     const int wpr = e->obsRound;
     const int smem = bb::smem_bytes_for(threads, wpr);
     pdl = pdl && threads <= 128 && !e->phaseSync;
-    p.earlyTrigger = (pdl && early && threads == 32) ? 1 : 0;
+    const bool lat = threads == 32 || e->lone; /* latency-bound shapes */
+    p.earlyTrigger = (pdl && early && lat) ? 1 : 0;
     p.prefetchSelf = 0;
-    if (pdl && threads == 32 && e->prefetchSelf && !host_mapped)
+    if (pdl && lat && e->prefetchSelf && !host_mapped)
         p.prefetchSelf = 1 | ((!actions_dev || ((uintptr_t)actions_dev & 15u) == 0) ? 2 : 0);
 #define BB_LAUNCH_STEP(MAXT, SYNC, WPR)                                                                          \
     do {                                                                                                         \
@@ -970,7 +990,10 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
         if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_step_loop_kernel<MAXT, SYNC, WPR>, blocks, threads, (size_t)smem, stream, true, p, loop_n, action_stride)); \
         else bb::bb_step_loop_kernel<MAXT, SYNC, WPR><<<blocks, threads, smem, stream>>>(p, loop_n, action_stride); \
     } while (0)
-        if (!BB_NO_T32 && threads == 32 && wpr == 16) BB_LAUNCH_LOOP(32, false, 16);
+        if (e->lone) {
+            if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_step_loop_kernel<128, false, 16, 1>, blocks, threads, (size_t)smem, stream, true, p, loop_n, action_stride));
+            else bb::bb_step_loop_kernel<128, false, 16, 1><<<blocks, threads, smem, stream>>>(p, loop_n, action_stride);
+        } else if (!BB_NO_T32 && threads == 32 && wpr == 16) BB_LAUNCH_LOOP(32, false, 16);
         else if (threads <= 128 && !e->phaseSync && wpr == 16) BB_LAUNCH_LOOP(128, false, 16);
         else if (threads <= 128 && e->phaseSync && wpr == 8) BB_LAUNCH_LOOP(128, true, 8);
         else return 1;
@@ -979,7 +1002,10 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
         BB_CUDA_OK(cudaGetLastError());
         return 0;
     }
-    if (!BB_NO_T32 && threads == 32 && wpr == 16) { /* the latency-bound shape: one-warp blocks, no register cap worth having */
+    if (e->lone) { /* four lone warps per block, one block per SM */
+        if (pdl) BB_CUDA_OK(launch_pdl(bb::bb_step_kernel<128, false, 16, 1>, blocks, threads, (size_t)smem, stream, true, p));
+        else bb::bb_step_kernel<128, false, 16, 1><<<blocks, threads, smem, stream>>>(p);
+    } else if (!BB_NO_T32 && threads == 32 && wpr == 16) { /* the latency-bound shape: one-warp blocks, no register cap worth having */
         BB_LAUNCH_STEP(32, false, 16);
     } else if (threads <= 128) {
         if (e->phaseSync) { if (wpr == 8) BB_LAUNCH_STEP(128, true, 8); else BB_LAUNCH_STEP(128, true, 16); }
@@ -1078,6 +1104,16 @@ bb_engine *bb_create(const bb_config *cfg)
     e->params.prefetchBlocks = 0;
 
     pick_launch_shape(e->N, &e->blockThreads, &e->phaseSync, &e->obsRound);
+    {   /* lone warps (see bb_step_kernel): when the warps fit one per scheduler, four per block and one block per SM */
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.gpu_id);
+        const int64_t warps = (e->N * 2 + 31) / 32;
+        e->lone = 0;
+        if (const char *s = getenv("BB_LONE")) e->lone = atoi(s) != 0 && warps <= 4 * (int64_t)sms;
+        if (e->lone) { e->blockThreads = 128; e->phaseSync = 0; e->obsRound = 16; }
+        e->serveThreads = 32;
+        if (const char *s = getenv("BB_SERVE_THREADS")) { const int v = atoi(s); if ((v == 32 || v == 128) && (v == 32 || warps <= 4 * (int64_t)sms)) e->serveThreads = v; }
+    }
     e->pdlDefault = 1;
     if (const char *s = getenv("BB_PDL")) e->pdlDefault = atoi(s) != 0;
     {   /* Early release of the next programmatic launch (griddepcontrol.launch_dependents at the kernel's top): pays when this
@@ -1088,7 +1124,7 @@ bb_engine *bb_create(const bb_config *cfg)
         int sms = 148;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.gpu_id);
         const int64_t blocks = (e->N * 2 + e->blockThreads - 1) / e->blockThreads;
-        e->pdlEarly = (e->blockThreads == 32 && blocks <= 4 * (int64_t)sms) ? 1 : 0;
+        e->pdlEarly = ((e->blockThreads == 32 && blocks <= 4 * (int64_t)sms) || e->lone) ? 1 : 0;
         if (const char *s = getenv("BB_PDL_EARLY")) e->pdlEarly = atoi(s) != 0;
         /* one-warp blocks prefetch their own rows into L2 ahead of griddepcontrol.wait (bb_step_kernel): 8192 cold-row worlds
          * 9.43 -> 9.11 us per step in a graph, 9.74 -> 9.34 us as queued launches (same-box A/B, profiles r02i) */
@@ -1113,6 +1149,9 @@ bb_engine *bb_create(const bb_config *cfg)
         cudaFuncSetAttribute(bb::bb_step_kernel<128, false, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
         cudaFuncSetAttribute(bb::bb_step_kernel<512, true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
         cudaFuncSetAttribute(bb::bb_step_kernel<512, false, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_step_kernel<128, false, 16, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_step_loop_kernel<128, false, 16, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
+        cudaFuncSetAttribute(bb::bb_serve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
         cudaFuncSetAttribute(bb::bb_step_loop_kernel<128, true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
         cudaFuncSetAttribute(bb::bb_step_loop_kernel<128, false, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, big);
     }
@@ -1284,24 +1323,30 @@ static int step_host_impl(bb_engine *e, const void *actions_host, bool u8, float
 
 static int serve_launch(bb_engine *e)
 {
-    const int smem = bb::smem_bytes_for(bb::kServeThreads, bb::kWorldsPerWarp);
+    const int sthreads = e->serveThreads;
+    const int smem = bb::smem_bytes_for(sthreads, bb::kWorldsPerWarp);
     int perSm = 0, sms = 0;
-    BB_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, bb::bb_serve_kernel, bb::kServeThreads, smem));
+    BB_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, bb::bb_serve_kernel, sthreads, smem));
     BB_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.gpu_id));
     const int64_t tiles = (e->N + bb::kWorldsPerWarp - 1) / bb::kWorldsPerWarp;
+    const int64_t blocksWanted = (tiles * 32 + sthreads - 1) / sthreads;
     int64_t cap = (int64_t)perSm * sms;
     if (cap > 8 * (int64_t)sms) cap = 8 * (int64_t)sms; /* leave room for other kernels on every SM */
-    const int grid = (int)(tiles < cap ? tiles : cap);
+    if (sthreads == 128 && cap > sms) cap = sms;        /* four lone warps per block: one block per SM */
+    const int grid = (int)(blocksWanted < cap ? blocksWanted : cap);
     if (grid <= 0) { set_error("bb_serve_begin: server kernel cannot be resident"); return -1; }
     uint64_t idle_ns = 2000000000ull; /* the server leaves after 2 s without a doorbell */
     if (const char *s = getenv("BB_SERVE_IDLE_MS")) idle_ns = (uint64_t)atoll(s) * 1000000ull;
-    for (int i = 0; i < 4; i++) e->serveHost->word[i] = (unsigned long long)((unsigned)e->serveSeq & 0xffffu) << 48;
+    for (int i = 0; i < 8; i++) e->serveHost->word[i] = 0;
+    e->serveHost->word[0] = (unsigned long long)((unsigned)e->serveSeq & 0xffffu) << 48;
+    e->comboCount = 0; e->comboNext = 0; /* the device table is cleared below */
     e->serveHost->complete = e->serveSeq;
     e->serveHost->alive = 1;
     BB_CUDA_OK(cudaMemsetAsync(e->serveDev, 0, sizeof(bb::ServeDevCtl), e->serveStream));
-    {
-        const int32_t seq = e->serveSeq; /* dc->seq starts at the last completed sequence */
-        BB_CUDA_OK(cudaMemcpyAsync(&e->serveDev->seq, &seq, sizeof seq, cudaMemcpyHostToDevice, e->serveStream));
+    {   /* the forwarded doorbell starts with the tag of the last completed sequence, like the host's */
+        const unsigned long long bell = (unsigned long long)((unsigned)e->serveSeq & 0xffffu) << 48;
+        BB_CUDA_OK(cudaMemcpyAsync(&e->serveDev->bell, &bell, sizeof bell, cudaMemcpyHostToDevice, e->serveStream));
+        BB_CUDA_OK(cudaStreamSynchronize(e->serveStream)); /* `bell` is on this stack frame */
     }
     bb::StepParams p = e->params;
     p.prefetchBlocks = 0;
@@ -1309,7 +1354,7 @@ static int serve_launch(bb_engine *e)
     BB_CUDA_OK(cudaHostGetDevicePointer((void **)&hc_dev, e->serveHost, 0));
     int flags = 0;
     if (const char *s = getenv("BB_SERVE_FLAGS")) flags = atoi(s);
-    bb::bb_serve_kernel<<<grid, bb::kServeThreads, smem, e->serveStream>>>(p, hc_dev, e->serveDev, e->serveSeq, idle_ns, flags);
+    bb::bb_serve_kernel<<<grid, sthreads, smem, e->serveStream>>>(p, hc_dev, e->serveDev, e->serveSeq, idle_ns, flags);
     e->launches++;
     BB_CUDA_OK(cudaGetLastError());
     e->serving = true;
@@ -1370,12 +1415,30 @@ static int serve_step_impl(bb_engine *e, const void *actions_host, bool u8, floa
     const int32_t seq = ++e->serveSeq;
     e->launches++; /* one pass of the step code over every world, like a launch */
     const unsigned long long tag = (unsigned long long)((unsigned)seq & 0xffffu) << 48;
+    const void *hostPtrs[4] = {actions_host, reward_host, done_host, obs_host};
     const void *ptrs[4] = {act_dev, rew_dev, done_dev, obs_dev};
-    for (int i = 0; i < 4; i++) {
+    for (int i = 0; i < 4; i++)
         if ((unsigned long long)(uintptr_t)ptrs[i] & ~bb::kServePtrMask) { set_error("bb_serve_step: buffer alias beyond 47 bits"); return -1; }
-        const unsigned long long flag = (i == 0 && u8 && act_dev) ? bb::kServeU8Bit : 0ull;
-        __atomic_store_n(&hc->word[i], tag | flag | (unsigned long long)(uintptr_t)ptrs[i], __ATOMIC_RELEASE);
-    }
+    /* ring: ONE 8-byte word (the only one block 0 polls).  A buffer combination the device table does not hold yet travels
+     * once, in word[2..5], written before the doorbell word. */
+    auto ring = [&](bool forceLong) {
+        int slot = -1;
+        if (!forceLong)
+            for (int i = 0; i < e->comboCount && slot < 0; i++)
+                if (e->comboHost[i][0] == hostPtrs[0] && e->comboHost[i][1] == hostPtrs[1] && e->comboHost[i][2] == hostPtrs[2] &&
+                    e->comboHost[i][3] == hostPtrs[3]) slot = i;
+        unsigned long long w0 = tag | ((u8 && act_dev) ? bb::kServeU8Bit : 0ull);
+        if (slot < 0) {
+            slot = e->comboCount < bb::kServeSlots ? e->comboCount++ : (e->comboNext++ % bb::kServeSlots);
+            for (int i = 0; i < 4; i++) {
+                e->comboHost[slot][i] = hostPtrs[i];
+                __atomic_store_n(&hc->word[2 + i], (unsigned long long)(uintptr_t)ptrs[i], __ATOMIC_RELAXED);
+            }
+            w0 |= bb::kServeLongBit;
+        }
+        __atomic_store_n(&hc->word[0], w0 | (unsigned long long)slot, __ATOMIC_RELEASE);
+    };
+    ring(false);
     /* spin on the completion word the last block writes into this page */
     uint64_t spins = 0;
     int relaunches = 0;
@@ -1391,10 +1454,7 @@ static int serve_step_impl(bb_engine *e, const void *actions_host, bool u8, floa
                     const int rc = serve_launch(e);
                     e->serveSeq = seq;
                     if (rc != 0) return -1;
-                    for (int i = 0; i < 4; i++) {
-                        const unsigned long long flag = (i == 0 && u8 && act_dev) ? bb::kServeU8Bit : 0ull;
-                        __atomic_store_n(&hc->word[i], tag | flag | (unsigned long long)(uintptr_t)ptrs[i], __ATOMIC_RELEASE);
-                    }
+                    ring(true); /* serve_launch cleared the device table */
                     continue;
                 }
                 e->serving = false;

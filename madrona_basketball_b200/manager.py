@@ -8,6 +8,7 @@ engine's device memory as zero-copy tensors and to name the current stream.
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Dict, Optional, Tuple
 
 import numpy as np
@@ -16,6 +17,23 @@ from . import _lib
 from .madrona import ExecMode
 
 FLAG_TAG_MASK = 1  # include/bb_engine.h: BB_FLAG_TAG_MASK
+
+_FASTCALL = False
+
+
+def _fastcall_module():
+    """The bound-call glue (csrc/bb_fastcall.c), or None when it has not been built (the ctypes closures are used then).
+    BB_NO_FASTCALL=1 disables it (A/B runs)."""
+    global _FASTCALL
+    if _FASTCALL is False:
+        _FASTCALL = None
+        if not os.environ.get("BB_NO_FASTCALL"):
+            try:
+                from . import _fastcall
+                _FASTCALL = _fastcall
+            except ImportError:
+                pass
+    return _FASTCALL
 
 # include/bb_engine.h enum bb_slot
 SLOTS: Dict[str, int] = {
@@ -204,6 +222,10 @@ class SimpleGridworldSimulator:
         args = (self._h, self._host_ptr(actions, np.uint8 if u8 else np.int32, n * 12), self._host_ptr(reward, np.float32, n * 2),
                 self._host_ptr(done, np.float32, n * 2), self._host_ptr(obs, np.float32, n * 256))
         check = self._check
+        fast = _fastcall_module()
+        if fast is not None:   # csrc/bb_fastcall.c: the same C-ABI call with the same pointers, without ctypes' ~1.5 us per call
+            addr = lambda f: ctypes.cast(f, ctypes.c_void_p).value
+            return fast.bind5(addr(fn), addr(self._lib.bb_last_error), *(int(a or 0) for a in args))
 
         def call():
             if fn(*args) != 0:

@@ -180,3 +180,32 @@ def test_squared_length_thresholds_equal_the_sqrt_tests():
             assert np.array_equal(root <= c, s <= T), name
         else:
             assert np.array_equal(root >= c, s >= T), name
+
+
+def test_fastcall_glue_calls_the_bound_entry_point(lib):
+    """csrc/bb_fastcall.c: bind5(fn, last_error, a0..a4)() is `fn(a0..a4)` -- the arguments arrive unchanged, a zero return
+    yields None, a non-zero return raises with bb_last_error()'s text.  No compute: the bound function here is a ctypes
+    callback standing in for bb_serve_step."""
+    from madrona_basketball_b200 import build
+
+    build.build_fastcall()
+    from madrona_basketball_b200 import _fastcall
+
+    seen = []
+    proto = ctypes.CFUNCTYPE(ctypes.c_int, *([ctypes.c_void_p] * 5))
+
+    def target(a, b, c, d, e):
+        seen.append((a, b, c, d, e))
+        return 0 if len(seen) == 1 else 7
+
+    cb = proto(target)
+    addr = lambda f: ctypes.cast(f, ctypes.c_void_p).value
+    call = _fastcall.bind5(addr(cb), addr(lib.bb_last_error), 0x1000, 0x2000, 0x3000, 0, 0x5000)
+    assert call() is None
+    assert seen == [(0x1000, 0x2000, 0x3000, None, 0x5000)]
+    with pytest.raises(RuntimeError, match="rc 7"):
+        call()
+    with pytest.raises(TypeError):
+        call(1)
+    with pytest.raises(ValueError):
+        _fastcall.bind5(0, 0, 0, 0, 0, 0, 0)

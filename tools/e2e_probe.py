@@ -50,6 +50,17 @@ loop("bb_step_host_u8 pinned packed rows", lambda: lib.bb_step_host_u8(h, p8, pr
 lib.bb_serve_begin(h)
 loop("bb_serve_step_u8 pinned packed rows", lambda: lib.bb_serve_step_u8(h, p8, pr, pd, None), sync=False)
 loop("bb_serve_step_u8 packed rows only (no reward/done)", lambda: lib.bb_serve_step_u8(h, p8, None, None, None), sync=False)
+# bench.py's e2e conditions: a fresh random batch every step (some tile always runs a shot / reset path), ring of 32 buffers
+ring8 = []
+for s_ in range(32):
+    sh.fill_actions(1234, 100 + s_, out=dact)
+    ring8.append(dact.to(torch.uint8).cpu().pin_memory())
+ring_ptrs = [t_.data_ptr() for t_ in ring8]
+ring_i = [0]
+def serve_ring():
+    ring_i[0] = (ring_i[0] + 1) & 31
+    lib.bb_serve_step_u8(h, ring_ptrs[ring_i[0]], pr, pd, None)
+loop("bb_serve_step_u8 ring of 32 random batches (bench e2e)", serve_ring, sync=False)
 n8, = (u8.numpy(),)
 loop("sim.serve_step(numpy u8) python wrapper", lambda: sim.serve_step(n8, nr, nd), sync=False)
 def marks(name, fn):

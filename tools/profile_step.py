@@ -13,6 +13,7 @@ def main():
     ap.add_argument("--worlds", type=int, default=1 << 20)
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--times", action="store_true", help="print the event time of every step (to pick an event-heavy step for ncu -s)")
+    ap.add_argument("--loop", type=int, default=0, help="after the steps: one bb_step_n launch of this many steps (bb_step_loop_kernel)")
     args = ap.parse_args()
     import torch
     from madrona_basketball_b200.shard import ShardedSimulator
@@ -28,6 +29,8 @@ def main():
         sh.sim.step_with_actions(act)
         if args.times:
             ev[-1][1].record()
+    if args.loop:
+        sh.sim.step_n(args.loop)
     torch.cuda.synchronize()
     if args.times:
         us = [a.elapsed_time(b) * 1e3 for a, b in ev]
