@@ -517,7 +517,7 @@ template <int kMaxT, bool kSync, int kWPR, int kMinB = (kMaxT == 32 ? 8 : BB_MIN
 __global__ void __launch_bounds__(kMaxT, kMinB) bb_step_kernel(const __grid_constant__ StepParams p)
 {
     extern __shared__ float4 smem4[];
-    constexpr bool kLat = kMaxT == 32 || kMinB == 1; /* a latency-bound shape: every warp alone on its scheduler */
+    constexpr bool kLat = true; /* early release / self prefetch are the host's choice per launch shape (bb_create) */
     if (kLat && p.prefetchSelf) {
         /* A block released early by its predecessor (earlyTrigger) sits here until that grid has drained.  L2 prefetches of
          * the rows it is about to load cost nothing meanwhile and are safe before the wait: the L2 is the point of coherence,
@@ -817,6 +817,7 @@ struct bb_engine {
     bb::StepParams params;
     cudaStream_t hostStream; /* bb_step_host / setters */
     int blockThreads, phaseSync, prefetchBlocks, obsRound, pdlDefault, pdlEarly, prefetchSelf, stepLoop;
+    int pdlSync;      /* programmatic launches (+ early release, self prefetch) for the phase-barrier shape too (BB_PDL_SYNC) */
     int lone;         /* the "lone warps" launch shape (bb_step_kernel): 128-thread blocks, one per SM, no register cap */
     int serveThreads; /* block size of the persistent server: 32 or 128 */
     int64_t launches;
@@ -969,8 +970,8 @@ int launch_step(bb_engine *e, const int32_t *actions_dev, cudaStream_t stream, f
     const int blocks = (int)((e->N * 2 + threads - 1) / threads);
     const int wpr = e->obsRound;
     const int smem = bb::smem_bytes_for(threads, wpr);
-    pdl = pdl && threads <= 128 && !e->phaseSync;
-    const bool lat = threads == 32 || e->lone; /* latency-bound shapes */
+    const bool lat = threads <= 128 && (!e->phaseSync || e->pdlSync); /* shapes whose launches are programmatic (bb_create decides) */
+    pdl = pdl && lat;
     p.earlyTrigger = (pdl && early && lat) ? 1 : 0;
     p.prefetchSelf = 0;
     if (pdl && lat && e->prefetchSelf && !host_mapped)
@@ -1116,19 +1117,20 @@ bb_engine *bb_create(const bb_config *cfg)
     }
     e->pdlDefault = 1;
     if (const char *s = getenv("BB_PDL")) e->pdlDefault = atoi(s) != 0;
-    {   /* Early release of the next programmatic launch (griddepcontrol.launch_dependents at the kernel's top): pays when this
-         * grid and the next one fit on the GPU together -- one-warp blocks, at most half of the 8 block slots per SM -- so the
-         * next step's blocks are resident at their griddepcontrol.wait when this one drains.  Same-box A/B (profiles r02i):
-         * 2048 worlds 9.4 -> 6.6 us per queued launch, 8192 worlds 10.0 -> 8.9 us in a graph; 16 384 worlds (1024 blocks,
-         * they no longer fit twice) 10.7 -> 11.1 us, hence the bound.  BB_PDL_EARLY=0/1 overrides. */
-        int sms = 148;
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.gpu_id);
-        const int64_t blocks = (e->N * 2 + e->blockThreads - 1) / e->blockThreads;
-        e->pdlEarly = ((e->blockThreads == 32 && blocks <= 4 * (int64_t)sms) || e->lone) ? 1 : 0;
+    {   /* Early release of the next programmatic launch (every block executes griddepcontrol.launch_dependents once it is past
+         * its own griddepcontrol.wait, so the next grid is scheduled as soon as this grid's LAST block has started) together
+         * with the L2 self-prefetch (a block that sits at its griddepcontrol.wait has already asked for the rows it is about
+         * to load): the next step's blocks fill the slots this grid's tail frees, rows on their way.  On by default for every
+         * launch shape without phase barriers.  Same-box A/B, cold rows, us per step (profiles r02i, r02r): 2048 worlds
+         * 9.4 -> 6.6, 8192 10.0 -> 8.9, 16 384 10.95 -> 10.1, 32 768 16.4 -> 14.4, 65 536 30.0 -> 28.8; either half alone
+         * does nothing (early release) or harm (the prefetch on the critical path: 16 384 worlds 12.4).
+         * BB_PDL_EARLY / BB_PREFETCH_SELF = 0/1 override; BB_PDL_SYNC=1 extends all three to the phase-barrier shape. */
+        e->pdlSync = 0;
+        if (const char *s = getenv("BB_PDL_SYNC")) e->pdlSync = atoi(s) != 0;
+        const int on = (e->blockThreads <= 128 && (!e->phaseSync || e->pdlSync)) ? 1 : 0;
+        e->pdlEarly = on;
         if (const char *s = getenv("BB_PDL_EARLY")) e->pdlEarly = atoi(s) != 0;
-        /* one-warp blocks prefetch their own rows into L2 ahead of griddepcontrol.wait (bb_step_kernel): 8192 cold-row worlds
-         * 9.43 -> 9.11 us per step in a graph, 9.74 -> 9.34 us as queued launches (same-box A/B, profiles r02i) */
-        e->prefetchSelf = 1;
+        e->prefetchSelf = on;
         if (const char *s = getenv("BB_PREFETCH_SELF")) e->prefetchSelf = atoi(s) != 0;
     }
     if (!check_sqrt_thresholds()) {

@@ -17,6 +17,7 @@ timeout 120 python tools/profile_step.py --worlds $W --steps 72 > $O/${TAG}_plai
 done
 # the looping kernel (bb_step_n): 64 steps in one launch at 8192 worlds, and the one-launch rollout
 timeout 120 python tools/profile_step.py --worlds 8192 --steps 8 --loop 64 > $O/${TAG}_plain_prof_loop.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:bb_step_loop_kernel -c 1 -f -o $O/${TAG}_prof_step_loop_8192 python tools/profile_step.py --worlds 8192 --steps 8 --loop 64 > $O/${TAG}_ncu_prof_loop.log 2>&1
+timeout 120 python tools/profile_rollout.py > $O/${TAG}_plain_prof_rollout.log 2>&1 && timeout 600 ncu --set full --clock-control none --import-source on -k regex:bb_rollout_loop_kernel -s 2 -c 1 -f -o $O/${TAG}_prof_rollout_loop_8192 python tools/profile_rollout.py > $O/${TAG}_ncu_prof_rollout.log 2>&1
 fi
 timeout 300 python tools/ab_step.py madrona_basketball_b200/libbball.so:BB_STEP_N_GRAPH=1 madrona_basketball_b200/libbball.so 8192 65536 > $O/${TAG}_ab_step_n_loop.txt 2>&1
 ENVS_LIST="8192" bash tools/ab_rollout_loop.sh > $O/${TAG}_ab_rollout_loop.txt 2>&1
