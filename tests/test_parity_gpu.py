@@ -56,11 +56,15 @@ def test_ragged_world_counts(n):
                                    dict(BB_BLOCK_THREADS="128", BB_PHASE_SYNC="0", BB_OBS_ROUND="16"),
                                    dict(BB_BLOCK_THREADS="64", BB_OBS_ROUND="8"),
                                    dict(BB_BLOCK_THREADS="256", BB_PHASE_SYNC="1"),
-                                   dict(BB_PDL="0")])
+                                   dict(BB_PDL="0"),
+                                   dict(BB_LONE="1"),
+                                   dict(BB_PDL_EARLY="0", BB_PREFETCH_SELF="0"),
+                                   dict(BB_BLOCK_THREADS="128", BB_PHASE_SYNC="1", BB_OBS_ROUND="8", BB_PDL_SYNC="1")])
 def test_every_launch_shape_is_bit_exact(monkeypatch, shape):
     """The launch shapes the engine picks by world count (one-warp blocks / 64 threads / 128 threads with phase barriers and
-    two observation rounds / the 512-thread instantiation), forced here at a size the oracle checks every column of
-    (observations included): ragged count, dead-path flags off, 60 steps."""
+    two observation rounds / the 512-thread instantiation) and its tuning knobs (no programmatic launches, the lone-warps
+    shape, no early release / self-prefetch, all three with the phase-barrier shape), forced here at a size the oracle checks
+    every column of (observations included): ragged count, dead-path flags off, 60 steps."""
     for k, v in shape.items():
         monkeypatch.setenv(k, v)
     _run_lockstep(1000 + 37, 60, check_every=7)
@@ -287,6 +291,39 @@ def test_packed_u8_action_rows_match_int32_rows(n):
     assert_states_equal(engine_state(c), engine_state(a), "serve_step_u8")
     with pytest.raises(RuntimeError, match="pinned"):
         b.step_host(np.zeros((n, 2, 6), np.uint8))
+
+
+@pytest.mark.parametrize("serve_threads", ["32", "128"])
+def test_server_buffer_combinations_and_bound_calls(monkeypatch, serve_threads):
+    """The doorbell is one word carrying the slot of a device-side table of buffer combinations {actions, reward, done, obs}:
+    a ring of action buffers LARGER than the 64-slot table (slots are re-used), int32 and packed rows in turn, two sets of
+    result buffers, steps without result buffers, every call through bind_serve_step (the bound C-ABI call of
+    csrc/bb_fastcall.c when it is built) == the same steps as ordinary launches.  Both block sizes of the server."""
+    import torch
+
+    monkeypatch.setenv("BB_SERVE_THREADS", serve_threads)
+    n, ring, steps = 300, 70, 160
+    a, b = make_engine(n), make_engine(n)
+    act = torch.empty((n, 2, 6), dtype=torch.int32, device="cuda")
+    h32 = [torch.empty((n, 2, 6), dtype=torch.int32).pin_memory() for _ in range(ring)]
+    h8 = [torch.empty((n, 2, 6), dtype=torch.uint8).pin_memory() for _ in range(ring)]
+    res = [(torch.empty((n, 2)).pin_memory(), torch.empty((n, 2)).pin_memory()) for _ in range(2)]
+    b.serve_begin()
+    for s in range(steps):
+        a.fill_actions(SEED, s, out=act); a.step_with_actions(act)
+        torch.cuda.current_stream().synchronize()
+        i, packed, (rew, done) = s % ring, (s // 3) % 2 == 1, res[s % 2]
+        buf = h8[i] if packed else h32[i]
+        buf.copy_(act.to(buf.dtype))
+        if s % 5 == 4:
+            b.bind_serve_step(buf.numpy())()                       # no result buffers: another combination
+        else:
+            b.bind_serve_step(buf.numpy(), rew.numpy(), done.numpy())()
+            assert np.array_equal(rew.numpy().view(np.int32), a.reward_tensor().to_torch().cpu().numpy().view(np.int32)), s
+            assert np.array_equal(done.numpy(), a.done_tensor().to_torch().cpu().numpy()), s
+    b.serve_end()
+    torch.cuda.synchronize()
+    assert_states_equal(engine_state(b), engine_state(a), f"server combinations, {serve_threads}-thread blocks")
 
 
 def test_persistent_server_idle_exit_and_restart(monkeypatch):
