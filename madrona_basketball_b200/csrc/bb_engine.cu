@@ -1398,49 +1398,50 @@ static int serve_step_impl(bb_engine *e, const void *actions_host, bool u8, floa
         BB_CUDA_OK(cudaStreamSynchronize(e->serveStream));
         if (serve_launch(e) != 0) return -1;
     }
-    auto alias = [e](const void *host) -> void * {
-        if (!host) return nullptr;
-        for (int i = 0; i < e->aliasCount; i++)
-            if (e->aliasHost[i] == host) return e->aliasDev[i];
-        void *dev = mapped_alias(host);
-        if (dev && e->aliasCount < 64) { e->aliasHost[e->aliasCount] = host; e->aliasDev[e->aliasCount++] = dev; }
-        return dev;
+    const void *hostPtrs[4] = {actions_host, reward_host, done_host, obs_host};
+    const void *ptrs[4] = {nullptr, nullptr, nullptr, nullptr}; /* device aliases: resolved only for a combination the table lacks */
+    auto resolve = [&]() -> int {
+        auto alias = [e](const void *host) -> void * {
+            if (!host) return nullptr;
+            for (int i = 0; i < e->aliasCount; i++)
+                if (e->aliasHost[i] == host) return e->aliasDev[i];
+            void *dev = mapped_alias(host);
+            if (dev && e->aliasCount < 64) { e->aliasHost[e->aliasCount] = host; e->aliasDev[e->aliasCount++] = dev; }
+            return dev;
+        };
+        for (int i = 0; i < 4; i++) {
+            ptrs[i] = alias(hostPtrs[i]);
+            if (hostPtrs[i] && !ptrs[i]) { set_error("bb_serve_step: buffers must be pinned (page-locked, mapped) host memory"); return -1; }
+            if ((unsigned long long)(uintptr_t)ptrs[i] & ~bb::kServePtrMask) { set_error("bb_serve_step: buffer alias beyond 47 bits"); return -1; }
+        }
+        return 0;
     };
-    const int32_t *act_dev = (const int32_t *)alias(actions_host);
-    float *rew_dev = (float *)alias(reward_host);
-    float *done_dev = (float *)alias(done_host);
-    float *obs_dev = (float *)alias(obs_host);
-    if ((actions_host && !act_dev) || (reward_host && !rew_dev) || (done_host && !done_dev) || (obs_host && !obs_dev)) {
-        set_error("bb_serve_step: buffers must be pinned (page-locked, mapped) host memory");
-        return -1;
-    }
+    /* ring: ONE 8-byte word (the only one block 0 polls).  A buffer combination the device table does not hold yet is
+     * validated (pinned, mapped) and travels once, in word[2..5], written before the doorbell word; a combination the
+     * table holds costs a scan of at most 64 x 4 host pointers. */
+    int slot = -1;
+    for (int i = 0; i < e->comboCount && slot < 0; i++)
+        if (e->comboHost[i][0] == hostPtrs[0] && e->comboHost[i][1] == hostPtrs[1] && e->comboHost[i][2] == hostPtrs[2] &&
+            e->comboHost[i][3] == hostPtrs[3]) slot = i;
+    if (slot < 0 && resolve() != 0) return -1;
     const int32_t seq = ++e->serveSeq;
     e->launches++; /* one pass of the step code over every world, like a launch */
     const unsigned long long tag = (unsigned long long)((unsigned)seq & 0xffffu) << 48;
-    const void *hostPtrs[4] = {actions_host, reward_host, done_host, obs_host};
-    const void *ptrs[4] = {act_dev, rew_dev, done_dev, obs_dev};
-    for (int i = 0; i < 4; i++)
-        if ((unsigned long long)(uintptr_t)ptrs[i] & ~bb::kServePtrMask) { set_error("bb_serve_step: buffer alias beyond 47 bits"); return -1; }
-    /* ring: ONE 8-byte word (the only one block 0 polls).  A buffer combination the device table does not hold yet travels
-     * once, in word[2..5], written before the doorbell word. */
-    auto ring = [&](bool forceLong) {
-        int slot = -1;
-        if (!forceLong)
-            for (int i = 0; i < e->comboCount && slot < 0; i++)
-                if (e->comboHost[i][0] == hostPtrs[0] && e->comboHost[i][1] == hostPtrs[1] && e->comboHost[i][2] == hostPtrs[2] &&
-                    e->comboHost[i][3] == hostPtrs[3]) slot = i;
-        unsigned long long w0 = tag | ((u8 && act_dev) ? bb::kServeU8Bit : 0ull);
-        if (slot < 0) {
-            slot = e->comboCount < bb::kServeSlots ? e->comboCount++ : (e->comboNext++ % bb::kServeSlots);
+    auto ring = [&](int useSlot) -> int {
+        unsigned long long w0 = tag | ((u8 && actions_host) ? bb::kServeU8Bit : 0ull);
+        if (useSlot < 0) { /* a new combination, or the server was relaunched (its table is empty) */
+            if (!ptrs[0] && !ptrs[1] && !ptrs[2] && !ptrs[3] && resolve() != 0) return -1;
+            useSlot = e->comboCount < bb::kServeSlots ? e->comboCount++ : (e->comboNext++ % bb::kServeSlots);
             for (int i = 0; i < 4; i++) {
-                e->comboHost[slot][i] = hostPtrs[i];
+                e->comboHost[useSlot][i] = hostPtrs[i];
                 __atomic_store_n(&hc->word[2 + i], (unsigned long long)(uintptr_t)ptrs[i], __ATOMIC_RELAXED);
             }
             w0 |= bb::kServeLongBit;
         }
-        __atomic_store_n(&hc->word[0], w0 | (unsigned long long)slot, __ATOMIC_RELEASE);
+        __atomic_store_n(&hc->word[0], w0 | (unsigned long long)useSlot, __ATOMIC_RELEASE);
+        return 0;
     };
-    ring(false);
+    if (ring(slot) != 0) return -1;
     /* spin on the completion word the last block writes into this page */
     uint64_t spins = 0;
     int relaunches = 0;
@@ -1456,7 +1457,7 @@ static int serve_step_impl(bb_engine *e, const void *actions_host, bool u8, floa
                     const int rc = serve_launch(e);
                     e->serveSeq = seq;
                     if (rc != 0) return -1;
-                    ring(true); /* serve_launch cleared the device table */
+                    if (ring(-1) != 0) return -1; /* serve_launch cleared the device table */
                     continue;
                 }
                 e->serving = false;
