@@ -40,6 +40,11 @@ struct PolicyIo {
     double *epSums;
     int32_t *resetCol; /* both Reset flags of every world are cleared (end of env.reset(), env.py:182) */
     float *nextValue;
+    /* policy_rows8<true> (bb_rollout_loop_kernel): the tile's observation image in shared memory, the tile's first world and
+     * which of a world's two rows (agent index) to read */
+    const float4 *obsImg;
+    int64_t obsImgWorld0;
+    int obsImgRow;
 };
 
 /* ------------------------------------------------------------------------------------------------
@@ -171,7 +176,10 @@ __device__ __constant__ int kQuadBuckets[4][2] = {{0, 2}, {1, -1}, {3, 4}, {5, -
 /* Agent.forward + sampling + rollout bookkeeping for the 8 rows rw0 .. rw0 + 7 on the calling warp (quad (rb & 7) takes row
  * rw0 + (rb & 7); rb = the quad's row slot in S.hid / S.out; all 32 lanes must call it).  The body of bb_policy_kernel's row
  * loop, shared with bb_rollout_loop_kernel: the same instructions in the same order, hence the same bits. */
-template <class Smem>
+/* kImg (bb_rollout_loop_kernel): the rows are read from the step's observation IMAGE in shared memory (io.obsImg: the tile's
+ * rows as the step staged them, 26 chunks of columns 0..103; columns 104..127 are zero in the rows and have no chunk) instead
+ * of from the Observations column the step has just written through to L2 -- the same floats, without the L2 round trips. */
+template <bool kImg, class Smem>
 BBD void policy_rows8(const bb_policy &P, Smem &S, const PolicyIo &io, int64_t rw0, int rb, int q, int lane)
 {
     const int H = P.hidden;
@@ -179,7 +187,8 @@ BBD void policy_rows8(const bb_policy &P, Smem &S, const PolicyIo &io, int64_t r
     const bool valid = rr < io.n;
     const int64_t r = valid ? rr : io.n - 1; /* tail quads shadow the last row and never store */
     /* ---- backbone.0: observation normaliser (agent.py:27-39) fused into Linear(128,H) ---- */
-    const float4 *orow = reinterpret_cast<const float4 *>(io.obs + r * io.obsStride);
+    const float4 *orow = kImg ? io.obsImg + (r - io.obsImgWorld0) * kImgWorld4 + io.obsImgRow * kImgRow4
+                              : reinterpret_cast<const float4 *>(io.obs + r * io.obsStride);
     float4 *brow = (io.bufObs && valid) ? reinterpret_cast<float4 *>(io.bufObs + r * BB_OBS_DIM) : nullptr;
     float acc[kCh];
 #pragma unroll
@@ -187,10 +196,13 @@ BBD void policy_rows8(const bb_policy &P, Smem &S, const PolicyIo &io, int64_t r
 #if BB_POL_MMA
     if (brow) { /* buffer.obs[step] = obs (ppo.py:128): this thread's 8 of the row's 32 chunks */
 #pragma unroll
-        for (int i = 0; i < 8; i++) brow[4 * i + q] = orow[4 * i + q];
+        for (int i = 0; i < 8; i++) {
+            const int c = 4 * i + q;
+            brow[c] = (!kImg || c < kObsChunks) ? orow[c] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
     }
     {   /* 3xTF32 tensor-core product (see quad_mma_tf32x3): the A fragment comes straight from global memory, normalised on the fly */
-        const float *xr = io.obs + r * io.obsStride;
+        const float *xr = reinterpret_cast<const float *>(orow);
         const int g = lane >> 2;
         const float *wbase = &S.w1[0][0] + (4 * (g & 1) + (g >> 1)) * kW1Stride + q;
         float acc2[kCh];   /* odd k-steps accumulate separately: two independent MMA chains per tile (this kernel is latency bound) */
@@ -202,7 +214,8 @@ BBD void policy_rows8(const bb_policy &P, Smem &S, const PolicyIo &io, int64_t r
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 const int k = k0 + q + 4 * i;
-                xv[i] = (xr[k] - S.mean[k]) * S.inv[k];
+                const float xraw = (!kImg || k < 4 * kObsChunks) ? xr[k] : 0.f;
+                xv[i] = (xraw - S.mean[k]) * S.inv[k];
                 if (P.obs_clamp > 0.f) xv[i] = fminf(fmaxf(xv[i], -P.obs_clamp), P.obs_clamp);
             }
             quad_mma_step<kW1Stride, kCh / 2>(xv[0], xv[1], wbase + k0, acc);
@@ -212,6 +225,7 @@ BBD void policy_rows8(const bb_policy &P, Smem &S, const PolicyIo &io, int64_t r
         for (int c = 0; c < kCh; c++) acc[c] += acc2[c];
     }
 #else
+    static_assert(!kImg, "the image-fed rows exist for the tensor-core form only");
     float4 xq = orow[0];
 #pragma unroll 2
     for (int k4 = 0; k4 < BB_OBS_DIM / 4; k4++) {
@@ -390,7 +404,7 @@ __global__ void __launch_bounds__(kPolThreads) bb_policy_kernel(const bb_policy 
 
     const int64_t rowStride = (int64_t)gridDim.x * kRowsPerBlock;
     for (int64_t rw0 = (int64_t)blockIdx.x * kRowsPerBlock + (rb & ~7); rw0 < io.n; rw0 += rowStride) { /* warp-uniform trip count */
-        policy_rows8(P, S, io, rw0, rb, q, lane);
+        policy_rows8<false>(P, S, io, rw0, rb, q, lane);
     }
 }
 
@@ -457,6 +471,10 @@ BBD void stage_policy(const bb_policy &P, Smem &S, int tid, int nthreads)
     for (int j = tid; j < kHeads; j += nthreads) S.bh[j] = j < BB_NUM_LOGITS ? P.ba[j] : P.bc[0];
 }
 
+#ifndef BB_ROLLOUT_IMG
+#define BB_ROLLOUT_IMG 1 /* the looping rollout's policy rows read the step's shared-memory observation image (0: the Observations column) */
+#endif
+constexpr bool kLoopImg = BB_ROLLOUT_IMG != 0 && BB_POL_MMA != 0;
 constexpr int kLoopWarps = 2;
 using LoopSmem = PolicySmemT<8 * kLoopWarps>;
 __host__ __device__ constexpr size_t rollout_loop_smem_bytes(bool frozen)
@@ -517,7 +535,8 @@ __global__ void __launch_bounds__(kLoopWarps * 32) bb_rollout_loop_kernel(const 
         } else {
             io.resetCol = C.reset;
         }
-        if (rw0 < n) policy_rows8(trainee, St, io, rw0, rb, q, lane);
+        io.obsImg = tileImg; io.obsImgWorld0 = tileWorld0; io.obsImgRow = agent;
+        if (rw0 < n) policy_rows8<kLoopImg>(trainee, St, io, rw0, rb, q, lane);
         if (t == T) break;
         if (rl.hasFrozen && rw0 < n) { /* env.py:126-143: the frozen policy drives the other agent from its own observation row */
             PolicyIo fo{};
@@ -525,7 +544,8 @@ __global__ void __launch_bounds__(kLoopWarps * 32) bb_rollout_loop_kernel(const 
             fo.obs = C.obs + other * BB_OBS_DIM; fo.obsStride = 2 * BB_OBS_DIM; fo.n = n; fo.rowOffset = rl.worldOffset;
             fo.stochastic = 1; fo.seed = rl.seed; fo.draw = 0x80000000u + rl.drawBase + (uint32_t)t;
             fo.actionsOut = C.action + other * 6; fo.actionStride = 12;
-            policy_rows8(frozen, Sf, fo, rw0, rb, q, lane);
+            fo.obsImg = tileImg; fo.obsImgWorld0 = tileWorld0; fo.obsImgRow = other;
+            policy_rows8<kLoopImg>(frozen, Sf, fo, rw0, rb, q, lane);
         }
         __syncthreads(); /* both warps' sampled actions (and cleared Reset flags) before the step's loads */
         if (warp == 0) step_tile<false, kWorldsPerWarp>(p, p.io, tileImg, tileWorld0, lane);
