@@ -131,7 +131,8 @@ int bb_step_host_u8(bb_engine *e, const uint8_t *actions_host, float *reward_hos
  * columns updated as in bb_step) and publishes completion back; the call returns when the results
  * are in host memory.  No kernel launch and no stream wait per step.  All buffers must be pinned
  * (cudaHostAlloc / torch pin_memory) and must STAY pinned until bb_serve_end: their device aliases are looked up once per
- * serve session.  Between begin and end do not call bb_step* / setters, and
+ * serve session (a combination {actions, reward, done, obs} travels to a 64-slot device-side table on its first use and is
+ * named by its slot afterwards; beyond 64 combinations slots are re-used in turn).  Between begin and end do not call bb_step* / setters, and
  * do not write the exported columns from other streams while a step is in flight.  The server
  * leaves the GPU by itself after 2 s without a step (BB_SERVE_IDLE_MS) and is restarted
  * transparently by the next bb_serve_step; device-wide synchronisation (cudaDeviceSynchronize,
