@@ -1665,17 +1665,24 @@ int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, 
     const char *loopEnv = getenv("BB_ROLLOUT_LOOP"); /* read per call: the tests run both forms in one process */
     bool loop = !(loopEnv && atoi(loopEnv) == 0) && !policy_uses_umma(); /* the looping kernel carries the mma.sync policy rows */
     const int64_t tiles = (n + bb::kWorldsPerWarp - 1) / bb::kWorldsPerWarp;
-    const size_t loopSmem = bb::rollout_loop_smem_bytes(frozen != nullptr);
+    int tpb = 0; /* tiles per block of the looping kernel: 1, or 2 when only that makes the grid resident (frozen opponent) */
     if (loop) { /* only when every block of the looping kernel is resident at once (see the kernel) */
         static bool attr = false;
         if (!attr) {
-            BB_CUDA_OK(cudaFuncSetAttribute(bb::bb_rollout_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bb::rollout_loop_smem_bytes(true)));
+            BB_CUDA_OK(cudaFuncSetAttribute(bb::bb_rollout_loop_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bb::rollout_loop_smem_bytes<1>(true)));
+            BB_CUDA_OK(cudaFuncSetAttribute(bb::bb_rollout_loop_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bb::rollout_loop_smem_bytes<2>(true)));
             attr = true;
         }
-        int perSm = 0, sms = 148;
-        BB_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, bb::bb_rollout_loop_kernel, bb::kLoopWarps * 32, loopSmem));
+        int perSm1 = 0, perSm2 = 0, sms = 148;
+        BB_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm1, bb::bb_rollout_loop_kernel<1>, bb::kLoopWarps * 32, bb::rollout_loop_smem_bytes<1>(frozen != nullptr)));
+        BB_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm2, bb::bb_rollout_loop_kernel<2>, bb::kLoopWarps * 64, bb::rollout_loop_smem_bytes<2>(frozen != nullptr)));
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->cfg.gpu_id);
-        if (tiles > (int64_t)perSm * sms && !(loopEnv && atoi(loopEnv) == 2)) loop = false; /* BB_ROLLOUT_LOOP=2 forces it (tests, A/B) */
+        const int forced = loopEnv ? atoi(loopEnv) : 1; /* 2 / 3: force one / two tiles per block whatever the residency (tests, A/B) */
+        if (forced == 2) tpb = 1;
+        else if (forced == 3) tpb = 2;
+        else if ((tiles + 1) / 2 <= (int64_t)perSm2 * sms) tpb = 2; /* measured 2 % faster than one tile per block where both fit */
+        else if (tiles <= (int64_t)perSm1 * sms) tpb = 1;
+        else loop = false;
     }
     if (loop) {
         bb::RolloutLoop rl{};
@@ -1684,7 +1691,12 @@ int bb_rollout(bb_engine *e, const bb_policy *trainee, const bb_policy *frozen, 
         bb::StepParams p = e->params;
         p.io = bb::StepIo{nullptr, nullptr, nullptr, nullptr, 0, 0};
         p.prefetchBlocks = 0; p.prefetchSelf = 0; p.earlyTrigger = 0;
-        BB_CUDA_OK(launch_pdl(bb::bb_rollout_loop_kernel, (int)tiles, bb::kLoopWarps * 32, loopSmem, st, pdl_for(e, st), p, *trainee, frozen ? *frozen : *trainee, rl));
+        if (tpb == 1)
+            BB_CUDA_OK(launch_pdl(bb::bb_rollout_loop_kernel<1>, (int)tiles, bb::kLoopWarps * 32, bb::rollout_loop_smem_bytes<1>(frozen != nullptr), st,
+                                  pdl_for(e, st), p, *trainee, frozen ? *frozen : *trainee, rl));
+        else
+            BB_CUDA_OK(launch_pdl(bb::bb_rollout_loop_kernel<2>, (int)((tiles + 1) / 2), bb::kLoopWarps * 64, bb::rollout_loop_smem_bytes<2>(frozen != nullptr), st,
+                                  pdl_for(e, st), p, *trainee, frozen ? *frozen : *trainee, rl));
         e->launches += T + 1; /* passes of the step code over every world */
         BB_CUDA_OK(cudaGetLastError());
         return 0;

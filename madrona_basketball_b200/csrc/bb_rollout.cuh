@@ -475,30 +475,38 @@ BBD void stage_policy(const bb_policy &P, Smem &S, int tid, int nthreads)
 #define BB_ROLLOUT_IMG 1 /* the looping rollout's policy rows read the step's shared-memory observation image (0: the Observations column) */
 #endif
 constexpr bool kLoopImg = BB_ROLLOUT_IMG != 0 && BB_POL_MMA != 0;
-constexpr int kLoopWarps = 2;
-using LoopSmem = PolicySmemT<8 * kLoopWarps>;
+constexpr int kLoopWarps = 2; /* warps per tile */
+/* kTPB tiles per block (1 or 2): the policy weights are staged once per BLOCK, so two tiles per block halve their share of
+ * shared memory -- with a frozen opponent (two weight sets) that is what lets 8192 envs be resident at once. */
+template <int kTPB> using LoopSmemT = PolicySmemT<8 * kLoopWarps * kTPB>;
+template <int kTPB>
 __host__ __device__ constexpr size_t rollout_loop_smem_bytes(bool frozen)
 {
-    return sizeof(LoopSmem) * (frozen ? 2 : 1) + (size_t)kWorldsPerWarp * kImgWorld4 * 16;
+    return sizeof(LoopSmemT<kTPB>) * (frozen ? 2 : 1) + (size_t)kTPB * kWorldsPerWarp * kImgWorld4 * 16;
 }
 
-__global__ void __launch_bounds__(kLoopWarps * 32) bb_rollout_loop_kernel(const __grid_constant__ StepParams p, const bb_policy trainee,
-                                                                          const bb_policy frozen, const RolloutLoop rl)
+template <int kTPB>
+__global__ void __launch_bounds__(kLoopWarps * 32 * kTPB) bb_rollout_loop_kernel(const __grid_constant__ StepParams p, const bb_policy trainee,
+                                                                                 const bb_policy frozen, const RolloutLoop rl)
 {
+    using LoopSmem = LoopSmemT<kTPB>;
+    constexpr int kThreads = kLoopWarps * 32 * kTPB;
     extern __shared__ float4 smem4[];
     LoopSmem &St = *reinterpret_cast<LoopSmem *>(smem4);
     LoopSmem &Sf = *(reinterpret_cast<LoopSmem *>(smem4) + 1);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, q = tid & 3, rb = tid >> 2;
-    float4 *tileImg = reinterpret_cast<float4 *>(reinterpret_cast<LoopSmem *>(smem4) + (rl.hasFrozen ? 2 : 1));
+    const int tileInBlock = warp / kLoopWarps, half = warp % kLoopWarps;
+    float4 *tileImg = reinterpret_cast<float4 *>(reinterpret_cast<LoopSmem *>(smem4) + (rl.hasFrozen ? 2 : 1)) + tileInBlock * kWorldsPerWarp * kImgWorld4;
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    stage_policy(trainee, St, tid, kLoopWarps * 32);
-    if (rl.hasFrozen) stage_policy(frozen, Sf, tid, kLoopWarps * 32);
+    stage_policy(trainee, St, tid, kThreads);
+    if (rl.hasFrozen) stage_policy(frozen, Sf, tid, kThreads);
     const Columns &C = p.col;
     const int64_t n = p.numWorlds;
-    const int64_t tileWorld0 = (int64_t)blockIdx.x * kWorldsPerWarp;
-    if (tileWorld0 >= n) return; /* block-uniform */
+    if ((int64_t)blockIdx.x * kTPB * kWorldsPerWarp >= n) return; /* block-uniform */
+    const int64_t tileWorld0 = ((int64_t)blockIdx.x * kTPB + tileInBlock) * kWorldsPerWarp;
+    const bool stepper = half == 0 && tileWorld0 < n; /* this warp steps the tile (a block's last tile may lie past the end: it only keeps the barriers) */
     const int agent = rl.agentIdx, T = rl.buf.horizon;
-    if (warp == 0) { /* env.reset(), env.py:178-185: Reset flags = 1, trainee action = 0, one step (the flags are cleared by the first policy call) */
+    if (stepper) { /* env.reset(), env.py:178-185: Reset flags = 1, trainee action = 0, one step (the flags are cleared by the first policy call) */
         const int64_t w = tileWorld0 + (lane >> 1);
         const int me = lane & 1;
         if (w < n) {
@@ -512,7 +520,7 @@ __global__ void __launch_bounds__(kLoopWarps * 32) bb_rollout_loop_kernel(const 
         step_tile<false, kWorldsPerWarp>(p, p.io, tileImg, tileWorld0, lane);
     }
     __syncthreads(); /* the staged weights; the reset step's observation rows before the first policy call's loads */
-    const int64_t rw0 = tileWorld0 + 8 * warp; /* this warp's 8 rows */
+    const int64_t rw0 = tileWorld0 + 8 * half; /* this warp's 8 rows */
     for (int t = 0; t <= T; t++) {
         PolicyIo io{};
         io.obs = C.obs + agent * BB_OBS_DIM; io.obsStride = 2 * BB_OBS_DIM; io.n = n; io.rowOffset = rl.worldOffset;
@@ -547,8 +555,8 @@ __global__ void __launch_bounds__(kLoopWarps * 32) bb_rollout_loop_kernel(const 
             fo.obsImg = tileImg; fo.obsImgWorld0 = tileWorld0; fo.obsImgRow = other;
             policy_rows8<kLoopImg>(frozen, Sf, fo, rw0, rb, q, lane);
         }
-        __syncthreads(); /* both warps' sampled actions (and cleared Reset flags) before the step's loads */
-        if (warp == 0) step_tile<false, kWorldsPerWarp>(p, p.io, tileImg, tileWorld0, lane);
+        __syncthreads(); /* the tile's sampled actions (and cleared Reset flags) before the step's loads */
+        if (stepper) step_tile<false, kWorldsPerWarp>(p, p.io, tileImg, tileWorld0, lane);
         __syncthreads(); /* the step's observation rows, reward and done before the next policy call's loads */
     }
 }

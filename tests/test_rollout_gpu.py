@@ -152,14 +152,16 @@ def _reference_rollout(sim, w, frozen_w, buf_shape, agent_idx, seed, draw_base, 
     return out
 
 
-@pytest.mark.parametrize("form", ["one_launch", "kernel_chain"])
+@pytest.mark.parametrize("form", ["one_launch", "one_launch_two_tiles_per_block", "kernel_chain"])
 @pytest.mark.parametrize("agent_idx,with_frozen", [(1, False), (0, True)])
 def test_fused_rollout_matches_stepwise_loop(agent_idx, with_frozen, form, monkeypatch):
-    """bb_rollout in both forms -- the whole rollout as one launch of bb_rollout_loop_kernel (default) and the chain of policy /
-    step kernels (BB_ROLLOUT_LOOP=0) -- against ppo.py's rollout() replayed step by step: every buffer bit for bit."""
+    """bb_rollout in its three forms -- the whole rollout as one launch of bb_rollout_loop_kernel with one or two tiles per block
+    (the latter: n = 700 is 44 tiles, so the last block's second tile... is a real one; 22 blocks) and the chain of policy / step
+    kernels (BB_ROLLOUT_LOOP=0) -- against ppo.py's rollout() replayed step by step: every buffer bit for bit."""
     import torch
 
-    monkeypatch.setenv("BB_ROLLOUT_LOOP", "2" if form == "one_launch" else "0")   # 2: also when the grid is not resident at once
+    # 2 / 3: the looping kernel with one / two tiles per block, also when the grid is not resident at once
+    monkeypatch.setenv("BB_ROLLOUT_LOOP", {"one_launch": "2", "one_launch_two_tiles_per_block": "3", "kernel_chain": "0"}[form])
     monkeypatch.setenv("BB_POLICY_UMMA_FORCE", "0")     # the stepwise reference below calls bb_policy_forward: same kernel family
 
     from madrona_basketball_b200.rollout import FusedRollout, PolicyWeights, RolloutBuffers

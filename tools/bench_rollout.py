@@ -25,6 +25,8 @@ def main():
     ap.add_argument("--steps", type=int, default=32)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--agent-idx", type=int, default=1)
+    ap.add_argument("--frozen", action="store_true", help="self-play: a frozen opponent policy drives the other agent (fused path only)")
+    ap.add_argument("--no-torch", action="store_true", help="skip the torch loop")
     args = ap.parse_args()
     import torch
 
@@ -79,19 +81,22 @@ def main():
             obs = obs_
         return agent.logits_value(obs)[1]
 
-    for _ in range(3):
-        torch_rollout()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    for _ in range(args.iters):
-        torch_rollout()
-    torch.cuda.synchronize()
-    t_torch = (time.perf_counter() - t0) / args.iters
+    t_torch = float("nan")
+    if not args.no_torch:
+        for _ in range(3):
+            torch_rollout()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(args.iters):
+            torch_rollout()
+        torch.cuda.synchronize()
+        t_torch = (time.perf_counter() - t0) / args.iters
 
     # ---------------------------------------------------------------- (b) fused
     sim2 = mk()
     buf = RolloutBuffers(T, n, dev)
-    fr = FusedRollout(sim2, PolicyWeights.from_module(agent), idx, seed=321)
+    frozen_w = PolicyWeights.from_module(randomize(RefAgent(), seed=2, scale_heads=2.0).to(dev).eval()) if args.frozen else None
+    fr = FusedRollout(sim2, PolicyWeights.from_module(agent), idx, frozen=frozen_w, seed=321)
     for _ in range(3):
         fr.collect(buf)
     torch.cuda.synchronize()
@@ -121,7 +126,7 @@ def main():
     steps = n * (T + 1)   # env.reset() is one more simulator step per rollout
     print(json.dumps({
         "what": "rollout of ppo.py defaults on one B200: env.reset() + T x (policy forward + sample, sim step, bookkeeping)",
-        "envs": n, "rollout_steps": T, "iters": args.iters, "agent_idx": idx,
+        "envs": n, "rollout_steps": T, "iters": args.iters, "agent_idx": idx, "frozen_opponent": bool(args.frozen),
         "torch_loop": {"s_per_rollout": t_torch, "env_steps_per_s": steps / t_torch,
                        "what": "torch Agent.forward + Categorical sampling, env.py-style step with 3 clones, PPOStats host sync per step"},
         "fused": {"s_per_rollout": t_fused, "s_per_rollout_device": t_fused_dev, "env_steps_per_s": steps / t_fused,
