@@ -10,7 +10,8 @@
  * (ppo_stats.py:26 `dones.any()`).  Here one kernel does the whole forward + sampling for
  * every environment, reads the observation rows straight from the step engine's column,
  * writes the sampled action into the engine's Action column and fills the rollout buffer
- * (scripts/buffers.py:4-21); a whole T-step rollout is 2 kernels per step with no host
+ * (scripts/buffers.py:4-21); a whole T-step rollout is ONE kernel launch when its grid is resident at once (each block
+ * takes its worlds through policy rows and steps in turn; otherwise 2 kernels per step), with no host
  * synchronisation, and compute_advantages' GAE scan (ppo.py:144-166) is one kernel.
  *
  * Plain pointers and sizes only.  All pointers are DEVICE pointers unless stated.
@@ -88,7 +89,8 @@ int bb_umma_selftest(const float *a_dev, const float *b_dev, float *d_dev, int k
  * actions[:, 1 - agent_idx] = frozen.forward(observations[:, 1 - agent_idx]), env.py:126-143];
  * Manager::step; record obs / action / value / log-prob / reward / not-done; episode statistics },
  * then next_value = critic(observations after the last step).  Everything is enqueued on
- * `cuda_stream` (2 kernels per step, 3 with a frozen opponent) without host synchronisation.
+ * `cuda_stream` (one launch of the looping kernel when the grid is resident at once -- up to ~9400 envs on a B200 --
+ * otherwise 2 kernels per step, 3 with a frozen opponent; BB_ROLLOUT_LOOP=0 forces the chain) without host synchronisation.
  * `frozen` may be NULL (the other agent then keeps the action hardCodeDefenseSystem wrote).
  * `draw_base`: the sampling streams use draws draw_base .. draw_base + T - 1 (trainee) and
  * 0x80000000 + the same (frozen opponent). */
