@@ -173,6 +173,40 @@ __device__ __constant__ int kBucketOff[BB_NUM_ACTION_DIMS] = {0, 2, 10, 13, 15, 
 __device__ __constant__ int kBucketCnt[BB_NUM_ACTION_DIMS] = {2, 8, 3, 2, 2, 2};
 __device__ __constant__ int kQuadBuckets[4][2] = {{0, 2}, {1, -1}, {3, 4}, {5, -1}};
 
+/* One bucketed categorical (action.py:20-33) over the cnt <= kMax logits l[0..cnt): returns log_prob(a) = l[a] - logsumexp and
+ * the action a -- stochastic: inverse CDF, the smallest a with u * s < e_0 + .. + e_a, u = (word >> 8) * 2^-24; otherwise argmax.
+ * The exponentials are computed once and kept in registers (the loops are unrolled to kMax and predicated on cnt); sums run in
+ * index order, so the bits are those of the plain loops. */
+template <int kMax>
+BBD float sample_bucket(const float *l, int cnt, bool stochastic, uint32_t word, int &aOut)
+{
+    float m = l[0];
+#pragma unroll
+    for (int i = 1; i < kMax; i++) if (i < cnt) m = fmaxf(m, l[i]);
+    float e[kMax];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMax; i++) {
+        e[i] = 0.f;
+        if (i < cnt) { e[i] = expf(l[i] - m); s += e[i]; }
+    }
+    const float lse = m + logf(s);
+    int a = 0;
+    if (stochastic) {
+        const float us = ((float)(word >> 8) * 0x1p-24f) * s;
+        float c = 0.f;
+        bool found = false;
+        a = cnt - 1;
+#pragma unroll
+        for (int i = 0; i < kMax; i++)
+            if (i < cnt && !found) { c += e[i]; if (us < c) { a = i; found = true; } }
+    } else {
+        for (int i = 1; i < cnt; i++) if (l[i] > l[a]) a = i;
+    }
+    aOut = a;
+    return l[a] - lse;
+}
+
 /* Agent.forward + sampling + rollout bookkeeping for the 8 rows rw0 .. rw0 + 7 on the calling warp (quad (rb & 7) takes row
  * rw0 + (rb & 7); rb = the quad's row slot in S.hid / S.out; all 32 lanes must call it).  The body of bb_policy_kernel's row
  * loop, shared with bb_rollout_loop_kernel: the same instructions in the same order, hence the same bits. */
@@ -304,34 +338,24 @@ BBD void policy_rows8(const bb_policy &P, Smem &S, const PolicyIo &io, int64_t r
     }
     __syncwarp();
     if (!io.evaluateOnly) {
-        /* ---- bucketed categoricals (action.py:5-33): this thread's one or two buckets ---- */
+        /* ---- bucketed categoricals (action.py:5-33): this thread's one or two buckets ----
+         * Threefry call c gives the words of buckets 2c (x0) and 2c + 1 (x1).  The quad needs call 0 (q0: bucket 0, q1: bucket 1),
+         * call 1 (q0: bucket 2, q2: bucket 3) and call 2 (q2: bucket 4, q3: bucket 5): q0 / q1 compute call 0, q2 call 1, q3 call 2
+         * -- ONE Threefry per thread -- and the words of the second pass travel by shuffle (q0 takes call 1's x0 from q2, q2 call
+         * 2's x0 from q3).  Same words, same buckets as one call per bucket. */
         float lp[2] = {0.f, 0.f};
+        uint32_t wx0 = 0u, wx1 = 0u;
+        if (io.stochastic) threefry2x32(io.seed, (uint32_t)(io.rowOffset + r), io.draw, (uint32_t)(q < 2 ? 0 : q - 1), wx0, wx1);
+        const uint32_t nx0 = __shfl_sync(0xffffffffu, wx0, (lane & ~3) + (q == 0 ? 2 : 3));
 #pragma unroll
         for (int s2 = 0; s2 < 2; s2++) {
             const int b = kQuadBuckets[q][s2];
             if (b < 0) continue;
-            const int off = kBucketOff[b], cnt = kBucketCnt[b];
-            const float *l = &S.out[rb][off];
-            float m = l[0];
-            for (int i = 1; i < cnt; i++) m = fmaxf(m, l[i]);
-            float s = 0.f;
-            for (int i = 0; i < cnt; i++) s += expf(l[i] - m);
-            const float lse = m + logf(s);
-            int a = 0;
-            if (io.stochastic) { /* inverse CDF: smallest a with u * s < e_0 + .. + e_a; word (b & 1) of Threefry call b >> 1 */
-                uint32_t x0, x1;
-                threefry2x32(io.seed, (uint32_t)(io.rowOffset + r), io.draw, (uint32_t)(b >> 1), x0, x1);
-                const float us = ((float)(((b & 1) ? x1 : x0) >> 8) * 0x1p-24f) * s;
-                float c = 0.f;
-                a = cnt - 1;
-                for (int i = 0; i < cnt; i++) {
-                    c += expf(l[i] - m);
-                    if (us < c) { a = i; break; }
-                }
-            } else {
-                for (int i = 1; i < cnt; i++) if (l[i] > l[a]) a = i;
-            }
-            lp[s2] = l[a] - lse;
+            const float *l = &S.out[rb][kBucketOff[b]];
+            int a;
+            /* first pass: buckets of 2 / 8 / 2 / 2 entries over the quad; second pass: 3 / - / 2 / - */
+            if (s2 == 0) lp[0] = sample_bucket<8>(l, kBucketCnt[b], io.stochastic != 0, (b & 1) ? wx1 : wx0, a);
+            else lp[1] = sample_bucket<3>(l, kBucketCnt[b], io.stochastic != 0, nx0, a);
             if (valid) {
                 if (io.actionsOut) io.actionsOut[r * io.actionStride + b] = a;
                 if (io.bufActions) io.bufActions[r * BB_NUM_ACTION_DIMS + b] = (float)a;
