@@ -293,15 +293,22 @@ def test_packed_u8_action_rows_match_int32_rows(n):
         b.step_host(np.zeros((n, 2, 6), np.uint8))
 
 
-@pytest.mark.parametrize("serve_threads", ["32", "128"])
-def test_server_buffer_combinations_and_bound_calls(monkeypatch, serve_threads):
+@pytest.mark.parametrize("serve_threads,binding", [("32", "fastcall"), ("128", "fastcall"), ("32", "ctypes")])
+def test_server_buffer_combinations_and_bound_calls(monkeypatch, serve_threads, binding):
     """The doorbell is one word carrying the slot of a device-side table of buffer combinations {actions, reward, done, obs}:
     a ring of action buffers LARGER than the 64-slot table (slots are re-used), int32 and packed rows in turn, two sets of
     result buffers, steps without result buffers, every call through bind_serve_step (the bound C-ABI call of
-    csrc/bb_fastcall.c when it is built) == the same steps as ordinary launches.  Both block sizes of the server."""
+    csrc/bb_fastcall.c, and the ctypes closure it falls back to) == the same steps as ordinary launches.  Both block sizes
+    of the server."""
     import torch
 
     monkeypatch.setenv("BB_SERVE_THREADS", serve_threads)
+    from madrona_basketball_b200 import manager
+
+    if binding == "ctypes":       # the closure over the ctypes function that bind_serve_step falls back to without the glue module
+        monkeypatch.setattr(manager, "_FASTCALL", None)
+    else:
+        assert manager._fastcall_module() is not None, "csrc/bb_fastcall.c is not built (python -m madrona_basketball_b200.build)"
     n, ring, steps = 300, 70, 160
     a, b = make_engine(n), make_engine(n)
     act = torch.empty((n, 2, 6), dtype=torch.int32, device="cuda")
